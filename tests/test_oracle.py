@@ -1,0 +1,153 @@
+"""CPU tests: pin the oracle (our restatement) to the reference.
+
+1. against tests/golden/ (streams produced by the compiled reference, committed);
+2. against oracle/_ref (the reference compiled in place) on seeded random reads,
+   when that library exists (it does in the build container and travels to the
+   GPU box; /root/reference itself is never read at test time).
+"""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import cpu_impl
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+METHODS = list(cpu_impl.METHODS)
+
+
+@pytest.fixture(scope="module")
+def three_reads():
+    z = np.load(os.path.join(GOLD, "three_reads.npz"))
+    return z["samples"], z["offsets"], [str(x) for x in z["ids"]]
+
+
+def test_three_reads_shape(three_reads):
+    samples, offsets, ids = three_reads
+    assert np.diff(offsets).tolist() == [7329, 155185, 95350]
+    assert samples.dtype == np.int16 and samples.size == 257864
+
+
+@pytest.mark.parametrize("method", METHODS)
+def test_oracle_matches_reference_golden_three_reads(oracle, three_reads, method):
+    samples, offsets, ids = three_reads
+    gold = json.load(open(os.path.join(GOLD, "three_reads_ref.json")))
+    for r, rid in enumerate(ids):
+        s = samples[int(offsets[r]):int(offsets[r + 1])]
+        rc, st = oracle.press(method, s)
+        assert rc == 0
+        g = gold[rid][method]
+        assert len(st) == g["bytes"]
+        assert hashlib.sha256(st).hexdigest() == g["sha256"]
+        rc, back = oracle.depress(method, st, s.size)
+        assert rc == 0 and np.array_equal(back, s)
+
+
+def test_blow5_frames_are_vbz_svb_zd(oracle, three_reads):
+    """The .blow5 fixture stores each signal as [n u32][svb32 over zd]: a
+    known-answer vector written by slow5lib, not by press.c."""
+    samples, offsets, ids = three_reads
+    z = np.load(os.path.join(GOLD, "three_reads.npz"))
+    for r in range(3):
+        s = samples[int(offsets[r]):int(offsets[r + 1])]
+        rc, st = oracle.press("vbz_svb_zd", s)
+        assert rc == 0 and f"{cpu_impl.fnv1a64(st):016x}" == str(z["frame_fnv"][r])
+
+
+def _small_cases():
+    z = np.load(os.path.join(GOLD, "small_streams.npz"))
+    names = sorted({k.split("/")[0] for k in z.files})
+    return z, names
+
+
+@pytest.mark.parametrize("method", METHODS)
+def test_oracle_matches_reference_small_streams(oracle, method):
+    z, names = _small_cases()
+    for name in names:
+        s = z[f"{name}/in"]
+        ref_rc = int(z[f"{name}/{method}/rc"])
+        ref_st = z[f"{name}/{method}"].tobytes()
+        rc, st = oracle.press(method, s)
+        assert (rc == 0) == (ref_rc == 0), (name, rc, ref_rc)
+        if rc != 0:
+            continue
+        assert st == ref_st, (name, method)
+        if method == "shuff_vbe21_zd" and len(st) - (6 + 6 * int.from_bytes(st[2:6], "little")) <= 4:
+            assert oracle.depress(method, st, s.size)[0] != 0   # huffman.c:706 memread quirk
+            continue
+        rc, back = oracle.depress(method, st, s.size)
+        assert rc == 0 and np.array_equal(back, s), (name, method)
+
+
+def _random_read(rng, kind, n):
+    if kind == "walk":
+        return (475 + np.cumsum(rng.integers(-25, 26, n))).astype(np.int16)
+    if kind == "spiky":
+        d = rng.integers(-12, 13, n)
+        idx = rng.random(n) < 0.01
+        d[idx] = rng.integers(-900, 900, int(idx.sum()))
+        return (500 + np.cumsum(d)).astype(np.int16)
+    if kind == "q":
+        return ((100 + np.cumsum(rng.integers(-6, 7, n))) << int(rng.integers(1, 7))).astype(np.int16)
+    return rng.integers(-32768, 32768, n).astype(np.int16)       # "noise": mostly exceptions
+
+
+@pytest.mark.parametrize("method", METHODS)
+def test_oracle_matches_compiled_reference_random(oracle, ref, method):
+    rng = np.random.default_rng(1234)
+    for trial in range(60):
+        kind = ["walk", "spiky", "q", "noise"][trial % 4]
+        n = int(rng.integers(1, 6000)) if trial % 5 else int(rng.integers(1, 40))
+        s = _random_read(rng, kind, n)
+        rc_r, st_r = ref.press(method, s)
+        rc_o, st_o = oracle.press(method, s)
+        assert (rc_r == 0) == (rc_o == 0), (kind, n)
+        if rc_r != 0:
+            continue
+        assert st_o == st_r, (method, kind, n)
+        nsym = None
+        if method == "shuff_vbe21_zd":
+            nsym = len(st_o) - (6 + 6 * int.from_bytes(st_o[2:6], "little"))
+        if nsym is not None and nsym <= 4:
+            continue
+        rc2, b = oracle.depress(method, st_r, n)
+        assert rc2 == 0 and np.array_equal(b, s), (method, kind, n)
+        if method == "shuff_vbe21_zd" and 4 + 6 * int.from_bytes(st_o[2:6], "little") > 2 * n:
+            continue    # press.c:4472 sizes its scratch 2n bytes: the reference overflows it
+        rc, a = ref.depress(method, st_o, n)
+        assert rc == 0 and np.array_equal(a, s), (method, kind, n)
+
+
+def test_building_blocks(oracle):
+    import ctypes as C
+    lib = oracle.lib
+    lib.oracle_zigzag16.restype = C.c_uint16
+    lib.oracle_zigzag16.argtypes = [C.c_int16]
+    lib.oracle_unzigzag16.restype = C.c_int16
+    lib.oracle_unzigzag16.argtypes = [C.c_uint16]
+    assert [lib.oracle_zigzag16(x) for x in (0, -1, 1, -2, 2, 32767, -32768)] == \
+        [0, 1, 2, 3, 4, 65534, 65535]
+    for z in (0, 1, 2, 255, 256, 65534, 65535):
+        assert lib.oracle_zigzag16(lib.oracle_unzigzag16(z)) == z
+    lib.oracle_find_qts.restype = C.c_uint8
+    lib.oracle_find_qts.argtypes = [C.POINTER(C.c_int16), C.c_uint64, C.c_uint8]
+    for vals, q in (([4, 8, 0, -12], 2), ([0, 0], 5), ([64, 128], 5), ([3], 0), ([-32768], 5)):
+        a = np.array(vals, dtype=np.int16)
+        assert lib.oracle_find_qts(a.ctypes.data_as(C.POINTER(C.c_int16)), a.size, 5) == q
+
+
+def test_ex_zd_scratch_cap_failure(oracle, ref):
+    """ex_zd.c:411 -- stream longer than 2n + 1024 makes the reference return -1."""
+    rng = np.random.default_rng(7)
+    s = rng.integers(-32768, 32768, 20000).astype(np.int16) | 1   # q = 0, ~all exceptions
+    assert ref.press("ex_zd", s)[0] != 0
+    assert oracle.press("ex_zd", s)[0] != 0
+
+
+def test_cpu_driver_round_trips(oracle, three_reads):
+    samples, offsets, _ = three_reads
+    for m in ("svb16_zd", "ex_zd", "shuff_vbe21_zd"):
+        res = oracle.run_batch(m, samples, offsets, threads=2)
+        assert res["rc"] == 0 and res["mismatches"] == 0 and res["errors"] == 0
