@@ -1,0 +1,356 @@
+// press_gpu.cu -- C ABI of libpress_gpu.so (see include/press_gpu.h).
+//
+// Host side only: context, scratch layout, launch sequences, the per-read
+// drop-ins (press.h signatures) built on the batch path, and the host-buffer
+// batch path.  All device code lives in the .cuh files next to this one.
+#include "../../include/press_gpu.h"
+
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <mutex>
+#include <vector>
+
+#include "common.cuh"
+#include "plan.cuh"
+#include "svb_zd.cuh"
+#include "host_ctx.h"
+
+using namespace pg;
+
+// ---------------------------------------------------------------------------
+// context
+
+namespace {
+
+char g_err[512] = "";
+uint64_t g_launches = 0;
+std::once_flag g_once;
+HostCtx g_ctx;
+
+void set_err(const char *fmt, ...)
+{
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(g_err, sizeof g_err, fmt, ap);
+	va_end(ap);
+	fprintf(stderr, "press_gpu: %s\n", g_err);
+}
+
+#define CK(call)                                                                      \
+	do {                                                                          \
+		cudaError_t e_ = (call);                                              \
+		if (e_ != cudaSuccess) {                                              \
+			set_err("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+				__FILE__, __LINE__);                                  \
+			return -1;                                                    \
+		}                                                                     \
+	} while (0)
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+int ensure_init()
+{
+	if (g_ctx.ready)
+		return 0;
+	return press_gpu_init(-1);
+}
+
+}  // namespace
+
+// scratch layout -------------------------------------------------------------
+namespace pg {
+
+uint64_t max_tiles(uint64_t nreads, uint64_t nsamples)
+{
+	return nsamples / TILE + 2 * nreads + 2;
+}
+
+ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples)
+{
+	(void) method;
+	ScratchLayout l;
+	const uint64_t mt = max_tiles(nreads, nsamples);
+	size_t o = 0;
+	l.hdr = o;		o += sizeof(Hdr);
+	l.status = o;		o += align_up(mt * 8, 256);
+	l.status2 = o;		o += align_up(mt * 8, 256);
+	l.zero_bytes = o;	// [0, zero_bytes) is cleared before every batch call
+	l.tile_start = o;	o += align_up((nreads + 1) * 4, 256);
+	l.kx = o;		o += align_up((nreads + 1) * 8, 256);
+	l.tile_read = o;	o += align_up(mt * 4, 256);
+	l.total = o;
+	return l;
+}
+
+}  // namespace pg
+
+extern "C" {
+
+int press_gpu_init(int device)
+{
+	if (g_ctx.ready)
+		return 0;
+	int ndev = 0;
+	cudaError_t e = cudaGetDeviceCount(&ndev);
+	if (e != cudaSuccess || ndev == 0) {
+		set_err("no CUDA device (%s); libpress_gpu has no CPU fallback",
+			e != cudaSuccess ? cudaGetErrorString(e) : "count = 0");
+		return -1;
+	}
+	if (device >= 0)
+		CK(cudaSetDevice(device));
+	CK(cudaGetDevice(&g_ctx.device));
+	cudaDeviceProp prop;
+	CK(cudaGetDeviceProperties(&prop, g_ctx.device));
+	if (prop.major < 10) {
+		set_err("device %d is sm_%d%d; this library is built for sm_100a only", g_ctx.device,
+			prop.major, prop.minor);
+		return -1;
+	}
+	g_ctx.sms = prop.multiProcessorCount;
+	CK(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
+	g_ctx.ready = true;
+	return 0;
+}
+
+void press_gpu_shutdown(void)
+{
+	if (!g_ctx.ready)
+		return;
+	g_ctx.release();
+	cudaStreamDestroy(g_ctx.stream);
+	g_ctx.ready = false;
+}
+
+const char *press_gpu_last_error(void) { return g_err; }
+const char *press_gpu_version(void) { return "press_gpu 0.1 sm_100a"; }
+uint64_t press_gpu_launch_count(void) { return g_launches; }
+
+uint64_t press_gpu_batch_bound(int method, uint64_t nreads, uint64_t nsamples)
+{
+	switch (method) {
+	case PRESS_GPU_SVB16_ZD: return 2 * nsamples + nsamples / 8 + nreads + 16;
+	case PRESS_GPU_VBZ_SVB16_ZD: return 2 * nsamples + nsamples / 8 + 5 * nreads + 16;
+	case PRESS_GPU_SVB_ZD: return 2 * nsamples + nsamples / 4 + nreads + 16;
+	case PRESS_GPU_VBZ_SVB_ZD: return 2 * nsamples + nsamples / 4 + 5 * nreads + 16;
+	default: break;
+	}
+	return 0;
+}
+
+size_t press_gpu_batch_scratch_bytes(int method, uint64_t nreads, uint64_t nsamples)
+{
+	return scratch_layout(method, nreads, nsamples).total;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// launch sequences
+
+namespace {
+
+template <typename K>
+int persistent_grid(K kernel, int *grid)
+{
+	int per_sm = 0;
+	CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, NT, 0));
+	if (per_sm < 1)
+		per_sm = 1;
+	*grid = per_sm * g_ctx.sms;
+	return 0;
+}
+
+int run_plan(const ScratchLayout &l, uint8_t *scr, const uint64_t *d_offsets, uint64_t nreads,
+	     int tiling, uint32_t frame, uint32_t keydiv, uint32_t fixed, cudaStream_t st)
+{
+	CK(cudaMemsetAsync(scr, 0, l.zero_bytes, st));
+	PlanArgs pa;
+	pa.offsets = d_offsets;
+	pa.nreads = nreads;
+	pa.tiling = tiling;
+	pa.frame = frame;
+	pa.keydiv = keydiv;
+	pa.fixed = fixed;
+	pa.tile_start = reinterpret_cast<uint32_t *>(scr + l.tile_start);
+	pa.kx = reinterpret_cast<uint64_t *>(scr + l.kx);
+	pa.hdr = reinterpret_cast<Hdr *>(scr + l.hdr);
+	plan_scan_kernel<<<1, 1024, 0, st>>>(pa);
+	g_launches++;
+	if (nreads) {
+		unsigned blocks = (unsigned) ((nreads * 32 + 255) / 256);
+		plan_fill_kernel<<<blocks, 256, 0, st>>>(pa.tile_start, nreads,
+							 reinterpret_cast<uint32_t *>(scr + l.tile_read));
+		g_launches++;
+	}
+	CK(cudaGetLastError());
+	return 0;
+}
+
+template <int KEYBITS, bool FRAME>
+int launch_svb_encode(const SvbEncArgs &a, cudaStream_t st)
+{
+	int grid;
+	if (persistent_grid(svb_zd_encode_kernel<KEYBITS, FRAME>, &grid))
+		return -1;
+	svb_zd_encode_kernel<KEYBITS, FRAME><<<grid, NT, 0, st>>>(a);
+	g_launches++;
+	CK(cudaGetLastError());
+	return 0;
+}
+
+template <int KEYBITS, bool FRAME>
+int launch_svb_decode(const SvbDecArgs &a, cudaStream_t st)
+{
+	int grid;
+	if (persistent_grid(svb_zd_decode_kernel<KEYBITS, FRAME>, &grid))
+		return -1;
+	svb_zd_decode_kernel<KEYBITS, FRAME><<<grid, NT, 0, st>>>(a);
+	g_launches++;
+	CK(cudaGetLastError());
+	return 0;
+}
+
+bool is_svb(int m) { return m >= PRESS_GPU_SVB16_ZD && m <= PRESS_GPU_VBZ_SVB_ZD; }
+
+}  // namespace
+
+extern "C" {
+
+int press_gpu_batch_press(int method, const int16_t *d_samples, const uint64_t *d_offsets,
+			  uint64_t nreads, uint64_t nsamples, uint8_t *d_out, uint64_t out_capacity,
+			  uint64_t *d_out_offsets, void *d_scratch, size_t scratch_bytes, void *stream)
+{
+	if (ensure_init())
+		return -1;
+	cudaStream_t st = stream ? (cudaStream_t) stream : g_ctx.stream;
+	const ScratchLayout l = scratch_layout(method, nreads, nsamples);
+	if (scratch_bytes < l.total) {
+		set_err("scratch too small: %zu < %zu", scratch_bytes, l.total);
+		return -1;
+	}
+	if ((reinterpret_cast<uintptr_t>(d_samples) & 15) || (reinterpret_cast<uintptr_t>(d_scratch) & 255)) {
+		set_err("d_samples must be 16-byte and d_scratch 256-byte aligned");
+		return -1;
+	}
+	if (max_tiles(nreads, nsamples) >= (1ull << 32)) {
+		set_err("batch too large: split it (tile ids are 32-bit)");
+		return -1;
+	}
+	uint8_t *scr = static_cast<uint8_t *>(d_scratch);
+	CK(cudaMemsetAsync(d_out_offsets, 0xff, (nreads + 1) * sizeof(uint64_t), st));
+
+	if (is_svb(method)) {
+		const bool frame = method == PRESS_GPU_VBZ_SVB16_ZD || method == PRESS_GPU_VBZ_SVB_ZD;
+		const bool k2 = method == PRESS_GPU_SVB_ZD || method == PRESS_GPU_VBZ_SVB_ZD;
+		if (run_plan(l, scr, d_offsets, nreads, TILING_ALIGNED, frame ? 4 : 0, k2 ? 4 : 8, 0, st))
+			return -1;
+		SvbEncArgs a;
+		a.samples = reinterpret_cast<const uint4 *>(d_samples);
+		a.nsamples = nsamples;
+		a.offsets = d_offsets;
+		a.nreads = nreads;
+		a.out = d_out;
+		a.out_cap = out_capacity;
+		a.out_offsets = d_out_offsets;
+		a.hdr = reinterpret_cast<Hdr *>(scr + l.hdr);
+		a.tile_start = reinterpret_cast<const uint32_t *>(scr + l.tile_start);
+		a.tile_read = reinterpret_cast<const uint32_t *>(scr + l.tile_read);
+		a.kx = reinterpret_cast<const uint64_t *>(scr + l.kx);
+		a.status = reinterpret_cast<uint64_t *>(scr + l.status);
+		if (!k2 && !frame) return launch_svb_encode<1, false>(a, st);
+		if (!k2 && frame) return launch_svb_encode<1, true>(a, st);
+		if (k2 && !frame) return launch_svb_encode<2, false>(a, st);
+		return launch_svb_encode<2, true>(a, st);
+	}
+	set_err("batch_press: method %d not implemented", method);
+	return -1;
+}
+
+int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_in_offsets,
+			    uint64_t in_bytes, const uint64_t *d_offsets, uint64_t nreads,
+			    uint64_t nsamples, int16_t *d_samples_out, void *d_scratch,
+			    size_t scratch_bytes, void *stream)
+{
+	if (ensure_init())
+		return -1;
+	cudaStream_t st = stream ? (cudaStream_t) stream : g_ctx.stream;
+	const ScratchLayout l = scratch_layout(method, nreads, nsamples);
+	if (scratch_bytes < l.total) {
+		set_err("scratch too small: %zu < %zu", scratch_bytes, l.total);
+		return -1;
+	}
+	if ((reinterpret_cast<uintptr_t>(d_samples_out) & 15) || (reinterpret_cast<uintptr_t>(d_scratch) & 255)) {
+		set_err("d_samples_out must be 16-byte and d_scratch 256-byte aligned");
+		return -1;
+	}
+	if (max_tiles(nreads, nsamples) >= (1ull << 32)) {
+		set_err("batch too large: split it (tile ids are 32-bit)");
+		return -1;
+	}
+	uint8_t *scr = static_cast<uint8_t *>(d_scratch);
+
+	if (is_svb(method)) {
+		const bool frame = method == PRESS_GPU_VBZ_SVB16_ZD || method == PRESS_GPU_VBZ_SVB_ZD;
+		const bool k2 = method == PRESS_GPU_SVB_ZD || method == PRESS_GPU_VBZ_SVB_ZD;
+		if (run_plan(l, scr, d_offsets, nreads, TILING_READ, frame ? 4 : 0, k2 ? 4 : 8, 0, st))
+			return -1;
+		SvbDecArgs a;
+		a.in = d_in;
+		a.in_bytes = in_bytes;
+		a.in_offsets = d_in_offsets;
+		a.offsets = d_offsets;
+		a.nreads = nreads;
+		a.samples_out = d_samples_out;
+		a.hdr = reinterpret_cast<Hdr *>(scr + l.hdr);
+		a.tile_start = reinterpret_cast<const uint32_t *>(scr + l.tile_start);
+		a.tile_read = reinterpret_cast<const uint32_t *>(scr + l.tile_read);
+		a.status_bytes = reinterpret_cast<uint64_t *>(scr + l.status);
+		a.status_sum = reinterpret_cast<uint64_t *>(scr + l.status2);
+		if (!k2 && !frame) return launch_svb_decode<1, false>(a, st);
+		if (!k2 && frame) return launch_svb_decode<1, true>(a, st);
+		if (k2 && !frame) return launch_svb_decode<2, false>(a, st);
+		return launch_svb_decode<2, true>(a, st);
+	}
+	set_err("batch_depress: method %d not implemented", method);
+	return -1;
+}
+
+int press_gpu_batch_status(void *d_scratch, void *stream)
+{
+	if (ensure_init())
+		return -1;
+	cudaStream_t st = stream ? (cudaStream_t) stream : g_ctx.stream;
+	Hdr h;
+	if (cudaMemcpyAsync(&h, d_scratch, sizeof h, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+	    cudaStreamSynchronize(st) != cudaSuccess) {
+		set_err("batch_status: %s", cudaGetErrorString(cudaGetLastError()));
+		return -1;
+	}
+	return (int) h.error;
+}
+
+void *press_gpu_host_alloc(size_t bytes)
+{
+	void *p = nullptr;
+	if (ensure_init() || cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+		set_err("host_alloc(%zu) failed", bytes);
+		return nullptr;
+	}
+	return p;
+}
+
+void press_gpu_host_free(void *p)
+{
+	if (p)
+		cudaFreeHost(p);
+}
+
+}  // extern "C"
+
+#include "host_paths.inc"
+#include "todo_stubs.inc"

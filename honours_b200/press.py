@@ -1,0 +1,245 @@
+"""ctypes mirror of include/press_gpu.h.
+
+Per-read calls mirror the reference's press.h triples
+(``X_bound(nin)``, ``X_press(in, nin, out, *nout)``, ``X_depress(in, nin, out, *nout)``,
+press/press.h:10-33) with numpy arrays as the host buffers; the batch calls take
+raw device pointers (``tensor.data_ptr()``) exactly like the C ABI.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+
+METHODS = {
+    "svb16_zd": 0,
+    "svb_zd": 1,
+    "vbz_svb16_zd": 2,
+    "vbz_svb_zd": 3,
+    "vbe21_zd": 4,
+    "vbsse21_zd": 5,
+    "ex_zd": 6,
+    "shuff_vbe21_zd": 7,
+}
+
+# per-read entry points of include/press_gpu.h, by method
+PER_READ = {
+    "svb16_zd": ("svb12_zd_gpu_bound", "svb12_zd_gpu_press", "svb12_zd_gpu_depress"),
+    "svb_zd": ("svb_zd_gpu_bound_16", "svb_zd_gpu_press_16", "svb_zd_gpu_depress_16"),
+    "vbz_svb16_zd": ("vbz_svb12_zd_gpu_bound", "vbz_svb12_zd_gpu_press", "vbz_svb12_zd_gpu_depress"),
+    "vbz_svb_zd": ("vbz_svb_zd_gpu_bound_16", "vbz_svb_zd_gpu_press_16", "vbz_svb_zd_gpu_depress_16"),
+    "vbe21_zd": ("vbe21_zd_gpu_bound_16", "vbe21_zd_gpu_press_16", "vbe21_zd_gpu_depress_16"),
+    "vbsse21_zd": ("vbsse21_zd_gpu_bound_16", "vbsse21_zd_gpu_press_16", "vbsse21_zd_gpu_depress_16"),
+    "ex_zd": ("hasgam_vbsse21_zdq_gpu_bound_16", "hasgam_vbsse21_zdq_gpu_press_16",
+              "hasgam_vbsse21_zdq_gpu_depress_16"),
+    "shuff_vbe21_zd": ("shuffman_vbe21_zd_gpu_bound_16", "shuffman_vbe21_zd_gpu_press_16",
+                       "shuffman_vbe21_zd_gpu_depress_16"),
+}
+
+
+class PressGpuError(RuntimeError):
+    pass
+
+
+def lib_path() -> str:
+    return os.path.join(PKG, "libpress_gpu.so")
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load libpress_gpu.so.  Fails loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        p = lib_path()
+        if not os.path.exists(p):
+            raise PressGpuError(
+                f"{p} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(there is no CPU fallback)")
+        L = C.CDLL(p)
+        vp, u64, i32, sz = C.c_void_p, C.c_uint64, C.c_int, C.c_size_t
+        L.press_gpu_init.restype = i32
+        L.press_gpu_init.argtypes = [i32]
+        L.press_gpu_last_error.restype = C.c_char_p
+        L.press_gpu_version.restype = C.c_char_p
+        L.press_gpu_launch_count.restype = u64
+        L.press_gpu_set_huffman_table.restype = i32
+        L.press_gpu_set_huffman_table.argtypes = [C.c_char_p, sz]
+        L.press_gpu_batch_bound.restype = u64
+        L.press_gpu_batch_bound.argtypes = [i32, u64, u64]
+        L.press_gpu_batch_scratch_bytes.restype = sz
+        L.press_gpu_batch_scratch_bytes.argtypes = [i32, u64, u64]
+        L.press_gpu_batch_press.restype = i32
+        L.press_gpu_batch_press.argtypes = [i32, vp, vp, u64, u64, vp, u64, vp, vp, sz, vp]
+        L.press_gpu_batch_depress.restype = i32
+        L.press_gpu_batch_depress.argtypes = [i32, vp, vp, u64, vp, u64, u64, vp, vp, sz, vp]
+        L.press_gpu_batch_status.restype = i32
+        L.press_gpu_batch_status.argtypes = [vp, vp]
+        L.press_gpu_batch_press_host.restype = i32
+        L.press_gpu_batch_press_host.argtypes = [i32, vp, vp, u64, vp, u64, vp]
+        L.press_gpu_batch_depress_host.restype = i32
+        L.press_gpu_batch_depress_host.argtypes = [i32, vp, vp, vp, u64, vp]
+        L.press_gpu_host_alloc.restype = vp
+        L.press_gpu_host_alloc.argtypes = [sz]
+        L.press_gpu_host_free.argtypes = [vp]
+        _lib = L
+    return _lib
+
+
+def last_error() -> str:
+    return lib().press_gpu_last_error().decode()
+
+
+def init(device: int = -1) -> None:
+    if lib().press_gpu_init(device) != 0:
+        raise PressGpuError(last_error())
+
+
+def set_huffman_table(blob: bytes | None = None) -> None:
+    if blob is None:
+        blob = open(os.path.join(PKG, "data", "NA12878_zd.huffman"), "rb").read()
+    if lib().press_gpu_set_huffman_table(blob, len(blob)) != 0:
+        raise PressGpuError(last_error())
+
+
+# ---------------------------------------------------------------------------
+# per-read mirror of press.h
+
+def bound(method: str, nin: int) -> int:
+    f = getattr(lib(), PER_READ[method][0])
+    f.restype = C.c_uint64
+    f.argtypes = [C.c_uint64 if method in ("svb16_zd", "svb_zd") else C.c_uint32]
+    return int(f(nin))
+
+
+def press(method: str, sig: np.ndarray) -> tuple[int, bytes]:
+    """``X_press(in, nin, out, &nout)`` -> (return code, stream bytes[:nout])."""
+    L = lib()
+    sig = np.ascontiguousarray(sig, dtype=np.int16)
+    n = sig.size
+    cap = bound(method, n) + 8 * n + 64     # harness slack, like oracle/cpu_driver.c
+    out = np.zeros(cap, dtype=np.uint8)
+    nout = C.c_uint64(cap)
+    f = getattr(L, PER_READ[method][1])
+    rc = 0
+    if method in ("svb16_zd", "svb_zd"):
+        f.restype = None
+        f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64)]
+        f(sig.ctypes.data, n, out.ctypes.data, C.byref(nout))
+    elif method in ("vbe21_zd", "vbsse21_zd"):
+        f.restype = None
+        f.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]
+        f(sig.ctypes.data, n, out.ctypes.data, C.byref(nout))
+    elif method == "shuff_vbe21_zd":
+        f.restype = C.c_int
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]
+        rc = f(None, sig.ctypes.data, n, out.ctypes.data, C.byref(nout))
+    else:
+        f.restype = C.c_int
+        f.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]
+        rc = f(sig.ctypes.data, n, out.ctypes.data, C.byref(nout))
+    return rc, out[: nout.value].tobytes()
+
+
+def depress(method: str, stream: bytes, n: int) -> tuple[int, np.ndarray]:
+    """``X_depress(in, nin, out, &nout)`` -> (return code, samples[:nout]).
+
+    ``nin`` is the sample count for the svb methods and the byte count for the
+    others, as in press.h."""
+    L = lib()
+    buf = np.zeros(len(stream) + 64, dtype=np.uint8)
+    buf[: len(stream)] = np.frombuffer(stream, dtype=np.uint8)
+    out = np.zeros(n + 64, dtype=np.int16)
+    f = getattr(L, PER_READ[method][2])
+    rc = 0
+    if method in ("svb16_zd", "svb_zd"):
+        nout = C.c_uint64(n)
+        f.restype = None
+        f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64)]
+        f(buf.ctypes.data, n, out.ctypes.data, C.byref(nout))
+    elif method in ("vbe21_zd", "vbsse21_zd"):
+        nout = C.c_uint32(n)
+        f.restype = None
+        f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint32)]
+        f(buf.ctypes.data, len(stream), out.ctypes.data, C.byref(nout))
+    elif method == "shuff_vbe21_zd":
+        nout = C.c_uint32(n)
+        f.restype = C.c_int
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint32)]
+        rc = f(None, buf.ctypes.data, len(stream), out.ctypes.data, C.byref(nout))
+    else:
+        nout = C.c_uint32(n)
+        f.restype = C.c_int
+        f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint32)]
+        rc = f(buf.ctypes.data, len(stream), out.ctypes.data, C.byref(nout))
+    return rc, out[: nout.value].copy()
+
+
+# ---------------------------------------------------------------------------
+# batch mirror (raw pointers; host variants take numpy arrays)
+
+def batch_bound(method: str, nreads: int, nsamples: int) -> int:
+    return int(lib().press_gpu_batch_bound(METHODS[method], nreads, nsamples))
+
+
+def batch_scratch_bytes(method: str, nreads: int, nsamples: int) -> int:
+    return int(lib().press_gpu_batch_scratch_bytes(METHODS[method], nreads, nsamples))
+
+
+def batch_press(method: str, d_samples: int, d_offsets: int, nreads: int, nsamples: int,
+                d_out: int, out_capacity: int, d_out_offsets: int, d_scratch: int,
+                scratch_bytes: int, stream: int = 0) -> None:
+    rc = lib().press_gpu_batch_press(METHODS[method], d_samples, d_offsets, nreads, nsamples,
+                                     d_out, out_capacity, d_out_offsets, d_scratch,
+                                     scratch_bytes, stream)
+    if rc != 0:
+        raise PressGpuError(last_error())
+
+
+def batch_depress(method: str, d_in: int, d_in_offsets: int, in_bytes: int, d_offsets: int,
+                  nreads: int, nsamples: int, d_samples_out: int, d_scratch: int,
+                  scratch_bytes: int, stream: int = 0) -> None:
+    rc = lib().press_gpu_batch_depress(METHODS[method], d_in, d_in_offsets, in_bytes, d_offsets,
+                                       nreads, nsamples, d_samples_out, d_scratch,
+                                       scratch_bytes, stream)
+    if rc != 0:
+        raise PressGpuError(last_error())
+
+
+def batch_status(d_scratch: int, stream: int = 0) -> int:
+    return int(lib().press_gpu_batch_status(d_scratch, stream))
+
+
+def batch_press_host(method: str, samples: np.ndarray, offsets: np.ndarray):
+    """Host-buffer batch compress -> (rc, container bytes (uint8 array), out_offsets)."""
+    samples = np.ascontiguousarray(samples, dtype=np.int16)
+    offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+    nreads = offsets.size - 1
+    nsamples = int(offsets[-1] - offsets[0])
+    cap = batch_bound(method, nreads, nsamples)
+    out = np.empty(cap, dtype=np.uint8)
+    oo = np.zeros(nreads + 1, dtype=np.uint64)
+    rc = lib().press_gpu_batch_press_host(METHODS[method], samples.ctypes.data, offsets.ctypes.data,
+                                          nreads, out.ctypes.data, cap, oo.ctypes.data)
+    if rc < 0:
+        raise PressGpuError(last_error())
+    return rc, out[: int(oo[-1])], oo
+
+
+def batch_depress_host(method: str, container: np.ndarray, in_offsets: np.ndarray,
+                       offsets: np.ndarray) -> np.ndarray:
+    container = np.ascontiguousarray(container, dtype=np.uint8)
+    in_offsets = np.ascontiguousarray(in_offsets, dtype=np.uint64)
+    offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+    nreads = offsets.size - 1
+    out = np.zeros(int(offsets[-1]), dtype=np.int16)
+    rc = lib().press_gpu_batch_depress_host(METHODS[method], container.ctypes.data,
+                                            in_offsets.ctypes.data, offsets.ctypes.data,
+                                            nreads, out.ctypes.data)
+    if rc != 0:
+        raise PressGpuError(last_error())
+    return out

@@ -1,0 +1,169 @@
+/* press_gpu.h -- C ABI of libpress_gpu.so: the B200 (sm_100a) implementation of
+ * the per-read zd / svb16 / svb32 / exception / static-Huffman hot path of the
+ * `press` benchmark (sashajenner/honours, directory press/).
+ *
+ * Two layers, both plain C (no CUDA or torch types in any signature):
+ *
+ *  1. Per-read drop-ins with the reference's own press.h signatures, suffixed
+ *     _gpu, so press/test.c can select them with TEST(<method>_gpu, ...)
+ *     (press/test.h:10-37).  Host pointers in and out, synchronous.
+ *  2. A batch API on DEVICE-resident reads (this is what is measured): all
+ *     reads concatenated, one launch sequence per batch, tight container out.
+ *
+ * There is no CPU fallback: every entry point fails (nonzero / 0 bytes + a
+ * line on stderr, press_gpu_last_error()) when no sm_100 device is usable.
+ *
+ * Reference interface replaced by each entry point is cited as
+ * (press/<file>:<line>) relative to /root/reference.
+ */
+#ifndef PRESS_GPU_H
+#define PRESS_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- methods (batch API selector) --------------------------------------- */
+enum press_gpu_method {
+	PRESS_GPU_SVB16_ZD = 0,		/* svb12_zd_*              press.h:346-352  */
+	PRESS_GPU_SVB_ZD = 1,		/* svb_zd_*_16             press.h:322-328  */
+	PRESS_GPU_VBZ_SVB16_ZD = 2,	/* zstd_svb12_zd_* minus zstd: [n u32] + svb16-zd, press.c:2025-2045 */
+	PRESS_GPU_VBZ_SVB_ZD = 3,	/* zstd_svb_zd_*_16 minus zstd: [n u32] + svb-zd,  press.c:1865-1885 */
+	PRESS_GPU_VBE21_ZD = 4,		/* vbe21_zd_*_16           press.h:496-502  */
+	PRESS_GPU_VBSSE21_ZD = 5,	/* vbsse21_zd_*_16         press.c:3543-3580 */
+	PRESS_GPU_EX_ZD = 6,		/* hasgam_vbsse21_zdq_*_16 press.h:958-964, ex_zd.c */
+	PRESS_GPU_SHUFF_VBE21_ZD = 7,	/* shuffman_vbe21_zd_*_16  press.h:632-638  */
+	PRESS_GPU_NMETHODS = 8
+};
+
+/* ---- context ------------------------------------------------------------- */
+/* Bind the calling process to CUDA device `device` (-1: current device) and
+ * create the library's stream and staging buffers.  Idempotent.  0 on success. */
+int press_gpu_init(int device);
+void press_gpu_shutdown(void);
+/* Last error text of this process ("" if none). */
+const char *press_gpu_last_error(void);
+/* Library version / build arch string, e.g. "press_gpu 0.1 sm_100a". */
+const char *press_gpu_version(void);
+/* Number of kernel launches issued by this library so far (bench evidence). */
+uint64_t press_gpu_launch_count(void);
+
+/* Install the static Huffman code table from a code-table FILE IMAGE (the
+ * 1042-byte press/NA12878_zd.huffman; format of huffman.c:440-480).  Replaces
+ * read_code_table + build_symbol_encoder (press/test.c:3786-3791,
+ * huffman.c:549-694, 353-365).  0 on success. */
+int press_gpu_set_huffman_table(const uint8_t *file_image, size_t len);
+
+/* ---- 1. per-read drop-ins (host pointers; press.h signatures) ------------ */
+/* svb16-zd: press.h:346-352 (press.c:1678-1694).  depress nin = SAMPLES. */
+uint64_t svb12_zd_gpu_bound(uint64_t nin);
+void svb12_zd_gpu_press(const int16_t *in, uint64_t nin, uint8_t *out, uint64_t *nout);
+void svb12_zd_gpu_depress(const uint8_t *in, uint64_t nin, int16_t *out, uint64_t *nout);
+
+/* classical svb-zd: press.h:322-328 (press.c:1585-1612).  depress nin = SAMPLES. */
+uint64_t svb_zd_gpu_bound_16(uint64_t nin);
+void svb_zd_gpu_press_16(const int16_t *in, uint64_t nin, uint8_t *out, uint64_t *nout);
+void svb_zd_gpu_depress_16(const uint8_t *in, uint64_t nin, int16_t *out, uint64_t *nout);
+
+/* VBZ, the part before / after zstd (zstd itself stays on the host, outside
+ * this library): press.h:378-384, 402-408 (press.c:1860-1910, 2020-2070).
+ * press writes tmp = [nin u32 LE] ++ stream, exactly what the reference hands
+ * to zstd_press (press.c:1881, 2041); depress takes that tmp. */
+uint64_t vbz_svb_zd_gpu_bound_16(uint32_t nin);
+int vbz_svb_zd_gpu_press_16(const int16_t *in, uint32_t nin, uint8_t *out, uint64_t *nout);
+int vbz_svb_zd_gpu_depress_16(const uint8_t *in, uint64_t nin, int16_t *out, uint32_t *nout);
+uint64_t vbz_svb12_zd_gpu_bound(uint32_t nin);
+int vbz_svb12_zd_gpu_press(const int16_t *in, uint32_t nin, uint8_t *out, uint64_t *nout);
+int vbz_svb12_zd_gpu_depress(const uint8_t *in, uint64_t nin, int16_t *out, uint32_t *nout);
+
+/* vbe21-zd: press.h:496-502 (press.c:3411-3448).  depress nin = BYTES. */
+uint64_t vbe21_zd_gpu_bound_16(uint32_t nin);
+void vbe21_zd_gpu_press_16(const int16_t *in, uint32_t nin, uint8_t *out, uint64_t *nout);
+void vbe21_zd_gpu_depress_16(uint8_t *in, uint64_t nin, int16_t *out, uint32_t *nout);
+
+/* vbsse21-zd: press.c:3543-3580.  depress nin = BYTES. */
+uint64_t vbsse21_zd_gpu_bound_16(uint32_t nin);
+void vbsse21_zd_gpu_press_16(const int16_t *in, uint32_t nin, uint8_t *out, uint64_t *nout);
+void vbsse21_zd_gpu_depress_16(uint8_t *in, uint64_t nin, int16_t *out, uint32_t *nout);
+
+/* ex-zd v0: press.h:958-964 (press.c:8461-8501, ex_zd.c).  0 ok / -1 failure
+ * (including the reference's own 2n+1024 scratch-cap failure, ex_zd.c:411). */
+uint64_t hasgam_vbsse21_zdq_gpu_bound_16(uint32_t nin);
+int hasgam_vbsse21_zdq_gpu_press_16(const int16_t *in, uint32_t nin, uint8_t *out, uint64_t *nout);
+int hasgam_vbsse21_zdq_gpu_depress_16(uint8_t *in, uint64_t nin, int16_t *out, uint32_t *nout);
+
+/* static-Huffman-zd: press.h:632-638 (press.c:4409-4498).  The reference
+ * passes SymbolEncoder* / huffman_node*; here the first argument is an opaque
+ * table handle: NULL selects the table installed by press_gpu_set_huffman_table.
+ * depress: *nout = expected sample count on entry (press.c:4472).  0 ok / 1 error. */
+uint64_t shuffman_vbe21_zd_gpu_bound_16(uint32_t nin);
+int shuffman_vbe21_zd_gpu_press_16(const void *table, const int16_t *in, uint32_t nin,
+				   uint8_t *out, uint64_t *nout);
+int shuffman_vbe21_zd_gpu_depress_16(const void *table, uint8_t *in, uint64_t nin,
+				     int16_t *out, uint32_t *nout);
+
+/* ---- 2. batch API (device pointers) --------------------------------------
+ * Layout: d_samples = all reads back to back (int16, base 16-byte aligned),
+ * d_offsets[nreads+1] = sample index of each read's first sample (read r is
+ * [d_offsets[r], d_offsets[r+1]); any alignment).  The container d_out holds
+ * the per-read streams back to back with no gaps, stream r at byte
+ * d_out_offsets[r], total bytes in d_out_offsets[nreads]; each stream is byte
+ * identical to what the per-read reference function writes.
+ * `stream` is a cudaStream_t passed as void* (NULL = the library's stream).
+ * All calls are asynchronous on that stream and return 0 when enqueued;
+ * failures detected on the device (capacity, malformed stream, ex-zd scratch
+ * cap) are reported by press_gpu_batch_status() after synchronisation. */
+
+/* upper bound on container bytes for a batch (sum of the per-read bounds, tightened
+ * to what the format can actually produce) */
+uint64_t press_gpu_batch_bound(int method, uint64_t nreads, uint64_t nsamples);
+/* device scratch the batch calls need for (nreads, nsamples) */
+size_t press_gpu_batch_scratch_bytes(int method, uint64_t nreads, uint64_t nsamples);
+
+int press_gpu_batch_press(int method, const int16_t *d_samples, const uint64_t *d_offsets,
+			  uint64_t nreads, uint64_t nsamples, uint8_t *d_out,
+			  uint64_t out_capacity, uint64_t *d_out_offsets,
+			  void *d_scratch, size_t scratch_bytes, void *stream);
+
+int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_in_offsets,
+			    uint64_t in_bytes, const uint64_t *d_offsets, uint64_t nreads,
+			    uint64_t nsamples, int16_t *d_samples_out, void *d_scratch,
+			    size_t scratch_bytes, void *stream);
+
+/* Device-side error word of the last batch call that used d_scratch (blocks
+ * until `stream` is idle).  0 = ok; bit 0 capacity exceeded, bit 1 malformed
+ * input, bit 2 ex-zd scratch cap (the reference would have returned -1). */
+int press_gpu_batch_status(void *d_scratch, void *stream);
+
+/* Host-buffer batch (end-to-end path): pinned staging, H2D, kernels, D2H, all
+ * inside the call.  h_out must hold press_gpu_batch_bound() bytes. */
+int press_gpu_batch_press_host(int method, const int16_t *h_samples, const uint64_t *h_offsets,
+			       uint64_t nreads, uint8_t *h_out, uint64_t out_capacity,
+			       uint64_t *h_out_offsets);
+int press_gpu_batch_depress_host(int method, const uint8_t *h_in, const uint64_t *h_in_offsets,
+				 const uint64_t *h_offsets, uint64_t nreads, int16_t *h_samples_out);
+
+/* pinned host memory for the host-buffer path (cudaHostAlloc / cudaFreeHost) */
+void *press_gpu_host_alloc(size_t bytes);
+void press_gpu_host_free(void *p);
+
+/* ---- synthetic NA12878-like reads (bench / test workload generator) -------
+ * Deterministic, integer-only, identical on host and device: read r, sample i
+ * depend only on (seed, r, i-walk).  d_/h_ variants fill samples for reads
+ * whose lengths are given by offsets; x0[r] is the first sample, shift[r] the
+ * left shift applied to every sample (0 normally; 2 gives q = 2 reads).
+ * p_ex_u32 = exception probability * 2^32.  hist = 256 one-byte-zd counts. */
+int press_gpu_synth_device(int16_t *d_samples, const uint64_t *d_offsets, uint64_t nreads,
+			   const int16_t *d_x0, const uint8_t *d_shift, const uint64_t *hist256,
+			   uint32_t p_ex_u32, uint64_t seed, void *stream);
+int press_gpu_synth_host(int16_t *h_samples, const uint64_t *h_offsets, uint64_t nreads,
+			 const int16_t *h_x0, const uint8_t *h_shift, const uint64_t *hist256,
+			 uint32_t p_ex_u32, uint64_t seed);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PRESS_GPU_H */
