@@ -47,7 +47,7 @@ struct HostCtx {
 	int device = 0;
 	int sms = 0;
 	cudaStream_t stream = nullptr;
-	GrowBuf samples, offsets, out, out_offsets, scratch;
+	GrowBuf samples, offsets, out, out_offsets, scratch, misc;
 	void release()
 	{
 		samples.release();
@@ -55,6 +55,7 @@ struct HostCtx {
 		out.release();
 		out_offsets.release();
 		scratch.release();
+		misc.release();
 	}
 };
 

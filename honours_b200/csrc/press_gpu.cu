@@ -17,6 +17,7 @@
 #include "common.cuh"
 #include "plan.cuh"
 #include "svb_zd.cuh"
+#include "synth.cuh"
 #include "host_ctx.h"
 
 using namespace pg;
@@ -49,6 +50,33 @@ void set_err(const char *fmt, ...)
 			return -1;                                                    \
 		}                                                                     \
 	} while (0)
+
+// event brackets around the main kernels (press_gpu_profile_*)
+struct EvPair { cudaEvent_t a, b; int kind; };
+bool g_prof = false;
+std::vector<EvPair> g_ev_pending, g_ev_free;
+
+EvPair *prof_begin(int kind, cudaStream_t st)
+{
+	if (!g_prof)
+		return nullptr;
+	EvPair p;
+	if (!g_ev_free.empty()) {
+		p = g_ev_free.back();
+		g_ev_free.pop_back();
+	} else if (cudaEventCreate(&p.a) != cudaSuccess || cudaEventCreate(&p.b) != cudaSuccess) {
+		return nullptr;
+	}
+	p.kind = kind;
+	cudaEventRecord(p.a, st);
+	g_ev_pending.push_back(p);
+	return &g_ev_pending.back();
+}
+void prof_end(EvPair *p, cudaStream_t st)
+{
+	if (p)
+		cudaEventRecord(p->b, st);
+}
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
@@ -129,6 +157,10 @@ void press_gpu_shutdown(void)
 const char *press_gpu_last_error(void) { return g_err; }
 const char *press_gpu_version(void) { return "press_gpu 0.1 sm_100a"; }
 uint64_t press_gpu_launch_count(void) { return g_launches; }
+int press_gpu_method_implemented(int method)
+{
+	return method >= PRESS_GPU_SVB16_ZD && method <= PRESS_GPU_VBZ_SVB_ZD;
+}
 
 uint64_t press_gpu_batch_bound(int method, uint64_t nreads, uint64_t nsamples)
 {
@@ -197,7 +229,9 @@ int launch_svb_encode(const SvbEncArgs &a, cudaStream_t st)
 	int grid;
 	if (persistent_grid(svb_zd_encode_kernel<KEYBITS, FRAME>, &grid))
 		return -1;
+	EvPair *ev = prof_begin(0, st);
 	svb_zd_encode_kernel<KEYBITS, FRAME><<<grid, NT, 0, st>>>(a);
+	prof_end(ev, st);
 	g_launches++;
 	CK(cudaGetLastError());
 	return 0;
@@ -209,7 +243,9 @@ int launch_svb_decode(const SvbDecArgs &a, cudaStream_t st)
 	int grid;
 	if (persistent_grid(svb_zd_decode_kernel<KEYBITS, FRAME>, &grid))
 		return -1;
+	EvPair *ev = prof_begin(1, st);
 	svb_zd_decode_kernel<KEYBITS, FRAME><<<grid, NT, 0, st>>>(a);
+	prof_end(ev, st);
 	g_launches++;
 	CK(cudaGetLastError());
 	return 0;
@@ -334,6 +370,55 @@ int press_gpu_batch_status(void *d_scratch, void *stream)
 	return (int) h.error;
 }
 
+void press_gpu_profile_enable(int on) { g_prof = on != 0; }
+
+int press_gpu_profile_collect(double ms[2], uint64_t launches[2])
+{
+	ms[0] = ms[1] = 0;
+	launches[0] = launches[1] = 0;
+	for (EvPair &p : g_ev_pending) {
+		float t = 0;
+		CK(cudaEventSynchronize(p.b));
+		CK(cudaEventElapsedTime(&t, p.a, p.b));
+		ms[p.kind] += t;
+		launches[p.kind]++;
+		g_ev_free.push_back(p);
+	}
+	g_ev_pending.clear();
+	return 0;
+}
+
+__global__ void global_offsets_kernel(const uint64_t *gathered, int nranks, uint64_t nreads,
+				      uint64_t *global)
+{
+	const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	const uint64_t total = (uint64_t) nranks * nreads;
+	if (i > total)
+		return;
+	const int k = i == total ? nranks : (int) (i / nreads);
+	uint64_t base = 0;
+	for (int j = 0; j < k; j++)
+		base += gathered[(uint64_t) j * (nreads + 1) + nreads];
+	global[i] = i == total ? base : base + gathered[(uint64_t) k * (nreads + 1) + (i - (uint64_t) k * nreads)];
+}
+
+int press_gpu_global_offsets(const uint64_t *d_gathered, int nranks, uint64_t nreads,
+			     uint64_t *d_global, void *stream)
+{
+	if (ensure_init())
+		return -1;
+	if (nranks < 1 || nreads == 0) {
+		set_err("global_offsets: nranks >= 1 and nreads >= 1 required");
+		return -1;
+	}
+	cudaStream_t st = stream ? (cudaStream_t) stream : g_ctx.stream;
+	const uint64_t total = (uint64_t) nranks * nreads + 1;
+	global_offsets_kernel<<<(unsigned) ((total + 255) / 256), 256, 0, st>>>(d_gathered, nranks, nreads, d_global);
+	g_launches++;
+	CK(cudaGetLastError());
+	return 0;
+}
+
 void *press_gpu_host_alloc(size_t bytes)
 {
 	void *p = nullptr;
@@ -353,4 +438,5 @@ void press_gpu_host_free(void *p)
 }  // extern "C"
 
 #include "host_paths.inc"
+#include "synth_host.inc"
 #include "todo_stubs.inc"

@@ -67,6 +67,8 @@ def lib() -> C.CDLL:
         L.press_gpu_last_error.restype = C.c_char_p
         L.press_gpu_version.restype = C.c_char_p
         L.press_gpu_launch_count.restype = u64
+        L.press_gpu_method_implemented.restype = i32
+        L.press_gpu_method_implemented.argtypes = [i32]
         L.press_gpu_set_huffman_table.restype = i32
         L.press_gpu_set_huffman_table.argtypes = [C.c_char_p, sz]
         L.press_gpu_batch_bound.restype = u64
@@ -83,11 +85,26 @@ def lib() -> C.CDLL:
         L.press_gpu_batch_press_host.argtypes = [i32, vp, vp, u64, vp, u64, vp]
         L.press_gpu_batch_depress_host.restype = i32
         L.press_gpu_batch_depress_host.argtypes = [i32, vp, vp, vp, u64, vp]
+        L.press_gpu_global_offsets.restype = i32
+        L.press_gpu_global_offsets.argtypes = [vp, i32, u64, vp, vp]
+        L.press_gpu_profile_enable.restype = None
+        L.press_gpu_profile_enable.argtypes = [i32]
+        L.press_gpu_profile_collect.restype = i32
+        L.press_gpu_profile_collect.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
         L.press_gpu_host_alloc.restype = vp
         L.press_gpu_host_alloc.argtypes = [sz]
         L.press_gpu_host_free.argtypes = [vp]
         _lib = L
     return _lib
+
+
+def implemented_methods() -> list[str]:
+    L = lib()
+    return [m for m, k in METHODS.items() if L.press_gpu_method_implemented(k)]
+
+
+def launch_count() -> int:
+    return int(lib().press_gpu_launch_count())
 
 
 def last_error() -> str:
@@ -243,3 +260,41 @@ def batch_depress_host(method: str, container: np.ndarray, in_offsets: np.ndarra
     if rc != 0:
         raise PressGpuError(last_error())
     return out
+
+
+def global_offsets(d_gathered: int, nranks: int, nreads: int, d_global: int, stream: int = 0) -> None:
+    if lib().press_gpu_global_offsets(d_gathered, nranks, nreads, d_global, stream) != 0:
+        raise PressGpuError(last_error())
+
+
+def profile_enable(on: bool) -> None:
+    lib().press_gpu_profile_enable(1 if on else 0)
+
+
+def profile_collect() -> tuple[list[float], list[int]]:
+    """-> ([encode ms, decode ms], [encode launches, decode launches]) since the last call."""
+    ms = (C.c_double * 2)()
+    n = (C.c_uint64 * 2)()
+    if lib().press_gpu_profile_collect(ms, n) != 0:
+        raise PressGpuError(last_error())
+    return [ms[0], ms[1]], [int(n[0]), int(n[1])]
+
+
+def pinned_array(nbytes: int) -> np.ndarray:
+    """uint8 numpy view of cudaHostAlloc'd memory (kept alive by the returned array's base)."""
+    p = lib().press_gpu_host_alloc(nbytes)
+    if not p:
+        raise PressGpuError(last_error())
+    buf = (C.c_uint8 * nbytes).from_address(p)
+    arr = np.frombuffer(buf, dtype=np.uint8)
+    _pinned[arr.ctypes.data] = p
+    return arr
+
+
+def pinned_free(arr: np.ndarray) -> None:
+    p = _pinned.pop(arr.ctypes.data, None)
+    if p:
+        lib().press_gpu_host_free(p)
+
+
+_pinned: dict[int, int] = {}

@@ -50,6 +50,8 @@ const char *press_gpu_last_error(void);
 const char *press_gpu_version(void);
 /* Number of kernel launches issued by this library so far (bench evidence). */
 uint64_t press_gpu_launch_count(void);
+/* 1 if the batch calls accept `method` in this build, else 0. */
+int press_gpu_method_implemented(int method);
 
 /* Install the static Huffman code table from a code-table FILE IMAGE (the
  * 1042-byte press/NA12878_zd.huffman; format of huffman.c:440-480).  Replaces
@@ -146,22 +148,37 @@ int press_gpu_batch_press_host(int method, const int16_t *h_samples, const uint6
 int press_gpu_batch_depress_host(int method, const uint8_t *h_in, const uint64_t *h_in_offsets,
 				 const uint64_t *h_offsets, uint64_t nreads, int16_t *h_samples_out);
 
+/* Multi-GPU container index: d_gathered holds every rank's
+ * d_out_offsets array ([nranks][nreads + 1], the result of an NCCL allgather
+ * of the per-read compressed byte positions); writes the byte offset of every
+ * read of every rank inside ONE contiguous container, rank-major:
+ * d_global[k * nreads + r], total bytes in d_global[nranks * nreads]. */
+int press_gpu_global_offsets(const uint64_t *d_gathered, int nranks, uint64_t nreads,
+			     uint64_t *d_global, void *stream);
+
+/* Kernel timing for bench.py's roofline: when enabled every main codec kernel
+ * launch is bracketed by CUDA events on its stream.  collect() waits for them
+ * and returns, since the last collect, the summed device milliseconds and the
+ * launch counts of [0] encode kernels and [1] decode kernels. */
+void press_gpu_profile_enable(int on);
+int press_gpu_profile_collect(double ms[2], uint64_t launches[2]);
+
 /* pinned host memory for the host-buffer path (cudaHostAlloc / cudaFreeHost) */
 void *press_gpu_host_alloc(size_t bytes);
 void press_gpu_host_free(void *p);
 
 /* ---- synthetic NA12878-like reads (bench / test workload generator) -------
- * Deterministic, integer-only, identical on host and device: read r, sample i
- * depend only on (seed, r, i-walk).  d_/h_ variants fill samples for reads
+ * Deterministic, integer-only, identical on host and device: the samples of
+ * read r depend only on (seed, first_read + r), so shards of one batch agree.  d_/h_ variants fill samples for reads
  * whose lengths are given by offsets; x0[r] is the first sample, shift[r] the
  * left shift applied to every sample (0 normally; 2 gives q = 2 reads).
  * p_ex_u32 = exception probability * 2^32.  hist = 256 one-byte-zd counts. */
 int press_gpu_synth_device(int16_t *d_samples, const uint64_t *d_offsets, uint64_t nreads,
 			   const int16_t *d_x0, const uint8_t *d_shift, const uint64_t *hist256,
-			   uint32_t p_ex_u32, uint64_t seed, void *stream);
+			   uint32_t p_ex_u32, uint64_t seed, uint64_t first_read, void *stream);
 int press_gpu_synth_host(int16_t *h_samples, const uint64_t *h_offsets, uint64_t nreads,
 			 const int16_t *h_x0, const uint8_t *h_shift, const uint64_t *hist256,
-			 uint32_t p_ex_u32, uint64_t seed);
+			 uint32_t p_ex_u32, uint64_t seed, uint64_t first_read);
 
 #ifdef __cplusplus
 }
