@@ -263,7 +263,7 @@ int press_gpu_batch_press(int method, const int16_t *d_samples, const uint64_t *
 {
 	if (ensure_init())
 		return -1;
-	cudaStream_t st = stream ? (cudaStream_t) stream : g_ctx.stream;
+	cudaStream_t st = (cudaStream_t) stream;	// NULL = the CUDA default stream
 	const ScratchLayout l = scratch_layout(method, nreads, nsamples);
 	if (scratch_bytes < l.total) {
 		set_err("scratch too small: %zu < %zu", scratch_bytes, l.total);
@@ -314,7 +314,7 @@ int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_i
 {
 	if (ensure_init())
 		return -1;
-	cudaStream_t st = stream ? (cudaStream_t) stream : g_ctx.stream;
+	cudaStream_t st = (cudaStream_t) stream;	// NULL = the CUDA default stream
 	const ScratchLayout l = scratch_layout(method, nreads, nsamples);
 	if (scratch_bytes < l.total) {
 		set_err("scratch too small: %zu < %zu", scratch_bytes, l.total);
@@ -360,7 +360,7 @@ int press_gpu_batch_status(void *d_scratch, void *stream)
 {
 	if (ensure_init())
 		return -1;
-	cudaStream_t st = stream ? (cudaStream_t) stream : g_ctx.stream;
+	cudaStream_t st = (cudaStream_t) stream;	// NULL = the CUDA default stream
 	Hdr h;
 	if (cudaMemcpyAsync(&h, d_scratch, sizeof h, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
 	    cudaStreamSynchronize(st) != cudaSuccess) {
@@ -411,7 +411,7 @@ int press_gpu_global_offsets(const uint64_t *d_gathered, int nranks, uint64_t nr
 		set_err("global_offsets: nranks >= 1 and nreads >= 1 required");
 		return -1;
 	}
-	cudaStream_t st = stream ? (cudaStream_t) stream : g_ctx.stream;
+	cudaStream_t st = (cudaStream_t) stream;	// NULL = the CUDA default stream
 	const uint64_t total = (uint64_t) nranks * nreads + 1;
 	global_offsets_kernel<<<(unsigned) ((total + 255) / 256), 256, 0, st>>>(d_gathered, nranks, nreads, d_global);
 	g_launches++;

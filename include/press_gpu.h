@@ -114,7 +114,7 @@ int shuffman_vbe21_zd_gpu_depress_16(const void *table, uint8_t *in, uint64_t ni
  * the per-read streams back to back with no gaps, stream r at byte
  * d_out_offsets[r], total bytes in d_out_offsets[nreads]; each stream is byte
  * identical to what the per-read reference function writes.
- * `stream` is a cudaStream_t passed as void* (NULL = the library's stream).
+ * `stream` is a cudaStream_t passed as void* (NULL = the CUDA default stream, as in any CUDA call).
  * All calls are asynchronous on that stream and return 0 when enqueued;
  * failures detected on the device (capacity, malformed stream, ex-zd scratch
  * cap) are reported by press_gpu_batch_status() after synchronisation. */
