@@ -1,9 +1,10 @@
 // common.cuh -- shared device helpers for libpress_gpu (sm_100a).
 //
 // Work decomposition used by every kernel in this library:
-//   * a batch = all reads concatenated; a TILE = 4096 samples of ONE read;
-//   * persistent CTAs of 256 threads take tiles in ticket order (atomicAdd), so
-//     tile g only ever waits on tiles < g, which are running or finished;
+//   * a batch = all reads concatenated; a tile = a fixed number of samples of ONE read;
+//   * a persistent, cooperatively launched grid (all CTAs resident) walks the
+//     tiles round-robin, warp by warp, so tiles start in index order and tile g
+//     only ever waits on tiles < g, which are running or finished;
 //   * every loop-carried quantity of the reference's serial loops (output byte
 //     position, previous sample, running sum) becomes a prefix over tiles,
 //     resolved in ONE pass with decoupled look-back on a 64-bit status word
@@ -15,11 +16,17 @@
 
 namespace pg {
 
-constexpr int TILE = 4096;		// samples per tile
 constexpr int NT = 256;			// threads per CTA
 constexpr int NW = NT / 32;		// warps per CTA
-constexpr int GROUPS = TILE / 8;	// 8-sample groups per tile (one 16-byte vector each)
-constexpr int CHUNKS = GROUPS / NT;	// groups per thread
+
+// Warp tiles: the unit of work of the svb kernels.  One warp owns 1024
+// samples (128 sixteen-byte groups, 4 per lane, lane-interleaved so that every
+// load / store instruction of the warp covers 512 contiguous bytes).  Nothing
+// in a tile's life needs a CTA barrier, so the 32+ resident warps of an SM
+// hide each other's load, look-back and store latencies.
+constexpr int WT = 1024;		// samples per warp tile
+constexpr int WG = WT / 8;		// groups per warp tile
+constexpr int WC = WG / 32;		// groups per lane
 
 constexpr uint64_t LB_AGG = 1ull << 62;	// status: tile aggregate available
 constexpr uint64_t LB_INC = 2ull << 62;	// status: inclusive prefix available
@@ -58,35 +65,78 @@ __device__ __forceinline__ uint64_t warp_sum64(uint64_t v)
 	return v;
 }
 
-// Decoupled look-back, executed by ONE full warp.  Returns (in every lane) the
-// sum of the aggregates of tiles [first, tile).  Tiles below `first` are
-// treated as an inclusive prefix of 0 (segmented scans restart at a read's
-// first tile).
-__device__ __forceinline__ uint64_t lookback(const uint64_t *status, uint32_t tile, uint32_t first)
+// Spin until the status word at p has a flag, return it.
+__device__ __forceinline__ uint64_t lb_wait(const uint64_t *p)
+{
+	uint64_t w;
+	do {
+		w = ld_relaxed(p);
+	} while ((w >> 62) == 0);
+	return w;
+}
+
+// One window of a look-back: every lane holds one status word `w`, lane 0 the
+// nearest predecessor.  Adds the values up to and including the first
+// inclusive word to `sum`; returns true when one was found.
+__device__ __forceinline__ bool lb_window(uint64_t w, uint64_t &sum)
 {
 	const int lane = threadIdx.x & 31;
-	uint64_t sum = 0;
-	int64_t idx = (int64_t) tile - 1 - lane;
-	for (;;) {
-		uint64_t w = LB_INC;	// out of range == inclusive 0
-		if (idx >= (int64_t) first) {
-			do {
-				w = ld_relaxed(status + idx);
-			} while ((w >> 62) == 0);
+	const unsigned inc = __ballot_sync(0xffffffffu, (w >> 62) == 2);
+	uint64_t v = w & LB_VAL;
+	if (inc && lane > __ffs(inc) - 1)
+		v = 0;
+	sum += warp_sum64(v);
+	return inc != 0;
+}
+
+// Two-level decoupled look-back, executed by ONE full warp for tile g.
+// Publishes the tile's aggregate `my`, returns (in every lane) the sum of the
+// aggregates of tiles [first, g), then publishes the inclusive prefix.
+//   tile[g]  : per-tile status word
+//   block[b] : status of the 32 tiles [32 b, 32 b + 32), written by the block's
+//              LAST tile: aggregate / inclusive prefix counted from
+//              max(32 b, first) of that tile's segment.
+// A tile first inspects its predecessors inside its own block (one window) and
+// then whole blocks, 1024 tiles per window, so the walk stays 2-3 L2 round
+// trips however many tiles are in flight.  `first` is the first tile of the
+// segment (a read, or 0 for a batch-wide scan); every tile of a segment passes
+// the same `first`.
+__device__ __forceinline__ uint64_t scan_tile(uint64_t *tile, uint64_t *block, uint32_t g,
+					      uint32_t first, uint64_t my)
+{
+	const int lane = threadIdx.x & 31;
+	const uint32_t b = g >> 5;
+	const bool closes = (g & 31) == 31;	// this tile publishes its block's status
+	uint64_t D = 0;
+	if (g > first) {
+		if (lane == 0)
+			st_relaxed(tile + g, LB_AGG | my);
+		const int64_t lo = (int64_t) ((b << 5) > first ? (b << 5) : first);
+		const int64_t idx = (int64_t) g - 1 - lane;
+		// lanes before the window: nothing there (inclusive 0) when the segment starts
+		// inside this block, else "look in the block words"
+		uint64_t w = lo == (int64_t) first ? LB_INC : LB_AGG;
+		if (idx >= lo)
+			w = lb_wait(tile + idx);
+		if (!lb_window(w, D)) {
+			if (closes && lane == 0)
+				st_relaxed(block + b, LB_AGG | (D + my));
+			const int64_t bfirst = first >> 5;
+			for (int64_t bidx = (int64_t) b - 1 - lane;; bidx -= 32) {
+				w = LB_INC;	// below the segment's first block: inclusive 0
+				if (bidx >= bfirst)
+					w = lb_wait(block + bidx);
+				if (lb_window(w, D))
+					break;
+			}
 		}
-		unsigned inc = __ballot_sync(0xffffffffu, (w >> 62) == 2);
-		uint64_t v = w & LB_VAL;
-		if (inc) {
-			int stop = __ffs(inc) - 1;
-			if (lane > stop)
-				v = 0;
-			sum += warp_sum64(v);
-			break;
-		}
-		sum += warp_sum64(v);
-		idx -= 32;
 	}
-	return sum;
+	if (lane == 0) {
+		st_relaxed(tile + g, LB_INC | (D + my));
+		if (closes)
+			st_relaxed(block + b, LB_INC | (D + my));
+	}
+	return D;
 }
 
 // Exclusive scan over the CTA in (chunk, thread) order: element (c, tid) comes
@@ -135,20 +185,16 @@ __device__ __forceinline__ void block_scan(const uint32_t (&v)[C], uint32_t (&ex
 
 // ---- SWAR on two 16-bit lanes per 32-bit word -----------------------------
 
-// per-halfword a - b (mod 2^16)
-__device__ __forceinline__ uint32_t sub16x2(uint32_t a, uint32_t b)
-{
-	return ((a | 0x80008000u) - (b & 0x7fff7fffu)) ^ ((a ^ ~b) & 0x80008000u);
-}
-// per-halfword a + b (mod 2^16)
-__device__ __forceinline__ uint32_t add16x2(uint32_t a, uint32_t b)
-{
-	return ((a & 0x7fff7fffu) + (b & 0x7fff7fffu)) ^ ((a ^ b) & 0x80008000u);
-}
+// per-halfword a - b and a + b (mod 2^16): sm_100 has a native VIADD.16x2
+__device__ __forceinline__ uint32_t sub16x2(uint32_t a, uint32_t b) { return __vsub2(a, b); }
+__device__ __forceinline__ uint32_t add16x2(uint32_t a, uint32_t b) { return __vadd2(a, b); }
 // per-halfword zigzag: (d << 1) ^ (d >> 15 arithmetic)      (trans.c:75-78)
+// PRMT with the sign-replicate selector turns each halfword's top byte into 0x0000 / 0xffff.
 __device__ __forceinline__ uint32_t zigzag16x2(uint32_t d)
 {
-	return ((d << 1) & 0xfffefffeu) ^ (((d >> 15) & 0x00010001u) * 0xffffu);
+	uint32_t sign;	// __byte_perm() masks the selector's replicate bit, prmt.b32 honours it
+	asm("prmt.b32 %0, %1, %2, %3;" : "=r"(sign) : "r"(d), "r"(0u), "r"(0xbb99u));
+	return __vadd2(d, d) ^ sign;
 }
 // per-halfword inverse: (z >> 1) ^ -(z & 1)                  (trans.c:80-83)
 __device__ __forceinline__ uint32_t unzigzag16x2(uint32_t z)

@@ -8,7 +8,7 @@
 namespace pg {
 
 struct ScratchLayout {
-	size_t hdr, status, status2, zero_bytes, tile_start, kx, tile_read, extra, total;
+	size_t hdr, status, status2, status_blk, status2_blk, zero_bytes, tile_start, kx, tile_read, extra, total;
 };
 
 ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples);

@@ -13,13 +13,14 @@ namespace pg {
 
 enum PlanTiling : int {
 	TILING_ALIGNED = 0,	// encode: tiles start on 16-byte (8-sample) boundaries of d_samples
-	TILING_READ = 1		// decode: tiles start at multiples of TILE inside the read
+	TILING_READ = 1		// tiles start at multiples of the tile size inside the read
 };
 
 struct PlanArgs {
 	const uint64_t *offsets;	// [nreads + 1] sample offsets
 	uint64_t nreads;
 	int tiling;
+	uint32_t tile;			// samples per tile
 	uint32_t frame;			// fixed bytes before the key section (0, or 4 for VBZ)
 	uint32_t keydiv;		// values per key byte: 8 (svb16), 4 (svb32), 0 = none
 	uint32_t fixed;			// further fixed bytes per read (e.g. 6 for vbe21's zd0 + nex)
@@ -28,10 +29,10 @@ struct PlanArgs {
 	Hdr *hdr;
 };
 
-__device__ __forceinline__ uint32_t plan_tiles(uint64_t off, uint64_t n, int tiling)
+__device__ __forceinline__ uint32_t plan_tiles(uint64_t off, uint64_t n, int tiling, uint32_t tile)
 {
 	uint64_t span = tiling == TILING_ALIGNED ? (off & 7) + n : n;
-	uint64_t t = (span + TILE - 1) / TILE;
+	uint64_t t = (span + tile - 1) / tile;
 	return t ? (uint32_t) t : 1u;	// an empty read still owns one (empty) tile
 }
 
@@ -56,7 +57,7 @@ __global__ void __launch_bounds__(1024) plan_scan_kernel(PlanArgs a)
 			tl[i] = kb[i] = 0;
 			if (r < a.nreads) {
 				uint64_t off = a.offsets[r], n = a.offsets[r + 1] - off;
-				tl[i] = plan_tiles(off, n, a.tiling);
+				tl[i] = plan_tiles(off, n, a.tiling, a.tile);
 				kb[i] = a.frame + a.fixed +
 					(a.keydiv ? (n + a.keydiv - 1) / a.keydiv : 0);
 			}

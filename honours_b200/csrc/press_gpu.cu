@@ -94,7 +94,7 @@ namespace pg {
 
 uint64_t max_tiles(uint64_t nreads, uint64_t nsamples)
 {
-	return nsamples / TILE + 2 * nreads + 2;
+	return nsamples / WT + 2 * nreads + 2;
 }
 
 ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples)
@@ -106,6 +106,8 @@ ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples)
 	l.hdr = o;		o += sizeof(Hdr);
 	l.status = o;		o += align_up(mt * 8, 256);
 	l.status2 = o;		o += align_up(mt * 8, 256);
+	l.status_blk = o;	o += align_up((mt / 32 + 2) * 8, 256);
+	l.status2_blk = o;	o += align_up((mt / 32 + 2) * 8, 256);
 	l.zero_bytes = o;	// [0, zero_bytes) is cleared before every batch call
 	l.tile_start = o;	o += align_up((nreads + 1) * 4, 256);
 	l.kx = o;		o += align_up((nreads + 1) * 8, 256);
@@ -205,6 +207,7 @@ int run_plan(const ScratchLayout &l, uint8_t *scr, const uint64_t *d_offsets, ui
 	pa.offsets = d_offsets;
 	pa.nreads = nreads;
 	pa.tiling = tiling;
+	pa.tile = WT;
 	pa.frame = frame;
 	pa.keydiv = keydiv;
 	pa.fixed = fixed;
@@ -230,7 +233,9 @@ int launch_svb_encode(const SvbEncArgs &a, cudaStream_t st)
 	if (persistent_grid(svb_zd_encode_kernel<KEYBITS, FRAME>, &grid))
 		return -1;
 	EvPair *ev = prof_begin(0, st);
-	svb_zd_encode_kernel<KEYBITS, FRAME><<<grid, NT, 0, st>>>(a);
+	void *params[] = {const_cast<SvbEncArgs *>(&a)};
+	CK(cudaLaunchCooperativeKernel((const void *) svb_zd_encode_kernel<KEYBITS, FRAME>, dim3(grid),
+				       dim3(NT), params, 0, st));
 	prof_end(ev, st);
 	g_launches++;
 	CK(cudaGetLastError());
@@ -244,7 +249,9 @@ int launch_svb_decode(const SvbDecArgs &a, cudaStream_t st)
 	if (persistent_grid(svb_zd_decode_kernel<KEYBITS, FRAME>, &grid))
 		return -1;
 	EvPair *ev = prof_begin(1, st);
-	svb_zd_decode_kernel<KEYBITS, FRAME><<<grid, NT, 0, st>>>(a);
+	void *params[] = {const_cast<SvbDecArgs *>(&a)};
+	CK(cudaLaunchCooperativeKernel((const void *) svb_zd_decode_kernel<KEYBITS, FRAME>, dim3(grid),
+				       dim3(NT), params, 0, st));
 	prof_end(ev, st);
 	g_launches++;
 	CK(cudaGetLastError());
@@ -298,6 +305,7 @@ int press_gpu_batch_press(int method, const int16_t *d_samples, const uint64_t *
 		a.tile_read = reinterpret_cast<const uint32_t *>(scr + l.tile_read);
 		a.kx = reinterpret_cast<const uint64_t *>(scr + l.kx);
 		a.status = reinterpret_cast<uint64_t *>(scr + l.status);
+		a.status_blk = reinterpret_cast<uint64_t *>(scr + l.status_blk);
 		if (!k2 && !frame) return launch_svb_encode<1, false>(a, st);
 		if (!k2 && frame) return launch_svb_encode<1, true>(a, st);
 		if (k2 && !frame) return launch_svb_encode<2, false>(a, st);
@@ -333,7 +341,7 @@ int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_i
 	if (is_svb(method)) {
 		const bool frame = method == PRESS_GPU_VBZ_SVB16_ZD || method == PRESS_GPU_VBZ_SVB_ZD;
 		const bool k2 = method == PRESS_GPU_SVB_ZD || method == PRESS_GPU_VBZ_SVB_ZD;
-		if (run_plan(l, scr, d_offsets, nreads, TILING_READ, frame ? 4 : 0, k2 ? 4 : 8, 0, st))
+		if (run_plan(l, scr, d_offsets, nreads, TILING_ALIGNED, frame ? 4 : 0, k2 ? 4 : 8, 0, st))
 			return -1;
 		SvbDecArgs a;
 		a.in = d_in;
@@ -347,6 +355,8 @@ int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_i
 		a.tile_read = reinterpret_cast<const uint32_t *>(scr + l.tile_read);
 		a.status_bytes = reinterpret_cast<uint64_t *>(scr + l.status);
 		a.status_sum = reinterpret_cast<uint64_t *>(scr + l.status2);
+		a.status_bytes_blk = reinterpret_cast<uint64_t *>(scr + l.status_blk);
+		a.status_sum_blk = reinterpret_cast<uint64_t *>(scr + l.status2_blk);
 		if (!k2 && !frame) return launch_svb_decode<1, false>(a, st);
 		if (!k2 && frame) return launch_svb_decode<1, true>(a, st);
 		if (k2 && !frame) return launch_svb_decode<2, false>(a, st);
