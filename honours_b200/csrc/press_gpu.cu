@@ -17,6 +17,7 @@
 #include "common.cuh"
 #include "plan.cuh"
 #include "svb_zd.cuh"
+#include "svb_enc.cuh"
 #include "synth.cuh"
 #include "host_ctx.h"
 
@@ -200,14 +201,14 @@ int persistent_grid(K kernel, int *grid)
 }
 
 int run_plan(const ScratchLayout &l, uint8_t *scr, const uint64_t *d_offsets, uint64_t nreads,
-	     int tiling, uint32_t frame, uint32_t keydiv, uint32_t fixed, cudaStream_t st)
+	     int tiling, uint32_t tile, uint32_t frame, uint32_t keydiv, uint32_t fixed, cudaStream_t st)
 {
 	CK(cudaMemsetAsync(scr, 0, l.zero_bytes, st));
 	PlanArgs pa;
 	pa.offsets = d_offsets;
 	pa.nreads = nreads;
 	pa.tiling = tiling;
-	pa.tile = WT;
+	pa.tile = tile;
 	pa.frame = frame;
 	pa.keydiv = keydiv;
 	pa.fixed = fixed;
@@ -229,13 +230,22 @@ int run_plan(const ScratchLayout &l, uint8_t *scr, const uint64_t *d_offsets, ui
 template <int KEYBITS, bool FRAME>
 int launch_svb_encode(const SvbEncArgs &a, cudaStream_t st)
 {
-	int grid;
-	if (persistent_grid(svb_zd_encode_kernel<KEYBITS, FRAME>, &grid))
-		return -1;
+	auto kernel = svb_enc_kernel<KEYBITS, FRAME>;
+	const size_t smem = sizeof(EnSmem);
+	static int grid = 0;	// per instantiation
+	if (!grid) {
+		CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+		int per_sm = 0;
+		CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, EN_THREADS, smem));
+		if (per_sm < 1) {
+			set_err("svb_enc_kernel does not fit on an SM (%zu B shared)", smem);
+			return -1;
+		}
+		grid = per_sm * g_ctx.sms;
+	}
 	EvPair *ev = prof_begin(0, st);
 	void *params[] = {const_cast<SvbEncArgs *>(&a)};
-	CK(cudaLaunchCooperativeKernel((const void *) svb_zd_encode_kernel<KEYBITS, FRAME>, dim3(grid),
-				       dim3(NT), params, 0, st));
+	CK(cudaLaunchCooperativeKernel((const void *) kernel, dim3(grid), dim3(EN_THREADS), params, smem, st));
 	prof_end(ev, st);
 	g_launches++;
 	CK(cudaGetLastError());
@@ -290,7 +300,7 @@ int press_gpu_batch_press(int method, const int16_t *d_samples, const uint64_t *
 	if (is_svb(method)) {
 		const bool frame = method == PRESS_GPU_VBZ_SVB16_ZD || method == PRESS_GPU_VBZ_SVB_ZD;
 		const bool k2 = method == PRESS_GPU_SVB_ZD || method == PRESS_GPU_VBZ_SVB_ZD;
-		if (run_plan(l, scr, d_offsets, nreads, TILING_ALIGNED, frame ? 4 : 0, k2 ? 4 : 8, 0, st))
+		if (run_plan(l, scr, d_offsets, nreads, TILING_ALIGNED, EN_TS, frame ? 4 : 0, k2 ? 4 : 8, 0, st))
 			return -1;
 		SvbEncArgs a;
 		a.samples = reinterpret_cast<const uint4 *>(d_samples);
@@ -341,7 +351,7 @@ int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_i
 	if (is_svb(method)) {
 		const bool frame = method == PRESS_GPU_VBZ_SVB16_ZD || method == PRESS_GPU_VBZ_SVB_ZD;
 		const bool k2 = method == PRESS_GPU_SVB_ZD || method == PRESS_GPU_VBZ_SVB_ZD;
-		if (run_plan(l, scr, d_offsets, nreads, TILING_ALIGNED, frame ? 4 : 0, k2 ? 4 : 8, 0, st))
+		if (run_plan(l, scr, d_offsets, nreads, TILING_ALIGNED, WT, frame ? 4 : 0, k2 ? 4 : 8, 0, st))
 			return -1;
 		SvbDecArgs a;
 		a.in = d_in;
