@@ -139,6 +139,47 @@ __device__ __forceinline__ uint64_t scan_tile(uint64_t *tile, uint64_t *block, u
 	return D;
 }
 
+// Row look-back for the persistent CTA-tile kernels (pipe.cuh): tiles are dealt
+// round-robin, tile g = row * G + col with G = gridDim.x, so "row" = iteration
+// and col = blockIdx.x.  Executed by ONE full warp for tile g:
+//   publishes the tile's aggregate, returns (in every lane) the sum of the
+//   aggregates of ALL tiles < g (a batch-wide exclusive prefix); the row's last
+//   tile publishes its inclusive prefix in rowpref[row].
+// All words of the own row and the previous row's prefix are requested at once
+// (one L2 round trip in the common case); when rowpref[row - 1] is not there
+// yet the walk continues over the aggregates of whole earlier rows instead of
+// waiting for it, so no chain of dependent prefixes forms.
+__device__ __forceinline__ uint64_t row_scan(uint64_t *tile, uint64_t *rowpref, uint32_t g, uint32_t G,
+					     uint32_t total, uint64_t my)
+{
+	const int lane = threadIdx.x & 31;
+	const uint32_t row = g / G, col = g - row * G;
+	if (lane == 0)
+		st_relaxed(tile + g, LB_AGG | my);
+	uint64_t D = 0, wp = 0;
+	if (row > 0 && lane == 0)	// in flight together with the own-row words
+		wp = ld_relaxed(rowpref + row - 1);
+	// own row, tiles before this one
+	for (uint32_t j = lane; j < col; j += 32)
+		D += lb_wait(tile + (uint64_t) row * G + j) & LB_VAL;
+	for (int64_t r = (int64_t) row - 1; r >= 0; r--) {
+		const uint64_t w = __shfl_sync(0xffffffffu, wp, 0);
+		if ((w >> 62) == 2) {
+			if (lane == 0)
+				D += w & LB_VAL;
+			break;
+		}
+		if (r > 0 && lane == 0)
+			wp = ld_relaxed(rowpref + r - 1);
+		for (uint32_t j = lane; j < G; j += 32)	// earlier rows are always complete rows
+			D += lb_wait(tile + (uint64_t) r * G + j) & LB_VAL;
+	}
+	D = warp_sum64(D);
+	if (lane == 0 && (col == G - 1 || g == total - 1))	// tile[] keeps aggregates only
+		st_relaxed(rowpref + row, LB_INC | (D + my));
+	return D;
+}
+
 // Exclusive scan over the CTA in (chunk, thread) order: element (c, tid) comes
 // before (c, tid + 1) and all of chunk c before chunk c + 1.
 // s_warp needs C * NW + 1 words.  Contains two __syncthreads().

@@ -1,4 +1,5 @@
-// svb_enc.cuh -- fused zigzag-delta + streamvbyte ENCODE, CTA tiles staged by TMA.
+// svb_enc.cuh -- fused zigzag-delta + streamvbyte ENCODE: one persistent CTA per
+// SM, warp-specialised dataflow over a shared-memory ring filled by TMA.
 //
 //   KEYBITS = 1 : ONT svb16, 1 key bit / value   (svb16/encode_scalar.hpp:14-62; press.c:1678-1687)
 //   KEYBITS = 2 : classical streamvbyte over zd widened to u32; zd < 65536 so only
@@ -8,19 +9,23 @@
 // Stream of read r:  [frame][keys: ceil(n / (8 / KEYBITS)) bytes][data bytes].
 //
 // One pass over HBM.  A tile is 8192 samples of ONE read cut on 16-byte
-// boundaries of the sample array.  Per CTA (see pipe.cuh for the roles):
-//   producer warp : tile metadata -> one cp.async.bulk per tile into a ring of
-//                   EN_STAGES shared-memory stages (group before the tile and
-//                   group after it included: previous sample / last key byte);
-//   8 consumer warps, 1024 samples each (4 x LDS.128 per lane, lane interleaved):
-//       COUNT(i+1): delta + zigzag on 16-bit pairs (VIADD.16x2 / PRMT), number of
-//                   data bytes of the warp -> shared memory;
-//       EMIT(i)   : same registers recomputed from shared memory, bytes placed at
-//                   the tile's container position: aligned 64-bit stores for
-//                   warps without a two-byte value (the common case on nanopore
-//                   signal), per-sample placement through a staging line otherwise;
-//   scan warp     : decoupled look-back over the per-tile byte counts (batch
-//                   wide; the key sections are data independent, plan.cuh).
+// boundaries of the sample array; tiles are dealt round-robin to the CTAs.
+// Every tile walks through the ring stage it was loaded into:
+//
+//   producer warp   tile metadata -> ONE cp.async.bulk (the tile, the group before
+//                   it for the previous sample, the group after it for the last key)
+//   4 count warps   |delta| test on 16-bit pairs (VIADD.16x2): does any value need
+//                   two bytes?  -> data bytes of each 512-sample block
+//   2 scan warps    row look-back over the per-tile byte counts (batch-wide prefix;
+//                   the key sections are data independent, plan.cuh)
+//   16 emit warps   delta + zigzag again from shared memory, bytes to the tile's
+//                   container position: aligned 64-bit stores for blocks without a
+//                   two-byte value (the common case on nanopore signal),
+//                   per-sample placement through a staging line otherwise
+//
+// The stages between "counted" and "emitted" are the slack that hides the
+// look-back: a tile's prefix has ~8 tile times to resolve, and the count warps
+// (uniform, light work) are never held up by a slow emit.
 #pragma once
 
 #include "common.cuh"
@@ -31,13 +36,22 @@ namespace pg {
 
 constexpr int EN_TS = 8192;			// samples per tile
 constexpr int EN_TG = EN_TS / 8;		// 16-byte groups per tile
-constexpr int EN_CW = 8;			// consumer warps
-constexpr int EN_WG = EN_TG / EN_CW;		// groups per consumer warp (128)
-constexpr int EN_THREADS = (EN_CW + 2) * 32;	// + producer warp + scan warp
-constexpr int EN_STAGES = 4;			// input ring depth
-constexpr int EN_Q = 4;				// depth of the count / scan hand-off rings
+constexpr int EN_NEMIT = 16;			// emit warps: 64 groups (512 samples) each
+constexpr int EN_NCNT = 4;			// count warps: 256 groups each
+constexpr int EN_NSCAN = 2;
+constexpr int EN_EG = EN_TG / EN_NEMIT;		// groups per emit warp
+constexpr int EN_EC = EN_EG / 32;		// groups per emit lane (2)
+constexpr int EN_CG = EN_TG / EN_NCNT;		// groups per count warp
+constexpr int EN_CC = EN_CG / 32;		// groups per count lane (8)
+constexpr int EN_BPC = EN_NEMIT / EN_NCNT;	// 512-sample blocks per count warp
+constexpr int EN_W_CNT = EN_NEMIT;		// first count warp
+constexpr int EN_W_SCAN = EN_W_CNT + EN_NCNT;
+constexpr int EN_W_PROD = EN_W_SCAN + EN_NSCAN;
+constexpr int EN_THREADS = (EN_W_PROD + 1) * 32;
+constexpr int EN_STAGES = 12;
 constexpr int EN_STAGE_BYTES = (EN_TG + 2) * 16 + 96;	// slots 0 .. TG+1, padded to 128
-constexpr int EN_LINE_BYTES = 2 * 8 * EN_WG + 16;	// per-warp staging line (general path)
+constexpr int EN_LINE_BYTES = 2 * 8 * EN_EG + 16;	// per emit warp staging line (general path)
+static_assert(EN_STAGES % EN_NSCAN == 0, "a stage is always scanned by the same scan warp");
 
 struct EnTileInfo {
 	uint64_t off0, rend;	// sample range of the tile's read
@@ -48,91 +62,157 @@ struct EnTileInfo {
 
 struct EnSmem {
 	alignas(128) uint8_t in[EN_STAGES][EN_STAGE_BYTES];
-	alignas(16) uint8_t line[EN_CW][EN_LINE_BYTES];
+	alignas(16) uint8_t line[EN_NEMIT][EN_LINE_BYTES];
 	EnTileInfo info[EN_STAGES];
-	uint64_t full[EN_STAGES], empty[EN_STAGES];
-	uint64_t cnt_done[EN_Q], scan_done[EN_Q];
-	uint64_t D[EN_Q], base[EN_Q];
-	uint32_t warpL[EN_Q][EN_CW];
+	uint64_t full[EN_STAGES], cnt_done[EN_STAGES], scan_done[EN_STAGES], empty[EN_STAGES];
+	uint64_t D[EN_STAGES], base[EN_STAGES];
+	uint32_t blkL[EN_STAGES][EN_NEMIT];	// data bytes of each 512-sample block
 };
 
-// the 4 groups of a lane: zd words, valid-sample masks, two-byte flags
-struct EnRegs {
-	uint32_t z[WC][4];
-	uint32_t valid[WC], fl[WC];
-	uint32_t fh;		// flags of the group after the warp's region (valid part)
-	uint32_t high;		// nonzero iff one of this lane's values (or fh) needs two bytes
-};
-
-__device__ __forceinline__ uint4 en_group(const SvbEncArgs &a, const uint8_t *st, uint64_t k0, uint32_t gi,
-					  uint64_t nfull)
+// word holding the sample before each of x's words' low halves
+__device__ __forceinline__ void prev_words(const uint4 &x, uint32_t prev_half, uint32_t (&p)[4])
 {
-	const uint64_t k = k0 + gi;
-	if (k < nfull)
-		return *reinterpret_cast<const uint4 *>(st + 16 * (gi + 1));
-	return load_group(a.samples, a.nsamples, k);
+	p[0] = __byte_perm(prev_half, x.x, 0x5410);
+	p[1] = __funnelshift_l(x.x, x.y, 16);
+	p[2] = __funnelshift_l(x.y, x.z, 16);
+	p[3] = __funnelshift_l(x.z, x.w, 16);
 }
 
-// Everything EMIT needs and COUNT sums, from the staged tile.  One warp.
-__device__ __forceinline__ void en_regs(const SvbEncArgs &a, const EnTileInfo &ti, const uint8_t *st,
-					int w, int lane, EnRegs &R)
+// valid-sample mask of group k of a read [off0, rend)
+__device__ __forceinline__ uint32_t group_valid(uint64_t k, uint64_t off0, uint64_t rend)
 {
-	const uint64_t nfull = a.nsamples >> 3;
+	const int64_t lo64 = (int64_t) off0 - (int64_t) (8 * k);
+	const int64_t left = (int64_t) rend - (int64_t) (8 * k);
+	const int lo = lo64 > 0 ? (lo64 < 8 ? (int) lo64 : 8) : 0;
+	const int hi = left >= 8 ? 8 : (left > 0 ? (int) left : 0);
+	return range_mask(lo, hi);
+}
+
+// ---------------------------------------------------------------------------
+// count warp: data bytes of its four 512-sample blocks
+
+__device__ __forceinline__ void en_count(const EnTileInfo &ti, const uint8_t *st, uint32_t *blkL, int cw, int lane)
+{
 	const uint64_t A = ti.off0 >> 3;
-	const uint32_t m = (uint32_t) (ti.off0 & 7);
-	const uint32_t g0 = w * EN_WG;	// first group of the warp inside the tile
-	uint4 x[WC];
+	const uint32_t g0 = cw * EN_CG;
+	const uint64_t kw = ti.k0 + g0;
+	uint4 x[EN_CC];
 #pragma unroll
-	for (int c = 0; c < WC; c++)
-		x[c] = en_group(a, st, ti.k0, g0 + 32 * c + lane, nfull);
-	// sample before the warp's region: last halfword of slot g0 (group k0 + g0 - 1)
+	for (int c = 0; c < EN_CC; c++)
+		x[c] = *reinterpret_cast<const uint4 *>(st + 16 * (g0 + 32 * c + lane + 1));
 	const uint32_t prev0 = *reinterpret_cast<const uint16_t *>(st + 16 * g0 + 14);
-	const uint4 xh = en_group(a, st, ti.k0, g0 + EN_WG, nfull);
+	// d + 128 has a nonzero high byte  <=>  d outside [-128, 127]  <=>  zigzag(d) >= 256
+	uint32_t acc = 0;
+	uint32_t d[EN_CC][4];
 #pragma unroll
-	for (int c = 0; c < WC; c++) {
-		const uint32_t last = x[c].w >> 16;
-		uint32_t prev = __shfl_up_sync(0xffffffffu, last, 1);
+	for (int c = 0; c < EN_CC; c++) {
+		uint32_t prev = __shfl_up_sync(0xffffffffu, x[c].w >> 16, 1);
 		const uint32_t wrap = __shfl_sync(0xffffffffu, x[c > 0 ? c - 1 : 0].w >> 16, 31);
 		if (lane == 0)
 			prev = c > 0 ? wrap : prev0;
-		const uint64_t k = ti.k0 + g0 + 32 * c + lane;
-		zd_group(x[c], prev, (k == A) ? (int) m : -1, R.z[c]);
-		const int lo = k == A ? (int) m : 0;
-		const int64_t left = (int64_t) ti.rend - (int64_t) (8 * k);
-		const int hi = left >= 8 ? 8 : (left > 0 ? (int) left : 0);
-		R.valid[c] = k >= A ? range_mask(lo, hi) : 0u;
-		R.fl[c] = flags_group(R.z[c]) & R.valid[c];
+		uint32_t p[4];
+		prev_words(x[c], prev, p);
+		d[c][0] = sub16x2(x[c].x, p[0]);
+		d[c][1] = sub16x2(x[c].y, p[1]);
+		d[c][2] = sub16x2(x[c].z, p[2]);
+		d[c][3] = sub16x2(x[c].w, p[3]);
+#pragma unroll
+		for (int q = 0; q < 4; q++)
+			acc |= add16x2(d[c][q], 0x00800080u);
 	}
-	uint32_t zh[4];
-	zd_group(xh, __shfl_sync(0xffffffffu, x[WC - 1].w >> 16, 31), -1, zh);
-	{
-		const int64_t left = (int64_t) ti.rend - (int64_t) (8 * (ti.k0 + g0 + EN_WG));
-		const int hi = left >= 8 ? 8 : (left > 0 ? (int) left : 0);
-		R.fh = flags_group(zh) & range_mask(0, hi);
+	const bool inside = kw > A && 8 * (kw + EN_CG) <= ti.rend;
+	const bool any = __any_sync(0xffffffffu, (acc & 0xff00ff00u) != 0);
+	if (inside && !any) {
+		if (lane < EN_BPC)
+			blkL[cw * EN_BPC + lane] = 8 * EN_EG;
+		return;
 	}
-	R.high = R.fl[0] | R.fl[1] | R.fl[2] | R.fl[3] | R.fh;
+	// exact: valid samples + two-byte values, per block of EN_EC groups per lane
+#pragma unroll
+	for (int b = 0; b < EN_BPC; b++) {
+		uint32_t cnt = 0;
+#pragma unroll
+		for (int e = 0; e < EN_EC; e++) {
+			const int c = b * EN_EC + e;
+			const uint64_t k = kw + 32 * c + lane;
+			const uint32_t valid = group_valid(k, ti.off0, ti.rend);
+			uint32_t dd[4] = {d[c][0], d[c][1], d[c][2], d[c][3]};
+			if (k == A) {	// first sample of the read: delta against 0 (trans.c:221)
+				const uint32_t m = (uint32_t) (ti.off0 & 7);
+				const uint32_t xs[4] = {x[c].x, x[c].y, x[c].z, x[c].w};
+#pragma unroll
+				for (int q = 0; q < 4; q++)
+					if ((m >> 1) == (uint32_t) q)
+						dd[q] = (m & 1) ? (dd[q] & 0x0000ffffu) | (xs[q] & 0xffff0000u)
+								: (dd[q] & 0xffff0000u) | (xs[q] & 0x0000ffffu);
+			}
+			uint32_t z[4];
+#pragma unroll
+			for (int q = 0; q < 4; q++)
+				z[q] = zigzag16x2(dd[q]);
+			cnt += __popc(valid) + __popc(flags_group(z) & valid);
+		}
+#pragma unroll
+		for (int o = 16; o; o >>= 1)
+			cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+		if (lane == 0)
+			blkL[cw * EN_BPC + b] = cnt;
+	}
 }
 
+// ---------------------------------------------------------------------------
+// emit warp: one 512-sample block of the tile
+
 template <int KEYBITS, bool FRAME>
-__device__ __forceinline__ void en_emit(const SvbEncArgs &a, const EnTileInfo &ti, const EnRegs &R,
-					 uint64_t D, uint64_t base, const uint32_t *warpL, uint8_t *line,
-					 int w, int lane)
+__device__ __forceinline__ void en_emit(const SvbEncArgs &a, const EnTileInfo &ti, const uint8_t *st,
+					 uint64_t D, uint64_t base, const uint32_t *blkL, uint8_t *line,
+					 int ew, int lane)
 {
 	constexpr uint32_t VPK = 8 / KEYBITS;
 	const uint64_t n = ti.rend - ti.off0;
+	const uint64_t A = ti.off0 >> 3;
 	const uint32_t m = (uint32_t) (ti.off0 & 7);
-	const uint32_t g0 = w * EN_WG;
-	const uint64_t kw = ti.k0 + g0;			// first group of the warp
-	// the warp's region lies inside the read and has no two-byte value
-	const bool inside = 8 * kw >= ti.off0 && 8 * (kw + EN_WG + 1) <= ti.rend && !(ti.t == 0 && w == 0);
-	const bool fast = inside && !__any_sync(0xffffffffu, R.high != 0);
+	const uint32_t g0 = ew * EN_EG;
+	const uint64_t kw = ti.k0 + g0;			// first group of the block
+	if (FRAME && ti.t == 0 && ew == 0 && lane < 4 && base + 4 <= a.out_cap)
+		a.out[base + lane] = (uint8_t) ((uint32_t) n >> (8 * lane));
+	if (8 * kw >= ti.rend)
+		return;					// block past the end of the read: nothing else to write
 
-	uint32_t woff = 0;
+	// ---- load, zd -----------------------------------------------------------------
+	uint4 x[EN_EC];
 #pragma unroll
-	for (int q = 0; q < EN_CW; q++)
-		woff += q < w ? warpL[q] : 0u;
-	const uint32_t L = warpL[w];
-	const uint64_t P = ti.kx1 + D + woff;		// first data byte of this warp
+	for (int c = 0; c < EN_EC; c++)
+		x[c] = *reinterpret_cast<const uint4 *>(st + 16 * (g0 + 32 * c + lane + 1));
+	const uint32_t prev0 = *reinterpret_cast<const uint16_t *>(st + 16 * g0 + 14);
+	const uint4 xh = *reinterpret_cast<const uint4 *>(st + 16 * (g0 + EN_EG + 1));	// group after the block
+	uint32_t z[EN_EC][4], high = 0;
+#pragma unroll
+	for (int c = 0; c < EN_EC; c++) {
+		uint32_t prev = __shfl_up_sync(0xffffffffu, x[c].w >> 16, 1);
+		const uint32_t wrap = __shfl_sync(0xffffffffu, x[c > 0 ? c - 1 : 0].w >> 16, 31);
+		if (lane == 0)
+			prev = c > 0 ? wrap : prev0;
+		const uint64_t k = kw + 32 * c + lane;
+		zd_group(x[c], prev, (k == A) ? (int) m : -1, z[c]);
+		high |= z[c][0] | z[c][1] | z[c][2] | z[c][3];
+	}
+	uint32_t zh[4];
+	zd_group(xh, __shfl_sync(0xffffffffu, x[EN_EC - 1].w >> 16, 31), -1, zh);
+	high |= zh[0] | zh[1] | zh[2] | zh[3];
+	// the block and the group after it lie inside the read and hold no two-byte value
+	const bool inside = kw > A && 8 * (kw + EN_EG + 1) <= ti.rend;
+	const bool fast = inside && !__any_sync(0xffffffffu, (high & 0xff00ff00u) != 0);
+
+	// ---- container position of the block's data ---------------------------------------
+	uint32_t lv = lane < EN_NEMIT ? blkL[lane] : 0u;
+	const uint32_t L = __shfl_sync(0xffffffffu, lv, ew);
+	lv = lane < ew ? lv : 0u;
+#pragma unroll
+	for (int o = 8; o; o >>= 1)
+		lv += __shfl_xor_sync(0xffffffffu, lv, o);
+	const uint32_t woff = __shfl_sync(0xffffffffu, lv, 0);
+	const uint64_t P = ti.kx1 + D + woff;
 	if (P + L > a.out_cap) {
 		if (lane == 0)
 			atomicOr(&a.hdr->error, ERR_CAPACITY);
@@ -141,25 +221,26 @@ __device__ __forceinline__ void en_emit(const SvbEncArgs &a, const EnTileInfo &t
 	uint8_t *S = a.out + P;
 	const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(S) & 7);
 
+	uint32_t valid[EN_EC], fl[EN_EC], fh = 0;
 	if (fast) {
 		// chunk i = 32 c + lane holds exactly 8 data bytes; aligned word i of the output =
 		// top s bytes of chunk i - 1 | low 8 - s bytes of chunk i
-		uint64_t B[WC];
+		uint64_t B[EN_EC];
 #pragma unroll
-		for (int c = 0; c < WC; c++) {
-			const uint32_t w0 = __byte_perm(R.z[c][0], R.z[c][1], 0x6420);
-			const uint32_t w1 = __byte_perm(R.z[c][2], R.z[c][3], 0x6420);
+		for (int c = 0; c < EN_EC; c++) {
+			const uint32_t w0 = __byte_perm(z[c][0], z[c][1], 0x6420);
+			const uint32_t w1 = __byte_perm(z[c][2], z[c][3], 0x6420);
 			B[c] = ((uint64_t) w1 << 32) | w0;
 		}
 		uint64_t *W = reinterpret_cast<uint64_t *>(S - s);
 		if (s == 0) {
 #pragma unroll
-			for (int c = 0; c < WC; c++)
+			for (int c = 0; c < EN_EC; c++)
 				W[32 * c + lane] = B[c];
 		} else {
 			const uint32_t sh = 8 * s;
 #pragma unroll
-			for (int c = 0; c < WC; c++) {
+			for (int c = 0; c < EN_EC; c++) {
 				uint64_t pb = __shfl_up_sync(0xffffffffu, B[c], 1);
 				const uint64_t wrap = __shfl_sync(0xffffffffu, B[c > 0 ? c - 1 : 0], 31);
 				if (lane == 0)
@@ -172,9 +253,9 @@ __device__ __forceinline__ void en_emit(const SvbEncArgs &a, const EnTileInfo &t
 						S[b - s] = (uint8_t) (B[0] >> (8 * (b - s)));
 				}
 			}
-			if (lane == 31) {	// word EN_WG: the last s bytes of the warp's data
-				uint8_t *q = reinterpret_cast<uint8_t *>(W + EN_WG);
-				const uint64_t v = B[WC - 1] >> (64 - sh);
+			if (lane == 31) {	// word EN_EG: the last s bytes of the block's data
+				uint8_t *q = reinterpret_cast<uint8_t *>(W + EN_EG);
+				const uint64_t v = B[EN_EC - 1] >> (64 - sh);
 				for (uint32_t b = 0; b < s; b++)
 					q[b] = (uint8_t) (v >> (8 * b));
 			}
@@ -182,21 +263,24 @@ __device__ __forceinline__ void en_emit(const SvbEncArgs &a, const EnTileInfo &t
 	} else {
 		uint32_t run = 0;
 #pragma unroll
-		for (int c = 0; c < WC; c++) {
-			const uint32_t cnt = __popc(R.valid[c]) + __popc(R.fl[c]);
+		for (int c = 0; c < EN_EC; c++) {
+			valid[c] = group_valid(kw + 32 * c + lane, ti.off0, ti.rend);
+			fl[c] = flags_group(z[c]) & valid[c];
+			const uint32_t cnt = __popc(valid[c]) + __popc(fl[c]);
 			const uint32_t inc = warp_inc_scan(cnt, lane);
 			uint8_t *p = line + s + run + inc - cnt;
 			run += __shfl_sync(0xffffffffu, inc, 31);
 #pragma unroll
 			for (int e = 0; e < 8; e++) {
-				if ((R.valid[c] >> e) & 1) {
-					const uint32_t v = (R.z[c][e >> 1] >> (16 * (e & 1))) & 0xffffu;
+				if ((valid[c] >> e) & 1) {
+					const uint32_t v = (z[c][e >> 1] >> (16 * (e & 1))) & 0xffffu;
 					*p++ = (uint8_t) v;
-					if ((R.fl[c] >> e) & 1)
+					if ((fl[c] >> e) & 1)
 						*p++ = (uint8_t) (v >> 8);
 				}
 			}
 		}
+		fh = flags_group(zh) & group_valid(kw + EN_EG, ti.off0, ti.rend);
 		__syncwarp();
 		warp_copy_out(line, S, L, lane);
 		__syncwarp();
@@ -210,29 +294,20 @@ __device__ __forceinline__ void en_emit(const SvbEncArgs &a, const EnTileInfo &t
 		return;
 	}
 	uint8_t *kout = a.out + base + (FRAME ? 4 : 0);
-	if (FRAME && ti.t == 0 && w == 0 && lane < 4)
-		a.out[base + lane] = (uint8_t) ((uint32_t) n >> (8 * lane));
-	// read-relative 8-sample block of group k is k - A: block j = bits m..7 of group j's
-	// flags + bits 0..m-1 of group j + 1's
-	const uint64_t A = ti.off0 >> 3;
-	if (kw + EN_WG <= A || 8 * kw >= ti.rend)
-		return;			// warp entirely outside the read
-	const uint64_t j0 = kw - A;	// kw >= A here except for the read's first warp (kw == A)
+	// read-relative 8-sample block of group k is k - A: key block j = bits m..7 of group
+	// j's flags + bits 0..m-1 of group j + 1's
 	if (fast) {
-		warp_zero(kout + j0 * KEYBITS, EN_WG * KEYBITS, lane);
+		warp_zero(kout + (kw - A) * KEYBITS, EN_EG * KEYBITS, lane);
 		return;
 	}
 #pragma unroll
-	for (int c = 0; c < WC; c++) {
-		uint32_t fnext = __shfl_down_sync(0xffffffffu, R.fl[c], 1);
-		const uint32_t wrap = c + 1 < WC ? __shfl_sync(0xffffffffu, R.fl[c + 1 < WC ? c + 1 : c], 0) : R.fh;
+	for (int c = 0; c < EN_EC; c++) {
+		uint32_t fnext = __shfl_down_sync(0xffffffffu, fl[c], 1);
+		const uint32_t wrap = c + 1 < EN_EC ? __shfl_sync(0xffffffffu, fl[c + 1 < EN_EC ? c + 1 : c], 0) : fh;
 		if (lane == 31)
 			fnext = wrap;
-		const uint64_t k = kw + 32 * c + lane;
-		if (k < A)
-			continue;
-		const uint64_t j = k - A;
-		const uint32_t f = ((R.fl[c] >> m) | (fnext << (8 - m))) & 0xffu;
+		const uint64_t j = kw + 32 * c + lane - A;
+		const uint32_t f = ((fl[c] >> m) | (fnext << (8 - m))) & 0xffu;
 		if (KEYBITS == 1) {
 			if (8 * j < n)
 				kout[j] = (uint8_t) f;
@@ -250,7 +325,7 @@ __device__ __forceinline__ void en_emit(const SvbEncArgs &a, const EnTileInfo &t
 // the kernel
 
 template <int KEYBITS, bool FRAME>
-__global__ void __launch_bounds__(EN_THREADS) svb_enc_kernel(const __grid_constant__ SvbEncArgs a)
+__global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_constant__ SvbEncArgs a)
 {
 	extern __shared__ __align__(128) uint8_t smem_raw[];
 	EnSmem &sm = *reinterpret_cast<EnSmem *>(smem_raw);
@@ -263,11 +338,9 @@ __global__ void __launch_bounds__(EN_THREADS) svb_enc_kernel(const __grid_consta
 	if (threadIdx.x == 0) {
 		for (int s = 0; s < EN_STAGES; s++) {
 			mbar_init(&sm.full[s], 1);
-			mbar_init(&sm.empty[s], EN_CW);
-		}
-		for (int q = 0; q < EN_Q; q++) {
-			mbar_init(&sm.cnt_done[q], EN_CW);
-			mbar_init(&sm.scan_done[q], 1);
+			mbar_init(&sm.cnt_done[s], EN_NCNT);
+			mbar_init(&sm.scan_done[s], 1);
+			mbar_init(&sm.empty[s], EN_NEMIT);
 		}
 		mbar_fence_init();
 	}
@@ -275,7 +348,7 @@ __global__ void __launch_bounds__(EN_THREADS) svb_enc_kernel(const __grid_consta
 	if (nt == 0)
 		return;
 
-	if (warp == EN_CW) {
+	if (warp == EN_W_PROD) {
 		// ---- producer: metadata 32 tiles at a time, one bulk copy per tile ----------
 		const uint64_t nfull = a.nsamples >> 3;
 		for (uint32_t i0 = 0; i0 < nt; i0 += 32) {
@@ -301,12 +374,16 @@ __global__ void __launch_bounds__(EN_THREADS) svb_enc_kernel(const __grid_consta
 					mbar_wait(&sm.empty[s], ((it / EN_STAGES) & 1) ^ 1);
 				if (lane == (int) l) {
 					sm.info[s] = me;
-					// groups [kf, ke) -> slots kf - (k0 - 1) ...
+					// groups [kf, ke) of the sample array -> slots kf - (k0 - 1) ...
 					const uint64_t kf = me.k0 > 0 ? me.k0 - 1 : 0;
+					uint64_t kr = (me.rend + 7) >> 3;	// groups holding samples of the read
 					uint64_t ke = me.k0 + EN_TG + 1;
-					const uint64_t kr = (me.rend + 7) >> 3;
 					ke = ke < kr ? ke : kr;
-					ke = ke < nfull ? ke : nfull;
+					if (ke > nfull) {	// the array's last, partial group: by hand, zero filled
+						const uint4 v = load_group(a.samples, a.nsamples, nfull);
+						*reinterpret_cast<uint4 *>(sm.in[s] + 16 * (nfull + 1 - me.k0)) = v;
+						ke = nfull;
+					}
 					if (ke > kf) {
 						const uint32_t bytes = (uint32_t) (ke - kf) * 16;
 						mbar_arrive_expect_tx(&sm.full[s], bytes);
@@ -322,20 +399,20 @@ __global__ void __launch_bounds__(EN_THREADS) svb_enc_kernel(const __grid_consta
 		return;
 	}
 
-	if (warp == EN_CW + 1) {
-		// ---- scan warp: prefix of the data bytes, stream start of the read -----------
-		for (uint32_t i = 0; i < nt; i++) {
-			const uint32_t q = i % EN_Q, s = i % EN_STAGES;
-			mbar_wait(&sm.cnt_done[q], (i / EN_Q) & 1);
+	if (warp >= EN_W_SCAN) {
+		// ---- scan warps: prefix of the data bytes, stream start of the read -----------
+		for (uint32_t i = warp - EN_W_SCAN; i < nt; i += EN_NSCAN) {
+			const uint32_t s = i % EN_STAGES;
+			mbar_wait(&sm.cnt_done[s], (i / EN_STAGES) & 1);
 			const EnTileInfo ti = sm.info[s];
-			uint32_t L = lane < EN_CW ? sm.warpL[q][lane] : 0u;
+			uint32_t L = lane < EN_NEMIT ? sm.blkL[s][lane] : 0u;
 #pragma unroll
-			for (int o = 4; o; o >>= 1)
+			for (int o = 8; o; o >>= 1)
 				L += __shfl_xor_sync(0xffffffffu, L, o);
 			L = __shfl_sync(0xffffffffu, L, 0);
-			const uint64_t D = scan_tile(a.status, a.status_blk, ti.g, 0, L);
-			uint64_t base = 0;
+			const uint64_t D = row_scan(a.status, a.status_blk, ti.g, G, total, L);
 			if (lane == 0) {
+				uint64_t base;
 				if (ti.t == 0) {
 					base = ti.kx0 + D;
 					st_relaxed(a.out_offsets + ti.r, base);
@@ -346,42 +423,34 @@ __global__ void __launch_bounds__(EN_THREADS) svb_enc_kernel(const __grid_consta
 				}
 				if (ti.last)
 					st_relaxed(a.out_offsets + a.nreads, __ldg(a.kx + a.nreads) + D + L);
-				sm.D[q] = D;
-				sm.base[q] = base;
-				mbar_arrive(&sm.scan_done[q]);
+				sm.D[s] = D;
+				sm.base[s] = base;
+				mbar_arrive(&sm.scan_done[s]);
 			}
 			__syncwarp();
 		}
 		return;
 	}
 
-	// ---- consumers ----------------------------------------------------------------------
-	auto count = [&](uint32_t j) {
-		const uint32_t s = j % EN_STAGES, q = j % EN_Q;
-		mbar_wait(&sm.full[s], (j / EN_STAGES) & 1);
-		EnRegs R;
-		en_regs(a, sm.info[s], sm.in[s], warp, lane, R);
-		uint32_t cnt = 0;
-#pragma unroll
-		for (int c = 0; c < WC; c++)
-			cnt += __popc(R.valid[c]) + __popc(R.fl[c]);
-#pragma unroll
-		for (int o = 16; o; o >>= 1)
-			cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-		if (lane == 0) {
-			sm.warpL[q][warp] = cnt;
-			mbar_arrive(&sm.cnt_done[q]);
+	if (warp >= EN_W_CNT) {
+		// ---- count warps ------------------------------------------------------------------
+		const int cw = warp - EN_W_CNT;
+		for (uint32_t i = 0; i < nt; i++) {
+			const uint32_t s = i % EN_STAGES;
+			mbar_wait(&sm.full[s], (i / EN_STAGES) & 1);
+			en_count(sm.info[s], sm.in[s], sm.blkL[s], cw, lane);
+			__syncwarp();
+			if (lane == 0)
+				mbar_arrive(&sm.cnt_done[s]);
 		}
-	};
-	count(0);
+		return;
+	}
+
+	// ---- emit warps ---------------------------------------------------------------------------
 	for (uint32_t i = 0; i < nt; i++) {
-		if (i + 1 < nt)
-			count(i + 1);
-		const uint32_t s = i % EN_STAGES, q = i % EN_Q;
-		EnRegs R;
-		en_regs(a, sm.info[s], sm.in[s], warp, lane, R);
-		mbar_wait(&sm.scan_done[q], (i / EN_Q) & 1);
-		en_emit<KEYBITS, FRAME>(a, sm.info[s], R, sm.D[q], sm.base[q], sm.warpL[q], sm.line[warp], warp, lane);
+		const uint32_t s = i % EN_STAGES;
+		mbar_wait(&sm.scan_done[s], (i / EN_STAGES) & 1);
+		en_emit<KEYBITS, FRAME>(a, sm.info[s], sm.in[s], sm.D[s], sm.base[s], sm.blkL[s], sm.line[warp], warp, lane);
 		__syncwarp();
 		if (lane == 0)
 			mbar_arrive(&sm.empty[s]);
