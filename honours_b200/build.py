@@ -34,7 +34,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not _stale():
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc, *NVCC_FLAGS, "-o", LIB, *sources()]
+    extra = os.environ.get("PRESS_GPU_DEFINES", "").split()     # e.g. -DPG_ROLE_TIMING (tools/role_timing.py)
+    cmd = [nvcc, *NVCC_FLAGS, *extra, "-o", LIB, *sources()]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd))

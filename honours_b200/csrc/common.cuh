@@ -149,6 +149,32 @@ __device__ __forceinline__ uint64_t scan_tile(uint64_t *tile, uint64_t *block, u
 // (one L2 round trip in the common case); when rowpref[row - 1] is not there
 // yet the walk continues over the aggregates of whole earlier rows instead of
 // waiting for it, so no chain of dependent prefixes forms.
+// Sum of the aggregates tile[base + j], j in [0, count): all loads are issued
+// before the first flag is looked at (one L2 round trip when everything has
+// been published), words that were still empty are polled afterwards.  One warp;
+// returns this lane's partial sum.
+__device__ __forceinline__ uint64_t lb_row_sum(const uint64_t *tile, uint64_t base, uint32_t count)
+{
+	const int lane = threadIdx.x & 31;
+	uint64_t sum = 0;
+	for (uint32_t j0 = 0; j0 < count; j0 += 256) {
+		uint64_t w[8];
+#pragma unroll
+		for (int q = 0; q < 8; q++) {
+			const uint32_t j = j0 + 32 * q + lane;
+			w[q] = j < count ? ld_relaxed(tile + base + j) : LB_AGG;
+		}
+#pragma unroll
+		for (int q = 0; q < 8; q++) {
+			const uint32_t j = j0 + 32 * q + lane;
+			while ((w[q] >> 62) == 0)
+				w[q] = ld_relaxed(tile + base + j);
+			sum += w[q] & LB_VAL;
+		}
+	}
+	return sum;
+}
+
 __device__ __forceinline__ uint64_t row_scan(uint64_t *tile, uint64_t *rowpref, uint32_t g, uint32_t G,
 					     uint32_t total, uint64_t my)
 {
@@ -156,12 +182,10 @@ __device__ __forceinline__ uint64_t row_scan(uint64_t *tile, uint64_t *rowpref, 
 	const uint32_t row = g / G, col = g - row * G;
 	if (lane == 0)
 		st_relaxed(tile + g, LB_AGG | my);
-	uint64_t D = 0, wp = 0;
+	uint64_t wp = 0;
 	if (row > 0 && lane == 0)	// in flight together with the own-row words
 		wp = ld_relaxed(rowpref + row - 1);
-	// own row, tiles before this one
-	for (uint32_t j = lane; j < col; j += 32)
-		D += lb_wait(tile + (uint64_t) row * G + j) & LB_VAL;
+	uint64_t D = lb_row_sum(tile, (uint64_t) row * G, col);	// own row, tiles before this one
 	for (int64_t r = (int64_t) row - 1; r >= 0; r--) {
 		const uint64_t w = __shfl_sync(0xffffffffu, wp, 0);
 		if ((w >> 62) == 2) {
@@ -171,8 +195,7 @@ __device__ __forceinline__ uint64_t row_scan(uint64_t *tile, uint64_t *rowpref, 
 		}
 		if (r > 0 && lane == 0)
 			wp = ld_relaxed(rowpref + r - 1);
-		for (uint32_t j = lane; j < G; j += 32)	// earlier rows are always complete rows
-			D += lb_wait(tile + (uint64_t) r * G + j) & LB_VAL;
+		D += lb_row_sum(tile, (uint64_t) r * G, G);	// earlier rows are always complete rows
 	}
 	D = warp_sum64(D);
 	if (lane == 0 && (col == G - 1 || g == total - 1))	// tile[] keeps aggregates only

@@ -48,18 +48,18 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity)
 	uint32_t ok;
 	asm volatile(
 		"{\n\t.reg .pred p;\n\t"
-		"mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+		"mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
 		"selp.u32 %0, 1, 0, p;\n\t}"
 		: "=r"(ok)
-		: "r"(smem_u32(bar)), "r"(parity)
+		: "r"(smem_u32(bar)), "r"(parity), "r"(4000u)	// suspend-time hint (ns): idle roles stay off the issue ports
 		: "memory");
 	return ok != 0;
 }
 // Block until the phase with the given parity has completed.
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 {
-	while (!mbar_try_wait(bar, parity)) {
-	}
+	while (!mbar_try_wait(bar, parity))
+		__nanosleep(200);	// waiting roles must not take issue slots from working ones
 }
 
 // 1-D bulk copy global -> shared, completion signalled on `bar` (complete_tx).

@@ -242,6 +242,8 @@ int launch_svb_encode(const SvbEncArgs &a, cudaStream_t st)
 			return -1;
 		}
 		grid = per_sm * g_ctx.sms;
+		if (grid > EN_MAX_GRID)
+			grid = EN_MAX_GRID;	// the prefix window is sized for one CTA per SM
 	}
 	EvPair *ev = prof_begin(0, st);
 	void *params[] = {const_cast<SvbEncArgs *>(&a)};
@@ -388,6 +390,18 @@ int press_gpu_batch_status(void *d_scratch, void *stream)
 		return -1;
 	}
 	return (int) h.error;
+}
+
+/* debug: copy the scratch header's aux words (role timing of -DPG_ROLE_TIMING builds) */
+int press_gpu_debug_aux(void *d_scratch, void *stream, uint64_t out[29])
+{
+	Hdr h;
+	cudaStream_t st = (cudaStream_t) stream;
+	if (cudaMemcpyAsync(&h, d_scratch, sizeof h, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+	    cudaStreamSynchronize(st) != cudaSuccess)
+		return -1;
+	memcpy(out, h.aux, sizeof h.aux);
+	return 0;
 }
 
 void press_gpu_profile_enable(int on) { g_prof = on != 0; }

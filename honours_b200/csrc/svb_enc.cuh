@@ -15,10 +15,13 @@
 //   producer warp   tile metadata -> ONE cp.async.bulk (the tile, the group before
 //                   it for the previous sample, the group after it for the last key)
 //   4 count warps   |delta| test on 16-bit pairs (VIADD.16x2): does any value need
-//                   two bytes?  -> data bytes of each 512-sample block
-//   2 scan warps    row look-back over the per-tile byte counts (batch-wide prefix;
-//                   the key sections are data independent, plan.cuh)
-//   16 emit warps   delta + zigzag again from shared memory, bytes to the tile's
+//                   two bytes?  -> data bytes of each 1024-sample block
+//   publish warp    the tile's byte count -> global status word, as soon as it is known
+//   prefix warp     batch-wide prefix of the byte counts (the key sections are data
+//                   independent, plan.cuh) by a sliding window: P(g) = P(g - G) +
+//                   the G aggregates in between, G = grid size; the window holds
+//                   other CTAs' tiles only and is requested several tiles ahead
+//   8 emit warps    delta + zigzag again from shared memory, bytes to the tile's
 //                   container position: aligned 64-bit stores for blocks without a
 //                   two-byte value (the common case on nanopore signal),
 //                   per-sample placement through a staging line otherwise
@@ -36,14 +39,14 @@ namespace pg {
 
 constexpr int EN_TS = 8192;			// samples per tile
 constexpr int EN_TG = EN_TS / 8;		// 16-byte groups per tile
-constexpr int EN_NEMIT = 16;			// emit warps: 64 groups (512 samples) each
+constexpr int EN_NEMIT = 8;			// emit warps: 128 groups (1024 samples) each
 constexpr int EN_NCNT = 4;			// count warps: 256 groups each
 constexpr int EN_NSCAN = 2;
 constexpr int EN_EG = EN_TG / EN_NEMIT;		// groups per emit warp
-constexpr int EN_EC = EN_EG / 32;		// groups per emit lane (2)
+constexpr int EN_EC = EN_EG / 32;		// groups per emit lane (4)
 constexpr int EN_CG = EN_TG / EN_NCNT;		// groups per count warp
 constexpr int EN_CC = EN_CG / 32;		// groups per count lane (8)
-constexpr int EN_BPC = EN_NEMIT / EN_NCNT;	// 512-sample blocks per count warp
+constexpr int EN_BPC = EN_NEMIT / EN_NCNT;	// 1024-sample blocks per count warp
 constexpr int EN_W_CNT = EN_NEMIT;		// first count warp
 constexpr int EN_W_SCAN = EN_W_CNT + EN_NCNT;
 constexpr int EN_W_PROD = EN_W_SCAN + EN_NSCAN;
@@ -51,7 +54,9 @@ constexpr int EN_THREADS = (EN_W_PROD + 1) * 32;
 constexpr int EN_STAGES = 12;
 constexpr int EN_STAGE_BYTES = (EN_TG + 2) * 16 + 96;	// slots 0 .. TG+1, padded to 128
 constexpr int EN_LINE_BYTES = 2 * 8 * EN_EG + 16;	// per emit warp staging line (general path)
-static_assert(EN_STAGES % EN_NSCAN == 0, "a stage is always scanned by the same scan warp");
+constexpr int EN_PD = 4;				// look-back windows in flight (prefix warp)
+constexpr int EN_WW = 5;				// window words per lane: grid <= 32 * EN_WW + 1
+constexpr int EN_MAX_GRID = 32 * EN_WW + 1;
 
 struct EnTileInfo {
 	uint64_t off0, rend;	// sample range of the tile's read
@@ -65,8 +70,9 @@ struct EnSmem {
 	alignas(16) uint8_t line[EN_NEMIT][EN_LINE_BYTES];
 	EnTileInfo info[EN_STAGES];
 	uint64_t full[EN_STAGES], cnt_done[EN_STAGES], scan_done[EN_STAGES], empty[EN_STAGES];
-	uint64_t D[EN_STAGES], base[EN_STAGES];
-	uint32_t blkL[EN_STAGES][EN_NEMIT];	// data bytes of each 512-sample block
+	uint64_t blkP[EN_STAGES][EN_NEMIT];	// container position of each block's data (scan warp)
+	uint64_t base[EN_STAGES];		// start of the read's stream
+	uint32_t blkL[EN_STAGES][EN_NEMIT];	// data bytes of each 1024-sample block (count warps)
 };
 
 // word holding the sample before each of x's words' low halves
@@ -165,7 +171,7 @@ __device__ __forceinline__ void en_count(const EnTileInfo &ti, const uint8_t *st
 
 template <int KEYBITS, bool FRAME>
 __device__ __forceinline__ void en_emit(const SvbEncArgs &a, const EnTileInfo &ti, const uint8_t *st,
-					 uint64_t D, uint64_t base, const uint32_t *blkL, uint8_t *line,
+					 uint64_t P, uint64_t base, const uint32_t *blkL, uint8_t *line,
 					 int ew, int lane)
 {
 	constexpr uint32_t VPK = 8 / KEYBITS;
@@ -204,15 +210,8 @@ __device__ __forceinline__ void en_emit(const SvbEncArgs &a, const EnTileInfo &t
 	const bool inside = kw > A && 8 * (kw + EN_EG + 1) <= ti.rend;
 	const bool fast = inside && !__any_sync(0xffffffffu, (high & 0xff00ff00u) != 0);
 
-	// ---- container position of the block's data ---------------------------------------
-	uint32_t lv = lane < EN_NEMIT ? blkL[lane] : 0u;
-	const uint32_t L = __shfl_sync(0xffffffffu, lv, ew);
-	lv = lane < ew ? lv : 0u;
-#pragma unroll
-	for (int o = 8; o; o >>= 1)
-		lv += __shfl_xor_sync(0xffffffffu, lv, o);
-	const uint32_t woff = __shfl_sync(0xffffffffu, lv, 0);
-	const uint64_t P = ti.kx1 + D + woff;
+	// ---- container position of the block's data (scan warp) ---------------------------
+	const uint32_t L = blkL[ew];
 	if (P + L > a.out_cap) {
 		if (lane == 0)
 			atomicOr(&a.hdr->error, ERR_CAPACITY);
@@ -246,19 +245,17 @@ __device__ __forceinline__ void en_emit(const SvbEncArgs &a, const EnTileInfo &t
 				if (lane == 0)
 					pb = wrap;
 				const uint64_t v = (pb >> (64 - sh)) | (B[c] << sh);
-				if (c > 0 || lane > 0) {
+				if (c > 0 || lane > 0)
 					W[32 * c + lane] = v;
-				} else {	// the low s bytes of word 0 belong to whoever precedes
-					for (uint32_t b = s; b < 8; b++)
-						S[b - s] = (uint8_t) (B[0] >> (8 * (b - s)));
-				}
 			}
-			if (lane == 31) {	// word EN_EG: the last s bytes of the block's data
-				uint8_t *q = reinterpret_cast<uint8_t *>(W + EN_EG);
-				const uint64_t v = B[EN_EC - 1] >> (64 - sh);
-				for (uint32_t b = 0; b < s; b++)
-					q[b] = (uint8_t) (v >> (8 * b));
-			}
+			// partial words at both ends, one byte per lane: the low 8 - s bytes of
+			// chunk 0 and the top s bytes of the last chunk
+			const uint64_t b0 = __shfl_sync(0xffffffffu, B[0], 0);
+			const uint64_t bl = __shfl_sync(0xffffffffu, B[EN_EC - 1], 31) >> (64 - sh);
+			if ((uint32_t) lane < 8 - s)
+				S[lane] = (uint8_t) (b0 >> (8 * lane));
+			if ((uint32_t) lane < s)
+				reinterpret_cast<uint8_t *>(W + EN_EG)[lane] = (uint8_t) (bl >> (8 * lane));
 		}
 	} else {
 		uint32_t run = 0;
@@ -321,8 +318,34 @@ __device__ __forceinline__ void en_emit(const SvbEncArgs &a, const EnTileInfo &t
 	}
 }
 
+// number of window words of the CTA's i-th tile (tiles before it that are not its own)
+__device__ __forceinline__ uint32_t g_window(uint32_t i, uint32_t G)
+{
+	return i == 0 ? blockIdx.x : G - 1;
+}
+
 // ----------------------------------------------------------------------------
 // the kernel
+
+// role timing (cycles summed over warps and CTAs into hdr->aux[], lane 0 only);
+// compiled in with -DPG_ROLE_TIMING, see tools/role_timing.py
+#ifdef PG_ROLE_TIMING
+#define RT_DECL long long rt_t0 = 0, rt_acc[3] = {0, 0, 0}
+#define RT_BEGIN() (rt_t0 = clock64())
+#define RT_END(k) (rt_acc[k] += clock64() - rt_t0)
+#define RT_FLUSH(b)                                                                          \
+	do {                                                                                 \
+		if (lane == 0)                                                               \
+			for (int k_ = 0; k_ < 3; k_++)                                       \
+				atomicAdd((unsigned long long *) &a.hdr->aux[(b) + k_],      \
+					  (unsigned long long) rt_acc[k_]);                  \
+	} while (0)
+#else
+#define RT_DECL
+#define RT_BEGIN()
+#define RT_END(k)
+#define RT_FLUSH(b)
+#endif
 
 template <int KEYBITS, bool FRAME>
 __global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_constant__ SvbEncArgs a)
@@ -351,6 +374,7 @@ __global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_con
 	if (warp == EN_W_PROD) {
 		// ---- producer: metadata 32 tiles at a time, one bulk copy per tile ----------
 		const uint64_t nfull = a.nsamples >> 3;
+		RT_DECL;
 		for (uint32_t i0 = 0; i0 < nt; i0 += 32) {
 			const uint32_t i = i0 + lane;
 			EnTileInfo me = {};
@@ -370,8 +394,10 @@ __global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_con
 				const uint32_t it = i0 + l, s = it % EN_STAGES;
 				// the whole warp waits: a lane running ahead of its turn would see the
 				// parity of a phase that has not started yet as "complete"
+				RT_BEGIN();
 				if (it >= EN_STAGES)
 					mbar_wait(&sm.empty[s], ((it / EN_STAGES) & 1) ^ 1);
+				RT_END(0);
 				if (lane == (int) l) {
 					sm.info[s] = me;
 					// groups [kf, ke) of the sample array -> slots kf - (k0 - 1) ...
@@ -396,65 +422,173 @@ __global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_con
 				__syncwarp();
 			}
 		}
+		RT_FLUSH(0);
 		return;
 	}
 
-	if (warp >= EN_W_SCAN) {
-		// ---- scan warps: prefix of the data bytes, stream start of the read -----------
-		for (uint32_t i = warp - EN_W_SCAN; i < nt; i += EN_NSCAN) {
+	if (warp == EN_W_SCAN + 1) {
+		// ---- publish warp: the tile's byte count goes out the moment it is known ---------
+		for (uint32_t i = 0; i < nt; i++) {
 			const uint32_t s = i % EN_STAGES;
 			mbar_wait(&sm.cnt_done[s], (i / EN_STAGES) & 1);
-			const EnTileInfo ti = sm.info[s];
 			uint32_t L = lane < EN_NEMIT ? sm.blkL[s][lane] : 0u;
 #pragma unroll
-			for (int o = 8; o; o >>= 1)
+			for (int o = EN_NEMIT / 2; o; o >>= 1)
 				L += __shfl_xor_sync(0xffffffffu, L, o);
-			L = __shfl_sync(0xffffffffu, L, 0);
-			const uint64_t D = row_scan(a.status, a.status_blk, ti.g, G, total, L);
-			if (lane == 0) {
-				uint64_t base;
-				if (ti.t == 0) {
-					base = ti.kx0 + D;
-					st_relaxed(a.out_offsets + ti.r, base);
-				} else {	// published by the read's first tile (a lower tile)
-					do {
-						base = ld_relaxed(a.out_offsets + ti.r);
-					} while (base == SENTINEL);
-				}
-				if (ti.last)
-					st_relaxed(a.out_offsets + a.nreads, __ldg(a.kx + a.nreads) + D + L);
-				sm.D[s] = D;
-				sm.base[s] = base;
-				mbar_arrive(&sm.scan_done[s]);
-			}
-			__syncwarp();
+			if (lane == 0)
+				st_relaxed(a.status + blockIdx.x + (uint64_t) i * G, LB_AGG | L);
 		}
+		return;
+	}
+
+	if (warp == EN_W_SCAN) {
+		// ---- prefix warp: P(g) = P(g - G) + L(g - G) + sum of the G - 1 aggregates in between.
+		// The window holds other CTAs' tiles only, so it is requested EN_PD tiles ahead;
+		// nothing here waits for another CTA's prefix, only for its counts.
+		RT_DECL;
+		uint64_t w[EN_PD][EN_WW];
+		auto issue = [&](uint32_t i, uint64_t(&ww)[EN_WW]) {
+			const uint64_t g = blockIdx.x + (uint64_t) i * G;
+			const uint64_t lo = i == 0 ? 0 : g - G + 1;
+#pragma unroll
+			for (int q = 0; q < EN_WW; q++) {
+				const uint64_t j = lo + 32 * q + lane;
+				ww[q] = j < g ? ld_relaxed(a.status + j) : LB_AGG;
+			}
+		};
+		// -> sum of the window; Wt = sum of its last t words (the tiles of the same read
+		// before this one, when the read started inside the window)
+		auto resolve = [&](uint32_t i, uint64_t(&ww)[EN_WW], uint32_t t, uint64_t &Wt) -> uint64_t {
+			const uint64_t g = blockIdx.x + (uint64_t) i * G;
+			const uint64_t lo = i == 0 ? 0 : g - G + 1;
+			uint64_t sum = 0, sumt = 0;
+#pragma unroll
+			for (int q = 0; q < EN_WW; q++) {
+				const uint64_t j = lo + 32 * q + lane;
+				while ((ww[q] >> 62) == 0)
+					ww[q] = ld_relaxed(a.status + j);
+				sum += ww[q] & LB_VAL;
+				sumt += j + t >= g ? ww[q] & LB_VAL : 0;	// j >= g reads as 0
+			}
+			Wt = warp_sum64(sumt);
+			return warp_sum64(sum);
+		};
+#pragma unroll
+		for (int u = 0; u < EN_PD; u++)
+			if ((uint32_t) u < nt)
+				issue(u, w[u]);
+		uint64_t P = 0;		// exclusive prefix of the tile at hand
+		uint32_t Lprev = 0;
+		uint32_t r_prev = 0xffffffffu;
+		uint64_t base_prev = 0;
+		for (uint32_t i0 = 0; i0 < nt; i0 += EN_PD) {
+#pragma unroll
+			for (int u = 0; u < EN_PD; u++) {
+				const uint32_t i = i0 + u;
+				if (i >= nt)
+					break;
+				const uint32_t s = i % EN_STAGES;
+				RT_BEGIN();
+				mbar_wait(&sm.cnt_done[s], (i / EN_STAGES) & 1);
+				RT_END(0);
+				const EnTileInfo ti = sm.info[s];
+				// start of the read's stream = kx0 + prefix at the read's first tile.  When
+				// that tile lies inside the window (or is this tile) it follows from the
+				// window words; else it was published by that tile, at least a row ago
+				// (and the previous own tile of the same read already fetched it).
+				const bool far = ti.t > g_window(i, G);
+				uint64_t base = SENTINEL;
+				if (far && ti.r == r_prev)
+					base = base_prev;
+				else if (far && lane == 0)
+					base = ld_relaxed(a.out_offsets + ti.r);
+				RT_BEGIN();
+				uint64_t Wt;
+				const uint64_t W = resolve(i, w[u], ti.t, Wt);
+				RT_END(1);
+				RT_BEGIN();
+				P = i == 0 ? W : P + Lprev + W;
+				if (i + EN_PD < nt)
+					issue(i + EN_PD, w[u]);
+				const uint32_t lv = lane < EN_NEMIT ? sm.blkL[s][lane] : 0u;
+				uint32_t inc = lv;	// inclusive prefix over the blocks
+#pragma unroll
+				for (int o = 1; o < EN_NEMIT; o <<= 1) {
+					const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+					if (lane >= o)
+						inc += y;
+				}
+				const uint32_t L = __shfl_sync(0xffffffffu, inc, EN_NEMIT - 1);
+				Lprev = L;
+				if (lane < EN_NEMIT)
+					sm.blkP[s][lane] = ti.kx1 + P + inc - lv;
+				__syncwarp();	// ... before lane 0's releasing arrive
+				if (!far) {
+					base = ti.kx0 + P - Wt;
+				} else if (ti.r != r_prev) {
+					if (lane == 0)
+						while (base == SENTINEL)
+							base = ld_relaxed(a.out_offsets + ti.r);
+					base = __shfl_sync(0xffffffffu, base, 0);
+				}
+				r_prev = ti.r;
+				base_prev = base;
+				if (lane == 0) {
+					if (ti.t == 0)
+						st_relaxed(a.out_offsets + ti.r, base);
+					if (ti.last)
+						st_relaxed(a.out_offsets + a.nreads, __ldg(a.kx + a.nreads) + P + L);
+					sm.base[s] = base;
+					mbar_arrive(&sm.scan_done[s]);
+				}
+				__syncwarp();
+				RT_END(2);
+			}
+		}
+		RT_FLUSH(3);
 		return;
 	}
 
 	if (warp >= EN_W_CNT) {
 		// ---- count warps ------------------------------------------------------------------
 		const int cw = warp - EN_W_CNT;
+		RT_DECL;
 		for (uint32_t i = 0; i < nt; i++) {
 			const uint32_t s = i % EN_STAGES;
+			RT_BEGIN();
 			mbar_wait(&sm.full[s], (i / EN_STAGES) & 1);
+			RT_END(0);
+			RT_BEGIN();
 			en_count(sm.info[s], sm.in[s], sm.blkL[s], cw, lane);
 			__syncwarp();
 			if (lane == 0)
 				mbar_arrive(&sm.cnt_done[s]);
+			RT_END(1);
 		}
+		RT_FLUSH(6);
 		return;
 	}
 
 	// ---- emit warps ---------------------------------------------------------------------------
+	RT_DECL;
+	const long long rt_start = clock64();
 	for (uint32_t i = 0; i < nt; i++) {
 		const uint32_t s = i % EN_STAGES;
+		RT_BEGIN();
 		mbar_wait(&sm.scan_done[s], (i / EN_STAGES) & 1);
-		en_emit<KEYBITS, FRAME>(a, sm.info[s], sm.in[s], sm.D[s], sm.base[s], sm.blkL[s], sm.line[warp], warp, lane);
+		RT_END(0);
+		RT_BEGIN();
+		en_emit<KEYBITS, FRAME>(a, sm.info[s], sm.in[s], sm.blkP[s][warp], sm.base[s], sm.blkL[s], sm.line[warp], warp, lane);
 		__syncwarp();
 		if (lane == 0)
 			mbar_arrive(&sm.empty[s]);
+		RT_END(1);
 	}
+#ifdef PG_ROLE_TIMING
+	rt_acc[2] = clock64() - rt_start;
+#endif
+	(void) rt_start;
+	RT_FLUSH(9);
 }
 
 }  // namespace pg
