@@ -46,9 +46,10 @@ sms = torch.cuda.get_device_properties(0).multi_processor_count
 comp = int(d_oo[nreads].item())
 print(f"{method}: {nreads} reads {ns} samples ~{tiles:.0f} tiles, {ms:.3f} ms (incl. plan), "
       f"{(2 * ns + comp) / ms / 1e6:.0f} GB/s algorithmic; per tile per CTA: {ms * 1e-3 * 1.965e9 / (tiles / sms):.0f} cycles")
-names = ["producer: wait empty", "-", "-", "scan: wait cnt_done", "scan: row_scan", "scan: post (base poll, stores)",
-         "count: wait full", "count: work", "-", "emit: wait scan_done", "emit: work", "emit: total loop"]
-nw = [1, 1, 1, 1, 1, 1, 4, 4, 4, 8, 8, 8]
+names = ["producer: wait empty", "-", "-", "prefix: wait cnt_done", "prefix: resolve window", "prefix: post (P, issue)",
+         "prefix: post (block positions)", "prefix: post (lane 0: publish, arrive)", "-", "worker: waits (full, scan_done)", "worker: phase A", "worker: phase B fast", "worker: total loop",
+         "worker: phase B slow", "worker: slow blocks (count)", "prefix: window re-polls (count)"]
+nw = [1, 1, 1, 1, 1, 1, 1, 1, 1, 16, 16, 16, 16, 16, 16, 1]
 for k, nm in enumerate(names):
     if nm != "-":
-        print(f"  {nm:34s} {a[k] / nw[k] / tiles:10.0f} cycles per tile per warp")
+        print(f"  {nm:34s} {a[k] / nw[k] / tiles:10.1f} per tile per warp")
