@@ -14,27 +14,27 @@
 //
 //   producer warp   tile metadata -> ONE cp.async.bulk (the tile, the group before
 //                   it for the previous sample, the group after it for the last key)
-//   16 worker warps in two teams (team = tiles of one parity), 1024 samples per
-//                   warp and tile, two phases per tile:
-//                   A  4 x LDS.128 per lane, delta + zigzag on 16-bit pairs
-//                      (VIADD.16x2 / PRMT); no two-byte value in the block (the
-//                      common case on nanopore signal): the 8 data bytes of each
-//                      group stay packed in registers, the block's byte count
-//                      (1024) goes to shared memory; else the exact count does
-//                   B  EN_K - 1 team tiles later, when the tile's container
-//                      position is known: aligned 64-bit stores of the packed
-//                      bytes re-phased to the destination, or (blocks with
-//                      two-byte values, first / last blocks of a read) per-sample
-//                      placement through a staging line
+//   12 A warps      pull (tile, 1024-sample block) jobs: 4 x LDS.128 per lane, delta +
+//                   zigzag on 16-bit pairs (VIADD.16x2 / PRMT).  No two-byte value
+//                   in the block (the common case on nanopore signal): its 1024
+//                   data bytes are packed into the middle of the block's own staged
+//                   samples and the byte count (1024) is posted; else the exact
+//                   count is posted and the samples stay as they are
+//   12 B warps      pull (tile, block) jobs once the tile's container position is
+//                   known: aligned 64-bit stores of the packed bytes re-phased to
+//                   the destination, or (blocks with two-byte values, first / last
+//                   blocks of a read) per-sample placement through a staging line
 //   publish warp    the tile's byte count -> global status word, as soon as it is known
-//   prefix warp     batch-wide prefix of the byte counts (the key sections are data
-//                   independent, plan.cuh) by a sliding window: P(g) = P(g - G) +
+//   window warp +   batch-wide prefix of the byte counts (the key sections are data
+//   prefix warp     independent, plan.cuh) by a sliding window: P(g) = P(g - G) +
 //                   the G aggregates in between, G = grid size; the window holds
-//                   other CTAs' tiles only and is requested several tiles ahead;
-//                   per-block positions, key pointer, capacity checks, frame
+//                   other CTAs' tiles only and is fetched several tiles ahead by a
+//                   bulk copy; then the tile's position, the read's key pointer,
+//                   capacity checks, frame
 //
-// Phase A of later tiles runs while the prefix of earlier ones resolves, so the
-// look-back latency (a few L2 round trips) never stalls a worker.
+// A runs ahead of B by up to the ring depth, so the look-back latency (a few L2
+// round trips) and the occasional slow general-path block never hold up the
+// counts other CTAs are waiting for.
 #pragma once
 
 #include "common.cuh"
@@ -45,22 +45,23 @@ namespace pg {
 
 constexpr int EN_TS = 8192;			// samples per tile
 constexpr int EN_TG = EN_TS / 8;		// 16-byte groups per tile
-constexpr int EN_NB = 8;			// blocks per tile = worker warps per team
-constexpr int EN_TEAMS = 2;
-constexpr int EN_NWORK = EN_NB * EN_TEAMS;
-constexpr int EN_K = 3;				// team tiles between phase A and phase B, + 1
+constexpr int EN_NB = 8;			// 1024-sample blocks per tile
+constexpr int EN_NA = 12;			// A warps
+constexpr int EN_NBW = 12;			// B warps
 constexpr int EN_EG = EN_TG / EN_NB;		// groups per block (128)
 constexpr int EN_EC = EN_EG / 32;		// groups per lane (4)
-constexpr int EN_W_SCAN = EN_NWORK;		// prefix warp; + 1: publish warp
-constexpr int EN_W_PROD = EN_W_SCAN + 2;
+constexpr int EN_W_B = EN_NA;			// first B warp
+constexpr int EN_W_SCAN = EN_NA + EN_NBW;	// prefix warp; + 1: publish warp
+constexpr int EN_W_PROD = EN_W_SCAN + 3;	// (+ 2: window warp)
 constexpr int EN_THREADS = (EN_W_PROD + 1) * 32;
-constexpr int EN_STAGES = 11;
+constexpr int EN_STAGES = 12;
 constexpr int EN_STAGE_BYTES = (EN_TG + 2) * 16 + 96;	// slots 0 .. TG+1, padded to 128
 constexpr int EN_LINE_BYTES = 2 * 8 * EN_EG + 16;	// per worker staging line (general path)
 constexpr int EN_PD = 4;				// look-back windows in flight (prefix warp)
 constexpr int EN_WW = 5;				// window words per lane: grid <= 32 * EN_WW + 1
 constexpr int EN_MAX_GRID = 32 * EN_WW + 1;
-static_assert(EN_STAGES >= EN_TEAMS * EN_K + 2, "ring too short for the A/B distance");
+constexpr int EN_WIN_WORDS = 32 * EN_WW + 4;	// window + alignment slack
+constexpr int EN_PACK_OFF = 512;			// packed bytes of a fast block: middle of its 2 KB of samples
 
 struct EnTileInfo {
 	uint64_t off0, rend;	// sample range of the tile's read
@@ -73,13 +74,20 @@ struct EnTileInfo {
 
 struct EnSmem {
 	alignas(128) uint8_t in[EN_STAGES][EN_STAGE_BYTES];
-	alignas(16) uint8_t line[EN_NWORK][EN_LINE_BYTES];
+	alignas(16) uint8_t line[EN_NBW][EN_LINE_BYTES];
 	EnTileInfo info[EN_STAGES];
-	uint64_t full[EN_STAGES], cnt_done[EN_STAGES], scan_done[EN_STAGES], empty[EN_STAGES];
-	uint64_t blkP[EN_STAGES][EN_NB];	// container position of each block's data (prefix warp);
+	uint64_t full[EN_STAGES], cnt_done[EN_STAGES], pub_done[EN_STAGES], scan_done[EN_STAGES], empty[EN_STAGES];
+	uint64_t tileP[EN_STAGES];		// container position of the tile's data (prefix warp);
 						// SENTINEL: the tile does not fit, write nothing
+	uint32_t blkOff[EN_STAGES][EN_NB];	// data bytes of the tile's earlier blocks (publish warp)
+	uint32_t tileL[EN_STAGES];		// data bytes of the tile (publish warp)
 	uint64_t kbase[EN_STAGES];		// container position of the read's key section
 	uint32_t blkL[EN_STAGES][EN_NB];	// data bytes of each 1024-sample block (phase A)
+	uint32_t blkF[EN_STAGES][EN_NB];	// 1: the block's data bytes are packed in its stage (phase A)
+	uint32_t ajob, bjob;			// next (tile, block) job of the A / B warps
+	alignas(16) uint64_t win[EN_PD][EN_WIN_WORDS];	// look-back windows (prefix warp)
+	uint64_t win_full[EN_PD], wsum_done[EN_PD], wsum_free[EN_PD];
+	uint2 wsum[EN_PD];				// window sum, sum of its last t words
 };
 
 // word holding the sample before each of x's words' low halves
@@ -102,171 +110,130 @@ __device__ __forceinline__ uint32_t group_valid(uint64_t k, uint64_t off0, uint6
 }
 
 // ---------------------------------------------------------------------------
-// worker warp: one 1024-sample block of a tile
+// worker warps: one 1024-sample block of a tile.  The code a warp runs for the
+// common block is kept short and straight (the kernel is instruction-fetch
+// bound otherwise: five roles share one SM's instruction cache); everything
+// rare sits in compact, not unrolled, out-of-line routines.
 
-// what a worker keeps in registers between phase A and phase B of a block
-struct EnBlk {
-	uint64_t B[EN_EC];	// the 8 data bytes of each of the lane's groups (fast blocks)
-	uint32_t fast;		// warp-uniform
-};
-
-// zd words of the lane's EN_EC groups of block bw (+ of the group after the block)
-__device__ __forceinline__ void en_block_zd(const EnTileInfo &ti, const uint8_t *st, int bw, int lane,
-					    uint32_t (&z)[EN_EC][4], uint32_t (&zh)[4])
+// zd words of group gi of the staged tile (gi = -1 ... EN_TG: group before / after
+// included); the sample before the group comes straight from shared memory
+__device__ __forceinline__ void en_group_zd(const EnTileInfo &ti, const uint8_t *st, int gi, uint32_t (&z)[4])
 {
-	const uint64_t A = ti.off0 >> 3;
-	const uint32_t m = (uint32_t) (ti.off0 & 7);
-	const uint32_t g0 = bw * EN_EG;
-	uint4 x[EN_EC];
-#pragma unroll
-	for (int c = 0; c < EN_EC; c++)
-		x[c] = *reinterpret_cast<const uint4 *>(st + 16 * (g0 + 32 * c + lane + 1));
-	const uint32_t prev0 = *reinterpret_cast<const uint16_t *>(st + 16 * g0 + 14);
-	const uint4 xh = *reinterpret_cast<const uint4 *>(st + 16 * (g0 + EN_EG + 1));
-	// only the read's first group needs the "previous sample is 0" rule (trans.c:221)
-	const bool first = ti.t == 0 && bw == 0;
-#pragma unroll
-	for (int c = 0; c < EN_EC; c++) {
-		uint32_t prev = __shfl_up_sync(0xffffffffu, x[c].w >> 16, 1);
-		if (c > 0) {
-			const uint32_t wrap = __shfl_sync(0xffffffffu, x[c > 0 ? c - 1 : 0].w >> 16, 31);
-			if (lane == 0)
-				prev = wrap;
-		} else if (lane == 0) {
-			prev = prev0;
-		}
-		zd_group(x[c], prev, (first && c == 0 && lane == 0) ? (int) m : -1, z[c]);
-	}
-	zd_group(xh, __shfl_sync(0xffffffffu, x[EN_EC - 1].w >> 16, 31), -1, zh);
-	(void) A;
+	const uint4 x = *reinterpret_cast<const uint4 *>(st + 16 * (gi + 1));
+	const uint32_t prev = *reinterpret_cast<const uint16_t *>(st + 16 * (gi + 1) - 2);
+	// the read's first sample is coded against 0 (trans.c:221)
+	const bool first = ti.t == 0 && gi == 0;
+	zd_group(x, prev, first ? (int) (ti.off0 & 7) : -1, z);
 }
 
-// Phase A: byte count of the block -> blkL[bw]; fast blocks keep their bytes in R.
-__device__ __forceinline__ void en_phase_a(const EnTileInfo &ti, const uint8_t *st, uint32_t *blkL, int bw,
-					   int lane, EnBlk &R)
+// exact data-byte count of block bw (valid samples + two-byte values).  One warp.
+__device__ __noinline__ uint32_t en_count_slow(const EnTileInfo &ti, const uint8_t *st, int bw, int lane)
 {
-	uint32_t z[EN_EC][4], zh[4];
-	en_block_zd(ti, st, bw, lane, z, zh);
-	uint32_t high = zh[0] | zh[1] | zh[2] | zh[3];
-#pragma unroll
-	for (int c = 0; c < EN_EC; c++)
-		high |= z[c][0] | z[c][1] | z[c][2] | z[c][3];
-	const bool inside = (ti.flags >> bw) & 1u;
-	const bool fast = inside && !__any_sync(0xffffffffu, (high & 0xff00ff00u) != 0);
-	R.fast = fast;
-	if (fast) {
-#pragma unroll
-		for (int c = 0; c < EN_EC; c++) {
-			const uint32_t w0 = __byte_perm(z[c][0], z[c][1], 0x6420);
-			const uint32_t w1 = __byte_perm(z[c][2], z[c][3], 0x6420);
-			R.B[c] = ((uint64_t) w1 << 32) | w0;
-		}
-		if (lane == 0)
-			blkL[bw] = 8 * EN_EG;
-		return;
-	}
-	// exact: valid samples + two-byte values
 	const uint64_t kw = ti.k0 + bw * EN_EG;
 	uint32_t cnt = 0;
-#pragma unroll
+#pragma unroll 1
 	for (int c = 0; c < EN_EC; c++) {
+		uint32_t z[4];
+		en_group_zd(ti, st, bw * EN_EG + 32 * c + lane, z);
 		const uint32_t valid = group_valid(kw + 32 * c + lane, ti.off0, ti.rend);
-		cnt += __popc(valid) + __popc(flags_group(z[c]) & valid);
+		cnt += __popc(valid) + __popc(flags_group(z) & valid);
 	}
-#pragma unroll
-	for (int o = 16; o; o >>= 1)
-		cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-	if (lane == 0)
-		blkL[bw] = cnt;
+	return __reduce_add_sync(0xffffffffu, cnt);
 }
 
-// Phase B: the block's bytes to the container.  P = position of its data, L = their
-// number, kbase = position of the read's key section.
-template <int KEYBITS>
-__device__ __forceinline__ void en_phase_b(const SvbEncArgs &a, const EnTileInfo &ti, const uint8_t *st,
-					   uint64_t P, uint64_t kbase, uint32_t L, uint8_t *line, int bw,
-					   int lane, const EnBlk &R)
+// Phase A: byte count of the block -> blkL[bw].  A fast block (inside the read, no
+// two-byte value) also leaves its 1024 data bytes packed in the middle of its own
+// 2 KB of staged samples: the first and last group of the block, which the
+// neighbouring blocks read, stay intact.
+__device__ __forceinline__ void en_phase_a(const EnTileInfo &ti, uint8_t *st, uint32_t *blkL, uint32_t *blkF,
+					   int bw, int lane)
 {
-	const uint64_t jw = (uint64_t) ti.t * EN_TG + bw * EN_EG;	// read-relative group of the block
-	uint8_t *S = a.out + P;
-	const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(S) & 7);
-	if (R.fast) {
-		// chunk i = 32 c + lane holds exactly 8 data bytes; aligned word i of the output =
-		// top s bytes of chunk i - 1 | low 8 - s bytes of chunk i
-		uint64_t *W = reinterpret_cast<uint64_t *>(S - s);
-		if (s == 0) {
+	bool fast = (ti.flags >> bw) & 1u;	// block and the group after it inside the read
+	if (fast) {
+		const uint32_t g0 = bw * EN_EG;
+		uint4 x[EN_EC];
+#pragma unroll
+		for (int c = 0; c < EN_EC; c++)
+			x[c] = *reinterpret_cast<const uint4 *>(st + 16 * (g0 + 32 * c + lane + 1));
+		const uint32_t prev0 = *reinterpret_cast<const uint16_t *>(st + 16 * g0 + 14);
+		const uint4 xh = *reinterpret_cast<const uint4 *>(st + 16 * (g0 + EN_EG + 1));
+		uint32_t z[EN_EC][4], zh[4];
+#pragma unroll
+		for (int c = 0; c < EN_EC; c++) {
+			uint32_t prev = __shfl_up_sync(0xffffffffu, x[c].w >> 16, 1);
+			if (c > 0) {
+				const uint32_t wrap = __shfl_sync(0xffffffffu, x[c > 0 ? c - 1 : 0].w >> 16, 31);
+				if (lane == 0)
+					prev = wrap;
+			} else if (lane == 0) {
+				prev = prev0;
+			}
+			zd_group(x[c], prev, -1, z[c]);
+		}
+		zd_group(xh, __shfl_sync(0xffffffffu, x[EN_EC - 1].w >> 16, 31), -1, zh);
+		uint32_t high = zh[0] | zh[1] | zh[2] | zh[3];
+#pragma unroll
+		for (int c = 0; c < EN_EC; c++)
+			high |= z[c][0] | z[c][1] | z[c][2] | z[c][3];
+		fast = !__any_sync(0xffffffffu, (high & 0xff00ff00u) != 0);	// also orders the loads
+		if (fast) {
+			uint2 *pk = reinterpret_cast<uint2 *>(st + 16 * (g0 + 1) + EN_PACK_OFF);
 #pragma unroll
 			for (int c = 0; c < EN_EC; c++)
-				W[32 * c + lane] = R.B[c];
-		} else {
-			const uint32_t sh = 8 * s;
-#pragma unroll
-			for (int c = 0; c < EN_EC; c++) {
-				uint64_t pb = __shfl_up_sync(0xffffffffu, R.B[c], 1);
-				if (c > 0) {
-					const uint64_t wrap = __shfl_sync(0xffffffffu, R.B[c > 0 ? c - 1 : 0], 31);
-					if (lane == 0)
-						pb = wrap;
-				}
-				const uint64_t v = (pb >> (64 - sh)) | (R.B[c] << sh);
-				if (c > 0 || lane > 0)
-					W[32 * c + lane] = v;
-			}
-			// partial words at both ends, one byte per lane: the low 8 - s bytes of
-			// chunk 0 and the top s bytes of the last chunk
-			const uint64_t b0 = __shfl_sync(0xffffffffu, R.B[0], 0);
-			const uint64_t bl = __shfl_sync(0xffffffffu, R.B[EN_EC - 1], 31) >> (64 - sh);
-			if ((uint32_t) lane < 8 - s)
-				S[lane] = (uint8_t) (b0 >> (8 * lane));
-			if ((uint32_t) lane < s)
-				reinterpret_cast<uint8_t *>(W + EN_EG)[lane] = (uint8_t) (bl >> (8 * lane));
+				pk[32 * c + lane] = make_uint2(__byte_perm(z[c][0], z[c][1], 0x6420),
+							       __byte_perm(z[c][2], z[c][3], 0x6420));
 		}
-		warp_zero(a.out + kbase + jw * KEYBITS, EN_EG * KEYBITS, lane);
-		return;
 	}
+	const uint32_t cnt = fast ? 8 * EN_EG : en_count_slow(ti, st, bw, lane);
+	if (lane == 0) {
+		blkF[bw] = fast;
+		blkL[bw] = cnt;
+	}
+}
 
-	// ---- general path: everything again from the staged tile ---------------------------
+// general path of phase B: per-sample placement through the warp's staging line,
+// key bytes from the two-byte flags.  Group by group, nothing unrolled.
+template <int KEYBITS>
+__device__ __noinline__ void en_emit_slow(const SvbEncArgs &a, const EnTileInfo &ti, const uint8_t *st,
+					  uint64_t P, uint64_t kbase, uint32_t L, uint8_t *line, int bw, int lane)
+{
 	const uint64_t kw = ti.k0 + bw * EN_EG;
 	if (8 * kw >= ti.rend)
 		return;			// block past the end of the read
 	const uint64_t n = ti.rend - ti.off0;
 	const uint32_t m = (uint32_t) (ti.off0 & 7);
-	uint32_t z[EN_EC][4], zh[4], valid[EN_EC], fl[EN_EC];
-	en_block_zd(ti, st, bw, lane, z, zh);
+	const uint64_t jw = (uint64_t) ti.t * EN_TG + bw * EN_EG;	// read-relative group of the block
+	uint8_t *S = a.out + P, *kout = a.out + kbase;
+	const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(S) & 7);
 	uint32_t run = 0;
-#pragma unroll
+#pragma unroll 1
 	for (int c = 0; c < EN_EC; c++) {
-		valid[c] = group_valid(kw + 32 * c + lane, ti.off0, ti.rend);
-		fl[c] = flags_group(z[c]) & valid[c];
-		const uint32_t cnt = __popc(valid[c]) + __popc(fl[c]);
+		const int gi = bw * EN_EG + 32 * c + lane;
+		uint32_t z[4], zn[4];
+		en_group_zd(ti, st, gi, z);
+		const uint32_t valid = group_valid(kw + 32 * c + lane, ti.off0, ti.rend);
+		const uint32_t fl = flags_group(z) & valid;
+		const uint32_t cnt = __popc(valid) + __popc(fl);
 		const uint32_t inc = warp_inc_scan(cnt, lane);
 		uint8_t *p = line + s + run + inc - cnt;
 		run += __shfl_sync(0xffffffffu, inc, 31);
 #pragma unroll
 		for (int e = 0; e < 8; e++) {
-			if ((valid[c] >> e) & 1) {
-				const uint32_t v = (z[c][e >> 1] >> (16 * (e & 1))) & 0xffffu;
+			const uint32_t v = (z[e >> 1] >> (16 * (e & 1))) & 0xffffu;
+			if ((valid >> e) & 1) {
 				*p++ = (uint8_t) v;
-				if ((fl[c] >> e) & 1)
+				if ((fl >> e) & 1)
 					*p++ = (uint8_t) (v >> 8);
 			}
 		}
-	}
-	const uint32_t fh = flags_group(zh) & group_valid(kw + EN_EG, ti.off0, ti.rend);
-	__syncwarp();
-	warp_copy_out(line, S, L, lane);
-	__syncwarp();
-	// keys: the read-relative 8-sample block of group k is k - A; key block j = bits m..7
-	// of group j's flags + bits 0..m-1 of group j + 1's
-	uint8_t *kout = a.out + kbase;
-#pragma unroll
-	for (int c = 0; c < EN_EC; c++) {
-		uint32_t fnext = __shfl_down_sync(0xffffffffu, fl[c], 1);
-		const uint32_t wrap = c + 1 < EN_EC ? __shfl_sync(0xffffffffu, fl[c + 1 < EN_EC ? c + 1 : c], 0) : fh;
+		// keys: the read-relative 8-sample block of group k is k - A; key block j = bits
+		// m..7 of group j's flags + bits 0..m-1 of group j + 1's
+		uint32_t fnext = __shfl_down_sync(0xffffffffu, fl, 1);
+		en_group_zd(ti, st, bw * EN_EG + 32 * c + 32, zn);	// the group after lane 31's
 		if (lane == 31)
-			fnext = wrap;
+			fnext = flags_group(zn) & group_valid(kw + 32 * c + 32, ti.off0, ti.rend);
 		const uint64_t j = jw + 32 * c + lane;
-		const uint32_t f = ((fl[c] >> m) | (fnext << (8 - m))) & 0xffu;
+		const uint32_t f = ((fl >> m) | (fnext << (8 - m))) & 0xffu;
 		if (KEYBITS == 1) {
 			if (8 * j < n)
 				kout[j] = (uint8_t) f;
@@ -278,6 +245,55 @@ __device__ __forceinline__ void en_phase_b(const SvbEncArgs &a, const EnTileInfo
 				kout[2 * j + 1] = (uint8_t) (kk >> 8);
 		}
 	}
+	__syncwarp();
+	warp_copy_out(line, S, L, lane);
+	__syncwarp();
+}
+
+// Phase B of a fast block: its packed bytes to the container, key bytes zero.
+template <int KEYBITS>
+__device__ __forceinline__ void en_emit_fast(const SvbEncArgs &a, const EnTileInfo &ti, const uint8_t *st,
+					     uint64_t P, uint64_t kbase, int bw, int lane)
+{
+	const uint64_t jw = (uint64_t) ti.t * EN_TG + bw * EN_EG;	// read-relative group of the block
+	uint8_t *S = a.out + P;
+	const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(S) & 7);
+	uint64_t B[EN_EC];
+	const uint64_t *pk = reinterpret_cast<const uint64_t *>(st + 16 * (bw * EN_EG + 1) + EN_PACK_OFF);
+#pragma unroll
+	for (int c = 0; c < EN_EC; c++)
+		B[c] = pk[32 * c + lane];
+	// chunk i = 32 c + lane holds exactly 8 data bytes; aligned word i of the output =
+	// top s bytes of chunk i - 1 | low 8 - s bytes of chunk i
+	uint64_t *W = reinterpret_cast<uint64_t *>(S - s);
+	if (s == 0) {
+#pragma unroll
+		for (int c = 0; c < EN_EC; c++)
+			W[32 * c + lane] = B[c];
+	} else {
+		const uint32_t sh = 8 * s;
+#pragma unroll
+		for (int c = 0; c < EN_EC; c++) {
+			uint64_t pb = __shfl_up_sync(0xffffffffu, B[c], 1);
+			if (c > 0) {
+				const uint64_t wrap = __shfl_sync(0xffffffffu, B[c > 0 ? c - 1 : 0], 31);
+				if (lane == 0)
+					pb = wrap;
+			}
+			const uint64_t v = (pb >> (64 - sh)) | (B[c] << sh);
+			if (c > 0 || lane > 0)
+				W[32 * c + lane] = v;
+		}
+		// partial words at both ends, one byte per lane: the low 8 - s bytes of chunk 0
+		// and the top s bytes of the last chunk
+		const uint64_t b0 = __shfl_sync(0xffffffffu, B[0], 0);
+		const uint64_t bl = __shfl_sync(0xffffffffu, B[EN_EC - 1], 31) >> (64 - sh);
+		if ((uint32_t) lane < 8 - s)
+			S[lane] = (uint8_t) (b0 >> (8 * lane));
+		if ((uint32_t) lane < s)
+			reinterpret_cast<uint8_t *>(W + EN_EG)[lane] = (uint8_t) (bl >> (8 * lane));
+	}
+	warp_zero(a.out + kbase + jw * KEYBITS, EN_EG * KEYBITS, lane);
 }
 
 // number of window words of the CTA's i-th tile (tiles before it that are not its own)
@@ -324,9 +340,17 @@ __global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_con
 		for (int s = 0; s < EN_STAGES; s++) {
 			mbar_init(&sm.full[s], 1);
 			mbar_init(&sm.cnt_done[s], EN_NB);
+			mbar_init(&sm.pub_done[s], 1);
 			mbar_init(&sm.scan_done[s], 1);
 			mbar_init(&sm.empty[s], EN_NB);
 		}
+		for (int u = 0; u < EN_PD; u++) {
+			mbar_init(&sm.win_full[u], 1);
+			mbar_init(&sm.wsum_done[u], 1);
+			mbar_init(&sm.wsum_free[u], 1);
+		}
+		sm.ajob = 0;
+		sm.bjob = 0;
 		mbar_fence_init();
 	}
 	__syncthreads();
@@ -396,221 +420,250 @@ __global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_con
 	}
 
 	if (warp == EN_W_SCAN + 1) {
-		// ---- publish warp: the tile's byte count goes out the moment it is known ---------
+		// ---- publish warp: the tile's byte count goes out the moment it is known; the
+		// blocks' offsets inside the tile for the B warps ---------------------------------
 		for (uint32_t i = 0; i < nt; i++) {
 			const uint32_t s = i % EN_STAGES;
 			mbar_wait(&sm.cnt_done[s], (i / EN_STAGES) & 1);
-			uint32_t L = lane < EN_NB ? sm.blkL[s][lane] : 0u;
+			const uint32_t lv = lane < EN_NB ? sm.blkL[s][lane] : 0u;
+			uint32_t inc = lv;	// inclusive prefix over the blocks
 #pragma unroll
-			for (int o = EN_NB / 2; o; o >>= 1)
-				L += __shfl_xor_sync(0xffffffffu, L, o);
-			if (lane == 0)
-				st_relaxed(a.status + blockIdx.x + (uint64_t) i * G, LB_AGG | L);
+			for (int o = 1; o < EN_NB; o <<= 1) {
+				const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+				if (lane >= o)
+					inc += y;
+			}
+			if (lane < EN_NB)
+				sm.blkOff[s][lane] = inc - lv;
+			if (lane == EN_NB - 1) {
+				st_relaxed(a.status + blockIdx.x + (uint64_t) i * G, LB_AGG | inc);
+				sm.tileL[s] = inc;
+			}
+			__syncwarp();
+			if (lane == EN_NB - 1)
+				mbar_arrive(&sm.pub_done[s]);
 		}
 		return;
 	}
 
-	if (warp == EN_W_SCAN) {
-		// ---- prefix warp: P(g) = P(g - G) + L(g - G) + sum of the G - 1 aggregates in between.
-		// The window holds other CTAs' tiles only, so it is requested EN_PD tiles ahead;
-		// nothing here waits for another CTA's prefix, only for its counts.
+	if (warp == EN_W_SCAN + 2) {
+		// ---- window warp: for every tile of the CTA the sum of the G - 1 aggregates between
+		// it and the CTA's previous tile (other CTAs' tiles only), requested EN_PD tiles ahead
+		// by a bulk copy into shared memory (in registers the pending loads would sit on the
+		// scoreboards every LDS / SHFL of the warp waits on).
 		RT_DECL;
-		uint64_t w[EN_PD][EN_WW];
-		auto issue = [&](uint32_t i, uint64_t(&ww)[EN_WW]) {
+		// window of the CTA's i-th tile: words [lo, g) of the status array; the copy covers
+		// the 16-byte aligned superset starting at lo & ~1
+		auto issue = [&](uint32_t i) {
 			const uint64_t g = blockIdx.x + (uint64_t) i * G;
 			const uint64_t lo = i == 0 ? 0 : g - G + 1;
-#pragma unroll
-			for (int q = 0; q < EN_WW; q++) {
-				const uint64_t j = lo + 32 * q + lane;
-				ww[q] = j < g ? ld_relaxed(a.status + j) : LB_AGG;
-			}
-		};
-		// reload the words that were still empty last time (non-blocking)
-		auto repoll = [&](uint32_t i, uint64_t(&ww)[EN_WW]) {
-			const uint64_t g = blockIdx.x + (uint64_t) i * G;
-			const uint64_t lo = i == 0 ? 0 : g - G + 1;
-#pragma unroll
-			for (int q = 0; q < EN_WW; q++)
-				if ((ww[q] >> 62) == 0) {
-					ww[q] = ld_relaxed(a.status + lo + 32 * q + lane);
-#ifdef PG_ROLE_TIMING
-					atomicAdd((unsigned long long *) &a.hdr->aux[15], 1ull);
-#endif
+			const uint64_t la = lo & ~1ull;
+			const uint32_t bytes = (uint32_t) ((g - la + 1) & ~1ull) * 8;
+			const uint32_t u = i % EN_PD;
+			if (lane == 0) {
+				if (bytes) {
+					mbar_arrive_expect_tx(&sm.win_full[u], bytes);
+					tma_load_1d(sm.win[u], a.status + la, bytes, &sm.win_full[u]);
+				} else {
+					mbar_arrive(&sm.win_full[u]);
 				}
-		};
-		auto complete = [&](const uint64_t(&ww)[EN_WW]) -> bool {
-			bool ok = true;
-#pragma unroll
-			for (int q = 0; q < EN_WW; q++)
-				ok = ok && (ww[q] >> 62) != 0;
-			return __all_sync(0xffffffffu, ok);
-		};
-		// -> sum of the (complete) window; Wt = sum of its last t words (the tiles of the
-		// same read before this one, when the read started inside the window)
-		auto resolve = [&](uint32_t i, const uint64_t(&ww)[EN_WW], uint32_t t, uint64_t &Wt) -> uint64_t {
-			const uint64_t g = blockIdx.x + (uint64_t) i * G;
-			const uint64_t lo = i == 0 ? 0 : g - G + 1;
-			uint64_t sum = 0, sumt = 0;
-#pragma unroll
-			for (int q = 0; q < EN_WW; q++) {
-				const uint64_t j = lo + 32 * q + lane;
-				sum += ww[q] & LB_VAL;
-				sumt += j + t >= g ? ww[q] & LB_VAL : 0;	// j >= g reads as 0
 			}
-			Wt = warp_sum64(sumt);
-			return warp_sum64(sum);
 		};
+		for (uint32_t i = 0; i < EN_PD && i < nt; i++)
+			issue(i);
+		uint32_t wphase = 0;	// bit u: parity of the next completion of win_full[u]
+		for (uint32_t i = 0; i < nt; i++) {
+			const uint32_t s = i % EN_STAGES, u = i % EN_PD;
+			RT_BEGIN();
+			mbar_wait(&sm.pub_done[s], (i / EN_STAGES) & 1);	// the tile's info is there
+			RT_END(0);
+			RT_BEGIN();
+			const uint32_t t = sm.info[s].t;
+			const uint32_t wl = g_window(i, G);	// window words: tiles [g - wl, g)
+			const uint32_t skew = (uint32_t) ((blockIdx.x + (uint64_t) i * G - wl) & 1);	// lo - (lo & ~1)
+			uint32_t W, Wt;
+			for (;;) {
+				mbar_wait(&sm.win_full[u], (wphase >> u) & 1);
+				wphase ^= 1u << u;
+				uint32_t sum = 0, sumt = 0;
+				bool ok = true;
 #pragma unroll
-		for (int u = 0; u < EN_PD; u++)
-			if ((uint32_t) u < nt)
-				issue(u, w[u]);
+				for (int q = 0; q < EN_WW; q++) {
+					const uint32_t j = 32 * q + lane;	// word j of the window
+					const uint64_t w = j < wl ? sm.win[u][j + skew] : LB_AGG;
+					ok = ok && (w >> 62) != 0;
+					sum += (uint32_t) w;			// a tile holds < 2^15 bytes
+					sumt += j + t >= wl ? (uint32_t) w : 0u;
+				}
+				if (__all_sync(0xffffffffu, ok)) {
+					W = __reduce_add_sync(0xffffffffu, sum);
+					Wt = __reduce_add_sync(0xffffffffu, sumt);
+					break;
+				}
+				issue(i);	// some counts were not out yet: fetch the window again
+#ifdef PG_ROLE_TIMING
+				if (lane == 0)
+					atomicAdd((unsigned long long *) &a.hdr->aux[24], 1ull);
+#endif
+			}
+			RT_END(1);
+			RT_BEGIN();
+			if (i + EN_PD < nt)	// (the __all_sync above: every lane has read win[u])
+				issue(i + EN_PD);
+			if (i >= EN_PD)		// the prefix warp has taken the sums of tile i - EN_PD
+				mbar_wait(&sm.wsum_free[u], ((i / EN_PD) & 1) ^ 1);
+			if (lane == 0) {
+				sm.wsum[u] = make_uint2(W, Wt);
+				mbar_arrive(&sm.wsum_done[u]);
+			}
+			__syncwarp();
+			RT_END(2);
+		}
+		RT_FLUSH(21);
+		return;
+	}
+
+	if (warp == EN_W_SCAN) {
+		// ---- prefix warp: P(g) = P(g - G) + L(g - G) + window sum.  Nothing here waits for
+		// another CTA's prefix, only (through the window warp) for its counts.
+		RT_DECL;
 		uint64_t P = 0;		// exclusive prefix of the tile at hand
 		uint32_t Lprev = 0;
 		uint32_t r_prev = 0xffffffffu;
 		uint64_t base_prev = 0;
-		for (uint32_t i0 = 0; i0 < nt; i0 += EN_PD) {
-#pragma unroll
-			for (int u = 0; u < EN_PD; u++) {
-				const uint32_t i = i0 + u;
-				if (i >= nt)
-					break;
-				const uint32_t s = i % EN_STAGES;
-				RT_BEGIN();
-				mbar_wait(&sm.cnt_done[s], (i / EN_STAGES) & 1);
-				RT_END(0);
-				const EnTileInfo ti = sm.info[s];
-				// start of the read's stream = kx0 + prefix at the read's first tile.  When
-				// that tile lies inside the window (or is this tile) it follows from the
-				// window words; else it was published by that tile, at least a row ago
-				// (and the previous own tile of the same read already fetched it).
-				const bool far = ti.t > g_window(i, G);
-				uint64_t base = SENTINEL;
-				if (far && ti.r == r_prev)
-					base = base_prev;
-				else if (far && lane == 0)
-					base = ld_relaxed(a.out_offsets + ti.r);
-				RT_BEGIN();
-				// windows of this and the next EN_PD - 1 tiles are polled together, so the
-				// round trips of one tile's late words overlap the others'
-				while (!complete(w[u])) {
-#pragma unroll
-					for (int v = 0; v < EN_PD; v++) {
-						const uint32_t tv = v >= u ? i0 + v : i0 + EN_PD + v;
-						if (tv < nt)
-							repoll(tv, w[v]);
-					}
-				}
-				uint64_t Wt;
-				const uint64_t W = resolve(i, w[u], ti.t, Wt);
-				RT_END(1);
-				RT_BEGIN();
-				P = i == 0 ? W : P + Lprev + W;
-				if (i + EN_PD < nt)
-					issue(i + EN_PD, w[u]);
-				RT_END(2);
-				RT_BEGIN();
-				const uint32_t lv = lane < EN_NB ? sm.blkL[s][lane] : 0u;
-				uint32_t inc = lv;	// inclusive prefix over the blocks
-#pragma unroll
-				for (int o = 1; o < EN_NB; o <<= 1) {
-					const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
-					if (lane >= o)
-						inc += y;
-				}
-				const uint32_t L = __shfl_sync(0xffffffffu, inc, EN_NB - 1);
-				Lprev = L;
-				if (!far) {
-					base = ti.kx0 + P - Wt;
-				} else if (ti.r != r_prev) {
-					if (lane == 0)
-						while (base == SENTINEL)
-							base = ld_relaxed(a.out_offsets + ti.r);
-					base = __shfl_sync(0xffffffffu, base, 0);
-				}
-				r_prev = ti.r;
-				base_prev = base;
+		for (uint32_t i = 0; i < nt; i++) {
+			const uint32_t s = i % EN_STAGES, u = i % EN_PD;
+			RT_BEGIN();
+			mbar_wait(&sm.pub_done[s], (i / EN_STAGES) & 1);
+			RT_END(0);
+			RT_BEGIN();
+			const EnTileInfo &ti = sm.info[s];
+			const uint32_t t = ti.t, r = ti.r;
+			const uint32_t L = sm.tileL[s];
+			// start of the read's stream = kx0 + prefix at the read's first tile.  When
+			// that tile lies inside the window (or is this tile) it follows from the
+			// window words; else it was published by that tile, at least a row ago
+			// (and the previous own tile of the same read already fetched it).
+			const bool far = t > g_window(i, G);
+			uint64_t base = SENTINEL;
+			if (far && r == r_prev)
+				base = base_prev;
+			else if (far && lane == 0)
+				base = ld_relaxed(a.out_offsets + r);
+			mbar_wait(&sm.wsum_done[u], (i / EN_PD) & 1);
+			const uint2 ws = sm.wsum[u];
+			__syncwarp();
+			if (lane == 0)
+				mbar_arrive(&sm.wsum_free[u]);
+			RT_END(1);
+			RT_BEGIN();
+			P = i == 0 ? ws.x : P + Lprev + ws.x;
+			Lprev = L;
+			if (!far) {
+				base = ti.kx0 + P - ws.y;
+			} else if (r != r_prev) {
+				if (lane == 0)
+					while (base == SENTINEL)
+						base = ld_relaxed(a.out_offsets + r);
+				base = __shfl_sync(0xffffffffu, base, 0);
+			}
+			r_prev = r;
+			base_prev = base;
+			if (lane == 0) {
 				// the tile's bytes and the read's frame + key section must fit
 				const uint64_t n = ti.rend - ti.off0;
 				const uint64_t kb = base + (FRAME ? 4 : 0);
-				const bool fits = ti.kx1 + P + L <= a.out_cap &&
+				const uint64_t tp = ti.kx1 + P;
+				const bool fits = tp + L <= a.out_cap &&
 						  kb + (n + 8 / KEYBITS - 1) / (8 / KEYBITS) <= a.out_cap;
-				if (lane < EN_NB)
-					sm.blkP[s][lane] = fits ? ti.kx1 + P + inc - lv : SENTINEL;
-				if (FRAME && fits && ti.t == 0 && lane < 4)	// press.c:1875-1879, 2035-2039
-					a.out[base + lane] = (uint8_t) ((uint32_t) n >> (8 * lane));
-				__syncwarp();	// ... before lane 0's releasing arrive
-				RT_END(3);
-				RT_BEGIN();
-				if (lane == 0) {
-					if (!fits)
-						atomicOr(&a.hdr->error, ERR_CAPACITY);
-					if (ti.t == 0)
-						st_relaxed(a.out_offsets + ti.r, base);
-					if (ti.flags >> 31)
-						st_relaxed(a.out_offsets + a.nreads, __ldg(a.kx + a.nreads) + P + L);
-					sm.kbase[s] = kb;
-					mbar_arrive(&sm.scan_done[s]);
+				if (!fits)
+					atomicOr(&a.hdr->error, ERR_CAPACITY);
+				if (FRAME && fits && t == 0) {	// press.c:1875-1879, 2035-2039
+#pragma unroll
+					for (int b = 0; b < 4; b++)
+						a.out[base + b] = (uint8_t) ((uint32_t) n >> (8 * b));
 				}
-				__syncwarp();
-				RT_END(4);
+				if (t == 0)
+					st_relaxed(a.out_offsets + r, base);
+				if (ti.flags >> 31)
+					st_relaxed(a.out_offsets + a.nreads, __ldg(a.kx + a.nreads) + P + L);
+				sm.tileP[s] = fits ? tp : SENTINEL;
+				sm.kbase[s] = kb;
+				mbar_arrive(&sm.scan_done[s]);
 			}
+			__syncwarp();
+			RT_END(2);
 		}
 		RT_FLUSH(3);
 		return;
 	}
 
-	// ---- worker warps: team = tiles of one parity, block = warp index in the team -------------
-	const int team = warp / EN_NB, bw = warp - team * EN_NB;
-	const uint32_t nk = nt > (uint32_t) team ? (nt - team + EN_TEAMS - 1) / EN_TEAMS : 0;	// team tiles
-	EnBlk R[EN_K];
-	RT_DECL;
-	const long long rt_start = clock64();
-	for (uint32_t k0 = 0; k0 < nk + EN_K - 1; k0 += EN_K) {
-#pragma unroll
-		for (int u = 0; u < EN_K; u++) {
-			const uint32_t k = k0 + u;
-			if (k < nk) {		// phase A of team tile k
-				const uint32_t i = team + k * EN_TEAMS, s = i % EN_STAGES;
-				RT_BEGIN();
-				mbar_wait(&sm.full[s], (i / EN_STAGES) & 1);
-				RT_END(0);
-				RT_BEGIN();
-				en_phase_a(sm.info[s], sm.in[s], sm.blkL[s], bw, lane, R[u]);
-				__syncwarp();
-				if (lane == 0)
-					mbar_arrive(&sm.cnt_done[s]);
-				RT_END(1);
-			}
-			if (k >= EN_K - 1 && k - (EN_K - 1) < nk) {	// phase B of team tile k - (EN_K - 1)
-				const uint32_t i = team + (k - (EN_K - 1)) * EN_TEAMS, s = i % EN_STAGES;
-				RT_BEGIN();
-				mbar_wait(&sm.scan_done[s], (i / EN_STAGES) & 1);
-				RT_END(0);
-				RT_BEGIN();
-				const uint64_t P = sm.blkP[s][bw];
-				if (P != SENTINEL)
-					en_phase_b<KEYBITS>(a, sm.info[s], sm.in[s], P, sm.kbase[s], sm.blkL[s][bw],
-							    sm.line[warp], bw, lane, R[(u + 1) % EN_K]);
-				__syncwarp();
-				if (lane == 0)
-					mbar_arrive(&sm.empty[s]);
-#ifdef PG_ROLE_TIMING
-				if (R[(u + 1) % EN_K].fast) {
-					RT_END(2);
-				} else {
-					RT_END(4);
-					rt_acc[5]++;
-				}
-#endif
-			}
+	const uint32_t njobs = nt * EN_NB;
+	if (warp < EN_W_B) {
+		// ---- A warps -------------------------------------------------------------------------
+		RT_DECL;
+		for (;;) {
+			uint32_t j = 0;
+			if (lane == 0)
+				j = atomicAdd(&sm.ajob, 1u);
+			j = __shfl_sync(0xffffffffu, j, 0);
+			if (j >= njobs)
+				break;
+			const uint32_t i = j / EN_NB, bw = j - i * EN_NB, s = i % EN_STAGES;
+			RT_BEGIN();
+			// the stage's previous tile is done (so this wait names the right phase even
+			// if bulk copies complete out of order), then this tile has landed
+			if (i >= EN_STAGES)
+				mbar_wait(&sm.empty[s], ((i / EN_STAGES) & 1) ^ 1);
+			mbar_wait(&sm.full[s], (i / EN_STAGES) & 1);
+			RT_END(0);
+			RT_BEGIN();
+			en_phase_a(sm.info[s], sm.in[s], sm.blkL[s], sm.blkF[s], bw, lane);
+			__syncwarp();
+			if (lane == 0)
+				mbar_arrive(&sm.cnt_done[s]);
+			RT_END(1);
 		}
+		RT_FLUSH(9);
+		return;
 	}
+
+	// ---- B warps ---------------------------------------------------------------------------------
+	RT_DECL;
+	for (;;) {
+		uint32_t j = 0;
+		if (lane == 0)
+			j = atomicAdd(&sm.bjob, 1u);
+		j = __shfl_sync(0xffffffffu, j, 0);
+		if (j >= njobs)
+			break;
+		const uint32_t i = j / EN_NB, bw = j - i * EN_NB, s = i % EN_STAGES;
+		RT_BEGIN();
+		mbar_wait(&sm.scan_done[s], (i / EN_STAGES) & 1);
+		RT_END(0);
+		RT_BEGIN();
+		const uint64_t P = sm.tileP[s];
+		const bool fast = sm.blkF[s][bw] != 0;
+		if (P != SENTINEL) {
+			if (fast)
+				en_emit_fast<KEYBITS>(a, sm.info[s], sm.in[s], P + sm.blkOff[s][bw], sm.kbase[s], bw, lane);
+			else
+				en_emit_slow<KEYBITS>(a, sm.info[s], sm.in[s], P + sm.blkOff[s][bw], sm.kbase[s],
+						      sm.blkL[s][bw], sm.line[warp - EN_W_B], bw, lane);
+		}
+		__syncwarp();
+		if (lane == 0)
+			mbar_arrive(&sm.empty[s]);
 #ifdef PG_ROLE_TIMING
-	if (lane == 0)
-		atomicAdd((unsigned long long *) &a.hdr->aux[12], (unsigned long long) (clock64() - rt_start));
+		if (fast) {
+			RT_END(1);
+		} else {
+			RT_END(2);
+			rt_acc[3]++;
+		}
 #endif
-	(void) rt_start;
-	RT_FLUSH(9);
+	}
+	RT_FLUSH(15);
 }
 
 }  // namespace pg

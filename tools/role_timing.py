@@ -46,10 +46,16 @@ sms = torch.cuda.get_device_properties(0).multi_processor_count
 comp = int(d_oo[nreads].item())
 print(f"{method}: {nreads} reads {ns} samples ~{tiles:.0f} tiles, {ms:.3f} ms (incl. plan), "
       f"{(2 * ns + comp) / ms / 1e6:.0f} GB/s algorithmic; per tile per CTA: {ms * 1e-3 * 1.965e9 / (tiles / sms):.0f} cycles")
-names = ["producer: wait empty", "-", "-", "prefix: wait cnt_done", "prefix: resolve window", "prefix: post (P, issue)",
-         "prefix: post (block positions)", "prefix: post (lane 0: publish, arrive)", "-", "worker: waits (full, scan_done)", "worker: phase A", "worker: phase B fast", "worker: total loop",
-         "worker: phase B slow", "worker: slow blocks (count)", "prefix: window re-polls (count)"]
-nw = [1, 1, 1, 1, 1, 1, 1, 1, 1, 16, 16, 16, 16, 16, 16, 1]
+rows = [(0, "producer: wait empty", 1), (3, "prefix: wait pub_done", 1), (4, "prefix: info, wait window sum", 1),
+        (5, "prefix: P, base, fits, arrive", 1), (21, "window: wait pub_done", 1), (22, "window: sum", 1),
+        (23, "window: issue next, hand over", 1), (9, "A warps: wait (empty, full)", 12),
+        (10, "A warps: phase A", 12), (15, "B warps: wait scan_done", 12), (16, "B warps: fast blocks", 12),
+        (17, "B warps: slow blocks", 12), (24, "prefix: window re-polls (count)", 1)]
+for k, nm, n in rows:
+    print(f"  {nm:40s} {a[k] / n / tiles:10.1f} per tile per warp")
+print(f"  slow blocks: {a[18] / tiles:.3f} per tile, {a[17] / max(a[18], 1):.0f} cycles each; "
+      f"fast blocks {a[16] / max(8 * tiles - a[18], 1):.0f} cycles each; phase A {a[10] / (8 * tiles):.0f} cycles per block")
+raise SystemExit
 for k, nm in enumerate(names):
     if nm != "-":
         print(f"  {nm:34s} {a[k] / nw[k] / tiles:10.1f} per tile per warp")
