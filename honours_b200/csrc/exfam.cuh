@@ -1,0 +1,688 @@
+// exfam.cuh -- the exception-coded methods: one-byte zigzag-delta payload with the
+// values > 255 ("exceptions") pulled out into a header.
+//
+//   VBE21_ZD        press.c:2679-2765, 3411-3448   raw u32 positions / u16 values
+//   VBSSE21_ZD      press.c:3186-3360, 3543-3580   svb32 position gaps / svb16 values - 256
+//   EX_ZD           ex_zd.c:9-515, press.c:8461-8501   qts shift, svb32 gaps / svb32 values - 256
+//   SHUFF_VBE21_ZD  press.c:4409-4498, huffman.c:848-887   VBE21 header + static Huffman payload
+//
+// Every stream is header first, and the header's length depends on ALL exceptions
+// of the read, so no byte of a read's payload can be placed before the whole read
+// has been seen: encode is two sweeps over the samples with small per-read steps
+// in between, every step a plain grid (no inter-CTA dependency anywhere):
+//
+//   ex_count   (tile)  zd in registers -> #exceptions, Huffman bits, OR of the samples;
+//                      exceptions captured in tile order into a pool
+//   ex_readq   (read)  ex-zd only: q = min(5, ctz(OR))  (ex_zd.c:358-381); reads with
+//                      q > 0 are re-counted on the shifted signal
+//   ex_size    (read)  per-tile prefixes (exception index, payload position), list
+//                      sizes, header length, stream size
+//   ex_offsets (batch) exclusive scan of the sizes -> out_offsets
+//   ex_header  (read)  header + exception lists at the stream's final place
+//   ex_emit    (tile)  zd again -> payload bytes / Huffman bits to their final place
+//
+// Tile = 4096 samples of one read cut on 16-byte boundaries of the sample array
+// (aligned 128-bit loads), 16 contiguous samples per thread.
+#pragma once
+
+#include "common.cuh"
+#include "svb_zd.cuh"
+
+namespace pg {
+
+constexpr int XT = 4096;		// samples per tile
+constexpr int XG = XT / 8;		// 16-byte groups per tile
+constexpr uint32_t X_FAIL = 0xffffffffu;	// r_hdr of a read that has no stream (empty, ex-zd cap)
+constexpr int X_STAGE = 22 * XT / 8 + 64;	// payload stage: 4096 x 22-bit codes, + phase + slack
+
+enum : uint32_t { ERR_SCRATCH = 8 };	// exception pool too small (press_gpu_set_exception_capacity)
+
+struct ExArgs {
+	int method;
+	const uint4 *samples;		// encode in
+	uint64_t nsamples;
+	const uint64_t *offsets;	// [nreads + 1] sample offsets
+	uint64_t nreads;
+	uint8_t *out;			// encode out (16-byte aligned)
+	uint64_t out_cap;
+	uint64_t *out_offsets;		// [nreads + 1]
+	Hdr *hdr;			// aux[0] = pool entries used
+	const uint32_t *tile_start, *tile_read;
+	uint32_t *t_nex, *t_pool, *t_bits, *t_or, *t_eb, *t_pb;	// per tile
+	uint32_t *r_nex, *r_q, *r_hdr;				// per read
+	uint64_t *r_size;
+	uint2 *pool;			// (position in v = sample index - 1, value)
+	uint64_t pool_cap;
+	const uint32_t *huff_enc;	// 256 x (code | length << 24)
+};
+
+// per-halfword arithmetic shift right (ex_zd.c:383-394 on int16)
+__device__ __forceinline__ uint32_t sar16x2(uint32_t x, uint32_t q)
+{
+	const uint32_t m = (0xffffu >> q) * 0x00010001u;
+	const uint32_t t = ((x ^ 0x80008000u) >> q) & m;
+	return __vsub2(t, (0x8000u >> q) * 0x00010001u);
+}
+__device__ __forceinline__ uint32_t shl16x2(uint32_t x, uint32_t q)
+{
+	return (x << q) & (((0xffffu << q) & 0xffffu) * 0x00010001u);
+}
+
+struct ExTile {
+	uint32_t r, t, ntiles;
+	uint64_t off0, rend, k0;	// read's sample range, tile's first 16-byte group
+	uint32_t m;			// off0 & 7
+};
+
+__device__ __forceinline__ void ex_tile_info(const uint32_t *tile_start, const uint32_t *tile_read,
+					     const uint64_t *offsets, uint32_t g, ExTile &T)
+{
+	T.r = __ldg(tile_read + g);
+	const uint32_t g0 = __ldg(tile_start + T.r);
+	T.t = g - g0;
+	T.ntiles = __ldg(tile_start + T.r + 1) - g0;
+	T.off0 = __ldg(offsets + T.r);
+	T.rend = __ldg(offsets + T.r + 1);
+	T.m = (uint32_t) (T.off0 & 7);
+	T.k0 = (T.off0 >> 3) + (uint64_t) T.t * XG;
+}
+
+// number of v-indices (sample index - 1) of the read that lie before tile t
+__device__ __forceinline__ uint32_t ex_v_before(uint32_t t, uint32_t m, uint64_t n)
+{
+	const int64_t first = (int64_t) t * XT - m;	// read index of the tile's first element
+	int64_t j = first - 1;
+	if (j < 0)
+		j = 0;
+	const int64_t mm = n ? (int64_t) n - 1 : 0;
+	return (uint32_t) (j < mm ? j : mm);
+}
+
+// The thread's 16 samples of the tile as zd values (two per word), with masks:
+// valid = element inside the read, first = the read's first sample (stored apart
+// as zd0), exc = exception (value > 255, not first).  i0 = read index of element 0.
+struct ExVals {
+	uint32_t z[8];
+	uint32_t valid, first, exc;
+	int64_t i0;
+	uint32_t orv;		// OR of the valid raw samples (both halves folded)
+};
+
+__device__ __forceinline__ void ex_load_zd(const uint4 *samples, uint64_t nsamples, const ExTile &T,
+					   uint32_t q, ExVals &v)
+{
+	const int tid = threadIdx.x, lane = tid & 31;
+	const uint64_t ka = T.k0 + 2 * tid;
+	uint4 xa = load_group(samples, nsamples, ka);
+	uint4 xb = load_group(samples, nsamples, ka + 1);
+	uint32_t prev = __shfl_up_sync(0xffffffffu, xb.w >> 16, 1);
+	if (lane == 0) {
+		prev = 0;
+		if (ka > 0 && 8 * ka - 1 < nsamples)
+			prev = __ldg(reinterpret_cast<const uint16_t *>(samples) + 8 * ka - 1);
+	}
+	v.valid = group_valid(ka, T.off0, T.rend) | (group_valid(ka + 1, T.off0, T.rend) << 8);
+	{
+		// OR of the valid samples: mask out elements outside the read
+		uint32_t w[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w}, o = 0;
+#pragma unroll
+		for (int j = 0; j < 8; j++) {
+			const uint32_t mk = ((v.valid >> (2 * j)) & 1u ? 0xffffu : 0u) |
+					    ((v.valid >> (2 * j + 1)) & 1u ? 0xffff0000u : 0u);
+			o |= w[j] & mk;
+		}
+		v.orv = (o | (o >> 16)) & 0xffffu;
+	}
+	if (q) {
+		xa.x = sar16x2(xa.x, q); xa.y = sar16x2(xa.y, q); xa.z = sar16x2(xa.z, q); xa.w = sar16x2(xa.w, q);
+		xb.x = sar16x2(xb.x, q); xb.y = sar16x2(xb.y, q); xb.z = sar16x2(xb.z, q); xb.w = sar16x2(xb.w, q);
+		prev = sar16x2(prev, q) & 0xffffu;
+	}
+	v.i0 = (int64_t) (8 * ka) - (int64_t) T.off0;
+	const bool holds_first = T.t == 0 && tid == 0;
+	v.first = holds_first ? 1u << T.m : 0u;
+	uint32_t za[4], zb[4];
+	zd_group(xa, prev, holds_first ? (int) T.m : -1, za);
+	zd_group(xb, xa.w >> 16, -1, zb);
+#pragma unroll
+	for (int j = 0; j < 4; j++) {
+		v.z[j] = za[j];
+		v.z[4 + j] = zb[j];
+	}
+	const uint32_t f = flags_group(za) | (flags_group(zb) << 8);
+	v.exc = f & v.valid & ~v.first;
+}
+
+__device__ __forceinline__ uint32_t ex_elem(const ExVals &v, int e)
+{
+	return (v.z[e >> 1] >> (16 * (e & 1))) & 0xffffu;
+}
+
+// ---------------------------------------------------------------------------
+// sweep 1: counts + exception capture
+
+template <bool HUFF, bool REQ>	// REQ: second counting sweep of the ex-zd reads with q > 0
+__global__ void __launch_bounds__(NT) ex_count_kernel(const __grid_constant__ ExArgs a)
+{
+	__shared__ uint32_t s_nex, s_bits, s_or, s_pool;
+	__shared__ uint32_t s_warp[NW + 1];
+	const int tid = threadIdx.x, lane = tid & 31;
+	const uint32_t total = a.hdr->total_tiles;
+	for (uint32_t g = blockIdx.x; g < total; g += gridDim.x) {
+		ExTile T;
+		ex_tile_info(a.tile_start, a.tile_read, a.offsets, g, T);
+		uint32_t q = 0;
+		if (REQ) {
+			q = a.r_q[T.r];
+			if (q == 0)
+				continue;
+		}
+		if (tid == 0)
+			s_nex = s_bits = s_or = 0;
+		__syncthreads();
+		ExVals v;
+		ex_load_zd(a.samples, a.nsamples, T, q, v);
+		const uint32_t cnt = __popc(v.exc);
+		uint32_t bits = 0;
+		if (HUFF) {
+			const uint32_t ne = v.valid & ~v.exc & ~v.first;
+#pragma unroll
+			for (int e = 0; e < 16; e++)
+				if ((ne >> e) & 1)
+					bits += __ldg(a.huff_enc + ex_elem(v, e)) >> 24;
+		}
+		const uint32_t wn = __reduce_add_sync(0xffffffffu, cnt);
+		const uint32_t wb = HUFF ? __reduce_add_sync(0xffffffffu, bits) : 0;
+		const uint32_t wo = __reduce_or_sync(0xffffffffu, v.orv);
+		if (lane == 0) {
+			if (wn)
+				atomicAdd(&s_nex, wn);
+			if (HUFF)
+				atomicAdd(&s_bits, wb);
+			if (!REQ && wo)
+				atomicOr(&s_or, wo);
+		}
+		__syncthreads();
+		const uint32_t nex = s_nex;
+		if (nex) {	// capture, in tile order
+			uint32_t c1[1] = {cnt}, ex1[1], tot;
+			block_scan<1>(c1, ex1, tot, s_warp);
+			if (tid == 0)
+				s_pool = (uint32_t) atomicAdd((unsigned long long *) &a.hdr->aux[0],
+							      (unsigned long long) nex);
+			__syncthreads();
+			const uint64_t base = s_pool;
+			if (base + nex <= a.pool_cap) {
+				uint2 *p = a.pool + base + ex1[0];
+				for (uint32_t m = v.exc; m; m &= m - 1) {
+					const int e = __ffs(m) - 1;
+					*p++ = make_uint2((uint32_t) (v.i0 + e - 1), ex_elem(v, e));
+				}
+			} else if (tid == 0) {
+				atomicOr(&a.hdr->error, ERR_SCRATCH);
+			}
+		}
+		if (tid == 0) {
+			a.t_nex[g] = nex;
+			a.t_pool[g] = nex ? s_pool : 0;
+			if (HUFF)
+				a.t_bits[g] = s_bits;
+			if (!REQ)
+				a.t_or[g] = s_or;
+		}
+		__syncthreads();
+	}
+}
+
+// ex-zd: q of every read from the OR of its samples (ex_zd.c:358-381).  One warp per read.
+__global__ void __launch_bounds__(NT) ex_readq_kernel(const __grid_constant__ ExArgs a)
+{
+	const uint64_t r = ((uint64_t) blockIdx.x * NT + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (r >= a.nreads)
+		return;
+	const uint32_t g0 = a.tile_start[r], g1 = a.tile_start[r + 1];
+	uint32_t o = 0;
+	for (uint32_t g = g0 + lane; g < g1; g += 32)
+		o |= a.t_or[g];
+	o = __reduce_or_sync(0xffffffffu, o);
+	if (lane == 0)
+		a.r_q[r] = __ffs(o | 32u) - 1;	// a zero sample never lowers q; cap 5
+}
+
+// ---------------------------------------------------------------------------
+// exception lists of a read, addressed by their index k inside the read
+
+struct ExList {
+	const uint32_t *t_eb, *t_pool;
+	const uint2 *pool;
+	uint32_t g0, ntiles;
+	__device__ __forceinline__ uint2 at(uint32_t k) const
+	{
+		// last tile whose exclusive exception prefix is <= k
+		uint32_t lo = 0, hi = ntiles;	// invariant: eb[lo] <= k, eb[hi] > k (hi == ntiles: virtual)
+		while (hi - lo > 1) {
+			const uint32_t mid = (lo + hi) >> 1;
+			if (t_eb[g0 + mid] <= k)
+				lo = mid;
+			else
+				hi = mid;
+		}
+		return pool[(uint64_t) t_pool[g0 + lo] + (k - t_eb[g0 + lo])];
+	}
+};
+
+// streamvbyte coding of `cnt` values by one warp: KB = 2 classical svb32
+// (streamvbyte_encode.c:11-59), KB = 1 svb16 without zd (svb16/encode_scalar.hpp:14-62).
+// Returns the byte length; writes when WRITE.
+template <int KB, bool WRITE, class F>
+__device__ __forceinline__ uint32_t warp_svb_list(F value, uint32_t cnt, uint8_t *dst, int lane)
+{
+	const uint32_t nkeys = KB == 2 ? (cnt + 3) / 4 : (cnt + 7) / 8;
+	uint32_t run = 0;
+	for (uint32_t k0 = 0; k0 < cnt; k0 += 32) {
+		const uint32_t k = k0 + lane;
+		const bool act = k < cnt;
+		const uint32_t val = act ? value(k) : 0u;
+		uint32_t len = 0;
+		if (act)
+			len = KB == 2 ? 1u + (val >= 256u) + (val >= 65536u) + (val >= (1u << 24))
+				      : 1u + ((val & 0xffffu) >= 256u);
+		const uint32_t inc = warp_inc_scan(len, lane);
+		if (WRITE) {
+			uint8_t *p = dst + nkeys + run + inc - len;
+			for (uint32_t b = 0; b < len; b++)
+				p[b] = (uint8_t) (val >> (8 * b));
+			uint32_t kk = act ? (len - 1) << (KB == 2 ? 2 * (lane & 3) : (lane & 7)) : 0u;
+			kk |= __shfl_xor_sync(0xffffffffu, kk, 1);
+			kk |= __shfl_xor_sync(0xffffffffu, kk, 2);
+			if (KB == 1)
+				kk |= __shfl_xor_sync(0xffffffffu, kk, 4);
+			if (act && (lane & (KB == 2 ? 3 : 7)) == 0)
+				dst[KB == 2 ? k >> 2 : k >> 3] = (uint8_t) kk;
+		}
+		run += __shfl_sync(0xffffffffu, inc, 31);
+	}
+	return nkeys + run;
+}
+
+__device__ __forceinline__ void put_le(uint8_t *p, uint64_t v, int nbytes)
+{
+	for (int b = 0; b < nbytes; b++)
+		p[b] = (uint8_t) (v >> (8 * b));
+}
+
+// header of one read past the fixed fields; returns its length.  One warp.
+template <bool WRITE>
+__device__ __forceinline__ uint32_t ex_lists(int method, const ExList &L, uint32_t nex, uint8_t *dst, int lane)
+{
+	auto gap = [&](uint32_t k) {
+		const uint32_t p = L.at(k).x;
+		return k ? p - L.at(k - 1).x - 1 : p;	// trans.c:129-149
+	};
+	auto val256 = [&](uint32_t k) { return L.at(k).y - 256u; };
+	if (method == PRESS_GPU_VBE21_ZD || method == PRESS_GPU_SHUFF_VBE21_ZD) {
+		if (WRITE)
+			for (uint32_t k = lane; k < nex; k += 32) {
+				const uint2 e = L.at(k);
+				put_le(dst + 4 * (uint64_t) k, e.x, 4);
+				put_le(dst + 4 * (uint64_t) nex + 2 * (uint64_t) k, e.y, 2);
+			}
+		return 6 * nex;
+	}
+	if (nex == 0)
+		return 0;
+	const bool ex = method == PRESS_GPU_EX_ZD;
+	if (nex == 1) {		// press.c:3269-3274 (u32, i16) / ex_zd.c:146-153 (u32, u32)
+		if (WRITE && lane == 0) {
+			const uint2 e = L.at(0);
+			put_le(dst, e.x, 4);
+			put_le(dst + 4, e.y - 256u, ex ? 4 : 2);
+		}
+		return ex ? 8 : 6;
+	}
+	const uint32_t lp = warp_svb_list<2, WRITE>(gap, nex, dst + 4, lane);
+	if (WRITE && lane == 0)
+		put_le(dst, lp, 4);
+	uint8_t *d2 = dst + 4 + lp;
+	const uint32_t lv = ex ? warp_svb_list<2, WRITE>(val256, nex, d2 + 4, lane)
+			       : warp_svb_list<1, WRITE>(val256, nex, d2 + 4, lane);
+	if (WRITE && lane == 0)
+		put_le(d2, lv, 4);
+	return 8 + lp + lv;
+}
+
+__device__ __forceinline__ uint32_t ex_fixed_bytes(int method)
+{
+	return method == PRESS_GPU_EX_ZD ? 16u : 6u;	// [ver][n u64][q] + [zd0 u16][nex u32]
+}
+
+// per-read sizes and per-tile prefixes.  One warp per read.
+__global__ void __launch_bounds__(NT) ex_size_kernel(const __grid_constant__ ExArgs a)
+{
+	const uint64_t r = ((uint64_t) blockIdx.x * NT + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (r >= a.nreads)
+		return;
+	const bool huff = a.method == PRESS_GPU_SHUFF_VBE21_ZD;
+	const uint32_t g0 = a.tile_start[r], nt = a.tile_start[r + 1] - g0;
+	const uint64_t off0 = a.offsets[r], n = a.offsets[r + 1] - off0;
+	const uint32_t m = (uint32_t) (off0 & 7);
+	uint32_t eb = 0;
+	uint64_t bb = 0;
+	for (uint32_t t0 = 0; t0 < nt; t0 += 32) {
+		const uint32_t t = t0 + lane;
+		const uint32_t nx = t < nt ? a.t_nex[g0 + t] : 0u;
+		const uint32_t bt = huff && t < nt ? a.t_bits[g0 + t] : 0u;
+		const uint32_t ie = warp_inc_scan(nx, lane);
+		uint64_t ib = bt;
+		if (huff) {
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) {
+				const uint64_t y = __shfl_up_sync(0xffffffffu, ib, o);
+				if (lane >= o)
+					ib += y;
+			}
+		}
+		if (t < nt) {
+			const uint32_t e0 = eb + ie - nx;
+			a.t_eb[g0 + t] = e0;
+			a.t_pb[g0 + t] = huff ? (uint32_t) (bb + ib - bt) : ex_v_before(t, m, n) - e0;
+		}
+		eb += __shfl_sync(0xffffffffu, ie, 31);
+		bb += __shfl_sync(0xffffffffu, ib, 31);
+	}
+	__syncwarp();
+	const uint32_t nex = eb;
+	uint32_t hdr = X_FAIL;
+	uint64_t size = 0;
+	if (n > 0 && !(a.hdr->error & ERR_SCRATCH)) {
+		const ExList L = {a.t_eb, a.t_pool, a.pool, g0, nt};
+		hdr = ex_fixed_bytes(a.method) + ex_lists<false>(a.method, L, nex, nullptr, lane);
+		const uint64_t mm = n - 1 - nex;
+		if (huff) {
+			hdr += 4;	// [count u32 BE], huffman.c:1199-1203
+			size = hdr + (bb + 7) / 8;
+			if (bb >> 32)
+				hdr = X_FAIL, size = 0;	// (cannot happen: 22 bits x 2^32 samples)
+		} else {
+			size = hdr + mm;
+		}
+		if (a.method == PRESS_GPU_EX_ZD && size > 2 * n + 1024) {	// ex_zd.c:411 scratch cap
+			if (lane == 0)
+				atomicOr(&a.hdr->error, ERR_EXZD_CAP);
+			hdr = X_FAIL;
+			size = 0;
+		}
+	}
+	if (lane == 0) {
+		a.r_nex[r] = nex;
+		a.r_hdr[r] = hdr;
+		a.r_size[r] = size;
+	}
+}
+
+// exclusive scan of the stream sizes -> out_offsets.  One CTA of 1024 threads.
+__global__ void __launch_bounds__(1024) ex_offsets_kernel(const uint64_t *size, uint64_t nreads,
+							  uint64_t *out_offsets, uint64_t out_cap, Hdr *hdr)
+{
+	__shared__ uint64_t s_w[33];
+	__shared__ uint64_t s_carry;
+	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	if (tid == 0)
+		s_carry = 0;
+	__syncthreads();
+	constexpr int IT = 4;
+	for (uint64_t base = 0; base < nreads; base += 1024 * IT) {
+		const uint64_t r0 = base + (uint64_t) tid * IT;
+		uint64_t v[IT], s = 0;
+#pragma unroll
+		for (int i = 0; i < IT; i++) {
+			v[i] = r0 + i < nreads ? size[r0 + i] : 0;
+			s += v[i];
+		}
+		uint64_t inc = s;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			const uint64_t y = __shfl_up_sync(0xffffffffu, inc, o);
+			if (lane >= o)
+				inc += y;
+		}
+		if (lane == 31)
+			s_w[warp] = inc;
+		__syncthreads();
+		if (warp == 0) {
+			uint64_t x = s_w[lane], o0 = x;
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) {
+				const uint64_t y = __shfl_up_sync(0xffffffffu, x, o);
+				if (lane >= o)
+					x += y;
+			}
+			s_w[lane] = x - o0;
+			if (lane == 31)
+				s_w[32] = x;
+		}
+		__syncthreads();
+		uint64_t e = s_carry + s_w[warp] + inc - s;
+#pragma unroll
+		for (int i = 0; i < IT; i++) {
+			if (r0 + i < nreads)
+				out_offsets[r0 + i] = e;
+			e += v[i];
+		}
+		__syncthreads();
+		if (tid == 0)
+			s_carry += s_w[32];
+		__syncthreads();
+	}
+	if (tid == 0) {
+		out_offsets[nreads] = s_carry;
+		if (s_carry > out_cap)
+			atomicOr(&hdr->error, ERR_CAPACITY);
+	}
+}
+
+// header of every read at its final place.  One warp per read.
+__global__ void __launch_bounds__(NT) ex_header_kernel(const __grid_constant__ ExArgs a)
+{
+	const uint64_t r = ((uint64_t) blockIdx.x * NT + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (r >= a.nreads || (a.hdr->error & (ERR_CAPACITY | ERR_SCRATCH)))
+		return;
+	const uint32_t hdr = a.r_hdr[r];
+	if (hdr == X_FAIL)
+		return;
+	const uint32_t g0 = a.tile_start[r], nt = a.tile_start[r + 1] - g0;
+	const uint64_t off0 = a.offsets[r], n = a.offsets[r + 1] - off0;
+	const uint32_t nex = a.r_nex[r];
+	const uint32_t q = a.method == PRESS_GPU_EX_ZD ? a.r_q[r] : 0u;
+	uint8_t *dst = a.out + a.out_offsets[r];
+	if (lane == 0) {
+		const int16_t x0 = reinterpret_cast<const int16_t *>(a.samples)[off0];
+		const int16_t s0 = (int16_t) (x0 >> q);
+		const uint16_t zd0 = (uint16_t) ((uint16_t) (s0 << 1) ^ (uint16_t) (s0 >> 15));	// trans.c:75-78
+		uint8_t *p = dst;
+		if (a.method == PRESS_GPU_EX_ZD) {
+			*p++ = 0;		// ex_zd.c:420-423
+			put_le(p, n, 8);	// ex_zd.c:425-428
+			p += 8;
+			*p++ = (uint8_t) q;	// ex_zd.c:436-439
+		}
+		put_le(p, zd0, 2);
+		put_le(p + 2, nex, 4);
+	}
+	const ExList L = {a.t_eb, a.t_pool, a.pool, g0, nt};
+	const uint32_t fx = ex_fixed_bytes(a.method);
+	const uint32_t ll = ex_lists<true>(a.method, L, nex, dst + fx, lane);
+	if (a.method == PRESS_GPU_SHUFF_VBE21_ZD) {
+		const uint32_t cnt = (uint32_t) (n - 1 - nex);
+		uint8_t *p = dst + fx + ll;
+		if (lane < 4)
+			p[lane] = (uint8_t) (cnt >> (8 * (3 - lane)));	// htonl, huffman.c:1199
+		// bytes shared by two tiles' bit ranges are OR-ed in by the emit sweep: clear them
+		uint8_t *bs = p + 4;
+		for (uint32_t t = 1 + lane; t < nt; t += 32) {
+			const uint32_t b = a.t_pb[g0 + t];
+			if (b & 7)
+				bs[b >> 3] = 0;
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------
+// sweep 2: payload
+
+// Copy `len` bytes staged at stage[0 .. len) (8-byte aligned base, 24 bytes of
+// readable slack) to global dst (any alignment) with aligned 16-byte stores.  One CTA.
+__device__ __forceinline__ void block_copy_out(const uint8_t *stage, uint8_t *dst, uint32_t len)
+{
+	const uint32_t a = (uint32_t) (reinterpret_cast<uintptr_t>(dst) & 15);
+	uint8_t *gb = dst - a;
+	const uint32_t end = a + len;
+	const uint32_t nw = (end + 15) >> 4;
+	const uint64_t *s64 = reinterpret_cast<const uint64_t *>(stage);
+	for (uint32_t w = threadIdx.x; w < nw; w += NT) {
+		const uint32_t lo = w << 4, hi = lo + 16;
+		if (lo >= a && hi <= end) {
+			const uint32_t o = lo - a, qd = o >> 3, sh = (o & 7) * 8;
+			const uint64_t x0 = s64[qd], x1 = s64[qd + 1], x2 = s64[qd + 2];
+			uint2 l2, h2;
+			uint64_t l = x0, h = x1;
+			if (sh) {
+				l = (x0 >> sh) | (x1 << (64 - sh));
+				h = (x1 >> sh) | (x2 << (64 - sh));
+			}
+			l2 = make_uint2((uint32_t) l, (uint32_t) (l >> 32));
+			h2 = make_uint2((uint32_t) h, (uint32_t) (h >> 32));
+			*reinterpret_cast<uint4 *>(gb + lo) = make_uint4(l2.x, l2.y, h2.x, h2.y);
+		} else {
+			const uint32_t b0 = lo < a ? a : lo, b1 = hi > end ? end : hi;
+			for (uint32_t b = b0; b < b1; b++)
+				gb[b] = stage[b - a];
+		}
+	}
+}
+
+template <bool HUFF>
+__global__ void __launch_bounds__(NT) ex_emit_kernel(const __grid_constant__ ExArgs a)
+{
+	__shared__ __align__(16) uint8_t s_stage[X_STAGE];
+	__shared__ uint32_t s_warp[NW + 1];
+	__shared__ uint32_t s_lut[HUFF ? 256 : 1];
+	const int tid = threadIdx.x;
+	if (a.hdr->error & (ERR_CAPACITY | ERR_SCRATCH))
+		return;
+	if (HUFF) {
+		s_lut[tid] = a.huff_enc[tid];
+		__syncthreads();
+	}
+	const uint32_t total = a.hdr->total_tiles;
+	for (uint32_t g = blockIdx.x; g < total; g += gridDim.x) {
+		ExTile T;
+		ex_tile_info(a.tile_start, a.tile_read, a.offsets, g, T);
+		const uint32_t hdr = a.r_hdr[T.r];
+		if (hdr == X_FAIL)
+			continue;
+		const uint32_t q = a.method == PRESS_GPU_EX_ZD ? a.r_q[T.r] : 0u;
+		ExVals v;
+		ex_load_zd(a.samples, a.nsamples, T, q, v);
+		const uint32_t ne = v.valid & ~v.exc & ~v.first;
+		uint8_t *pay = a.out + a.out_offsets[T.r] + hdr;	// first payload byte of the read
+		if (!HUFF) {
+			uint32_t c1[1] = {(uint32_t) __popc(ne)}, ex1[1], tot;
+			block_scan<1>(c1, ex1, tot, s_warp);
+			if (ne == 0xffffu && (ex1[0] & 7) == 0) {
+				uint2 *p = reinterpret_cast<uint2 *>(s_stage + ex1[0]);
+				p[0] = make_uint2(__byte_perm(v.z[0], v.z[1], 0x6420), __byte_perm(v.z[2], v.z[3], 0x6420));
+				p[1] = make_uint2(__byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420));
+			} else {
+				uint8_t *p = s_stage + ex1[0];
+				for (uint32_t mk = ne; mk; mk &= mk - 1)
+					*p++ = (uint8_t) ex_elem(v, __ffs(mk) - 1);
+			}
+			__syncthreads();
+			block_copy_out(s_stage, pay + a.t_pb[g], tot);
+		} else {
+			// code lengths -> bit position of every symbol (huffman.c:848-887: codes back
+			// to back, first bit of the stream in bit 0 of byte 0)
+			uint32_t bits = 0;
+#pragma unroll
+			for (int e = 0; e < 16; e++)
+				if ((ne >> e) & 1)
+					bits += s_lut[ex_elem(v, e)] >> 24;
+			uint32_t c1[1] = {bits}, ex1[1], tot;
+			block_scan<1>(c1, ex1, tot, s_warp);
+			// the stage mirrors global memory from the 16-byte word holding the tile's first bit
+			const uint64_t G = 8 * (uint64_t) (pay - a.out) + a.t_pb[g];
+			const uint32_t s0 = (uint32_t) (G & 127);
+			const uint32_t nwords = (s0 + tot + 31) >> 5;
+			uint32_t *sw = reinterpret_cast<uint32_t *>(s_stage);
+			for (uint32_t w = tid; w < nwords + 4; w += NT)
+				sw[w] = 0;
+			__syncthreads();
+			uint32_t pos = s0 + ex1[0];
+			uint64_t acc = 0;	// bits not yet written, starting at bit (pos & ~31)
+			uint32_t nacc = pos & 31;	// bits of acc in use (the low `pos & 31` are other threads')
+			uint32_t word = pos >> 5;
+#pragma unroll
+			for (int e = 0; e < 16; e++) {
+				if ((ne >> e) & 1) {
+					const uint32_t c = s_lut[ex_elem(v, e)];
+					acc |= (uint64_t) (c & 0xffffffu) << nacc;
+					nacc += c >> 24;
+					if (nacc >= 32) {
+						atomicOr(sw + word, (uint32_t) acc);
+						acc >>= 32;
+						nacc -= 32;
+						word++;
+					}
+				}
+			}
+			if (acc)
+				atomicOr(sw + word, (uint32_t) acc);
+			__syncthreads();
+			if (tot) {
+				uint8_t *gb = a.out + ((G >> 7) << 4);	// global address of stage byte 0
+				const uint32_t e0 = s0 + tot;		// stage bit range [s0, e0)
+				const uint32_t fb = (s0 + 7) >> 3, lb = e0 >> 3;	// wholly owned bytes [fb, lb)
+				if (lb > fb) {
+					const uint32_t w0 = (fb + 15) >> 4, w1 = lb >> 4;	// wholly owned 16-byte words
+					if (w1 > w0) {
+						for (uint32_t w = w0 + tid; w < w1; w += NT)
+							reinterpret_cast<uint4 *>(gb)[w] = reinterpret_cast<const uint4 *>(s_stage)[w];
+						for (uint32_t b = fb + tid; b < (w0 << 4); b += NT)
+							gb[b] = s_stage[b];
+						for (uint32_t b = (w1 << 4) + tid; b < lb; b += NT)
+							gb[b] = s_stage[b];
+					} else {
+						for (uint32_t b = fb + tid; b < lb; b += NT)
+							gb[b] = s_stage[b];
+					}
+				}
+				if (tid == 0) {
+					// partial bytes: shared with the neighbouring tiles, OR-ed into bytes the
+					// header kernel cleared; the stream's last byte belongs to the last tile
+					const bool head = (s0 & 7) != 0, tail = (e0 & 7) != 0;
+					const uint32_t hb = s0 >> 3, tb = e0 >> 3;
+					auto or_byte = [&](uint32_t b) {
+						uint8_t *p = gb + b;
+						const uintptr_t al = reinterpret_cast<uintptr_t>(p) & 3;
+						atomicOr(reinterpret_cast<uint32_t *>(p - al), (uint32_t) s_stage[b] << (8 * al));
+					};
+					if (head)
+						or_byte(hb);
+					if (tail && !(head && tb == hb)) {
+						if (T.t + 1 == T.ntiles)
+							gb[tb] = s_stage[tb];
+						else
+							or_byte(tb);
+					}
+				}
+			}
+		}
+		__syncthreads();
+	}
+}
+
+}  // namespace pg

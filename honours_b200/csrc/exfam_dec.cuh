@@ -1,0 +1,573 @@
+// exfam_dec.cuh -- decode of the exception-coded methods (see exfam.cuh for the
+// formats) and of the static Huffman payload.
+//
+//   ex_parse   (read)  header -> n, q, zd0, payload position; both exception lists
+//                      decoded into a pool (sorted positions, values)
+//   huff_decode(read)  SHUFF only: bitstream -> one-byte symbols in a scratch payload
+//                      (self-synchronising parallel decode, see below)
+//   ex_sum     (tile)  payload + exceptions -> sum of the tile's deltas (mod 2^16)
+//   ex_decode  (tile)  payload + exceptions -> unzigzag -> running sum carried in from
+//                      the sums of the read's earlier tiles -> << q -> samples
+//
+// The inverse delta (trans.c:260-270, a serial running sum in the reference) is the
+// only loop-carried value; it costs one extra read of the 1-byte payload.
+#pragma once
+
+#include "exfam.cuh"
+
+namespace pg {
+
+struct ExDecArgs {
+	int method;
+	const uint8_t *in;		// container, 16-byte aligned
+	uint64_t in_bytes;
+	const uint64_t *in_offsets;	// [nreads + 1]
+	const uint64_t *offsets;	// [nreads + 1] sample offsets of the output
+	uint64_t nreads;
+	int16_t *samples_out;		// 16-byte aligned
+	Hdr *hdr;			// aux[0] = pool entries used, ticket = next read (huff_decode)
+	const uint32_t *tile_start, *tile_read;
+	uint32_t *t_sum;
+	uint32_t *r_nex, *r_q, *r_zd0, *r_pool;
+	uint64_t *r_pay;		// byte offset of the payload / bitstream in `in`; SENTINEL: bad read
+	uint2 *pool;
+	uint64_t pool_cap;
+	uint8_t *paybuf;		// SHUFF: symbols of read r at paybuf + offsets[r]
+	const uint16_t *huff_dec;	// 2048 x (length << 8 | symbol), 0 = longer than 11 bits
+	const int16_t *huff_tree;	// child[node][bit]: > 0 node, <= 0 leaf -symbol... see huff.cuh
+};
+
+__device__ __forceinline__ uint64_t get_le(const uint8_t *p, int nbytes)
+{
+	uint64_t v = 0;
+	for (int b = 0; b < nbytes; b++)
+		v |= (uint64_t) p[b] << (8 * b);
+	return v;
+}
+
+// streamvbyte list decode by one warp (streamvbyte_decode.c:16-58 / svb16 decode_scalar.hpp:31-71);
+// sink(k, active, value) is called by all lanes for every chunk of 32 values.
+// Returns the bytes consumed; sets bad when the list does not fit in `avail`.
+template <int KB, class F>
+__device__ __forceinline__ uint32_t warp_svb_decode(const uint8_t *src, uint64_t avail, uint32_t cnt,
+						    F sink, int lane, bool &bad)
+{
+	const uint32_t nkeys = KB == 2 ? (cnt + 3) / 4 : (cnt + 7) / 8;
+	if (nkeys > avail) {
+		bad = true;
+		return 0;
+	}
+	uint64_t run = nkeys;
+	for (uint32_t k0 = 0; k0 < cnt; k0 += 32) {
+		const uint32_t k = k0 + lane;
+		const bool act = k < cnt;
+		uint32_t len = 0;
+		if (act)
+			len = KB == 2 ? ((src[k >> 2] >> (2 * (k & 3))) & 3u) + 1u : ((src[k >> 3] >> (k & 7)) & 1u) + 1u;
+		const uint32_t inc = warp_inc_scan(len, lane);
+		const uint64_t o = run + inc - len;
+		const bool over = act && o + len > avail;
+		if (__any_sync(0xffffffffu, over)) {
+			bad = true;
+			return 0;
+		}
+		uint32_t val = 0;
+		for (uint32_t b = 0; b < len; b++)
+			val |= (uint32_t) src[o + b] << (8 * b);
+		sink(k, act, val);
+		run += __shfl_sync(0xffffffffu, inc, 31);
+	}
+	return (uint32_t) run;
+}
+
+__global__ void __launch_bounds__(NT) ex_parse_kernel(const __grid_constant__ ExDecArgs a)
+{
+	const uint64_t r = ((uint64_t) blockIdx.x * NT + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (r >= a.nreads)
+		return;
+	const uint64_t n = a.offsets[r + 1] - a.offsets[r];
+	const uint64_t s0 = a.in_offsets[r], s1 = a.in_offsets[r + 1];
+	const bool exz = a.method == PRESS_GPU_EX_ZD, vbe = a.method == PRESS_GPU_VBE21_ZD ||
+							    a.method == PRESS_GPU_SHUFF_VBE21_ZD;
+	const uint32_t fx = ex_fixed_bytes(a.method);
+	if (n == 0) {	// no stream exists for an empty read (the reference underflows, press.c:3426)
+		if (lane == 0) {
+			a.r_pay[r] = SENTINEL;
+			a.r_nex[r] = 0;
+		}
+		return;
+	}
+	bool bad = s1 < s0 || s1 > a.in_bytes || s1 - s0 < fx || n > 0xffffffffull;
+	uint32_t q = 0, zd0 = 0, nex = 0;
+	const uint64_t m = n - 1;
+	if (!bad) {
+		const uint8_t *p = a.in + s0;
+		if (exz) {	// ex_zd.c:459-515
+			bad = p[0] != 0 || get_le(p + 1, 8) != n || p[9] > 5;
+			q = p[9];
+			p += 10;
+		}
+		zd0 = (uint32_t) get_le(p, 2);
+		nex = (uint32_t) get_le(p + 2, 4);
+		bad = bad || nex > m;
+	}
+	uint64_t off = s0 + fx;
+	uint64_t pbase = 0;
+	if (!bad && nex) {
+		if (lane == 0)
+			pbase = atomicAdd((unsigned long long *) &a.hdr->aux[0], (unsigned long long) nex);
+		pbase = __shfl_sync(0xffffffffu, pbase, 0);
+		if (pbase + nex > a.pool_cap) {
+			if (lane == 0)
+				atomicOr(&a.hdr->error, ERR_SCRATCH);
+			bad = true;
+		}
+	}
+	if (!bad && nex) {
+		uint2 *pl = a.pool + pbase;
+		bool order_bad = false;
+		if (vbe) {	// press.c:2738-2748: raw lists
+			if (off + 6ull * nex > s1) {
+				bad = true;
+			} else {
+				const uint8_t *pp = a.in + off, *pv = pp + 4ull * nex;
+				for (uint32_t k = lane; k < nex; k += 32) {
+					const uint32_t pos = (uint32_t) get_le(pp + 4ull * k, 4);
+					const uint32_t prv = k ? (uint32_t) get_le(pp + 4ull * (k - 1), 4) : 0u;
+					order_bad |= pos >= m || (k && pos <= prv);
+					pl[k] = make_uint2(pos, (uint32_t) get_le(pv + 2ull * k, 2));
+				}
+				off += 6ull * nex;
+			}
+		} else if (nex == 1) {	// press.c:3323-3330 / ex_zd.c:264-272
+			const uint32_t vb = exz ? 4 : 2;
+			if (off + 4 + vb > s1) {
+				bad = true;
+			} else {
+				if (lane == 0) {
+					const uint32_t pos = (uint32_t) get_le(a.in + off, 4);
+					order_bad = pos >= m;
+					pl[0] = make_uint2(pos, ((uint32_t) get_le(a.in + off + 4, vb) + 256u) & 0xffffu);
+				}
+				off += 4 + vb;
+			}
+		} else {
+			// positions: svb32 gaps, p[k] = p[k - 1] + gap + 1 (trans.c:186-197)
+			uint64_t carry = 0;
+			auto pos_sink = [&](uint32_t k, bool act, uint32_t val) {
+				uint64_t inc = act ? (uint64_t) val + 1 : 0;
+#pragma unroll
+				for (int o = 1; o < 32; o <<= 1) {
+					const uint64_t y = __shfl_up_sync(0xffffffffu, inc, o);
+					if (lane >= o)
+						inc += y;
+				}
+				const uint64_t pos = carry + inc - 1;
+				if (act) {
+					order_bad |= pos >= m;
+					pl[k].x = (uint32_t) pos;
+				}
+				carry += __shfl_sync(0xffffffffu, inc, 31);
+			};
+			auto val_sink = [&](uint32_t k, bool act, uint32_t val) {
+				if (act)
+					pl[k].y = (val + 256u) & 0xffffu;	// stored into uint16: wraps (press.c:3336)
+			};
+			for (int pass = 0; pass < 2 && !bad; pass++) {
+				if (off + 4 > s1) {
+					bad = true;
+					break;
+				}
+				const uint32_t len = (uint32_t) get_le(a.in + off, 4);
+				off += 4;
+				if (off + len > s1) {
+					bad = true;
+					break;
+				}
+				uint32_t used;
+				if (pass == 0)
+					used = warp_svb_decode<2>(a.in + off, len, nex, pos_sink, lane, bad);
+				else if (exz)
+					used = warp_svb_decode<2>(a.in + off, len, nex, val_sink, lane, bad);
+				else
+					used = warp_svb_decode<1>(a.in + off, len, nex, val_sink, lane, bad);
+				if (exz && used != len)	// ex_zd.c:222-232, 252-262
+					bad = true;
+				off += len;
+			}
+		}
+		bad = bad || __any_sync(0xffffffffu, order_bad);
+	}
+	if (!bad) {
+		if (a.method == PRESS_GPU_SHUFF_VBE21_ZD) {
+			// [count u32 BE] + bitstream; huffman.c:696-711 memread fails when no byte follows
+			bad = off + 4 >= s1;
+			if (!bad) {
+				const uint8_t *p = a.in + off;
+				const uint32_t cnt = ((uint32_t) p[0] << 24) | ((uint32_t) p[1] << 16) | ((uint32_t) p[2] << 8) | p[3];
+				bad = cnt != m - nex;
+				off += 4;
+			}
+		} else {
+			bad = s1 - off != m - nex;
+		}
+	}
+	if (lane == 0) {
+		if (bad)
+			atomicOr(&a.hdr->error, ERR_MALFORMED);
+		a.r_pay[r] = bad ? SENTINEL : off;
+		a.r_nex[r] = nex;
+		a.r_q[r] = q;
+		a.r_zd0[r] = zd0;
+		a.r_pool[r] = (uint32_t) pbase;
+	}
+}
+
+// ---------------------------------------------------------------------------
+// static Huffman decode (huffman.c:1219-1265: walk the tree bit by bit from bit 0
+// of every byte until `count` symbols are out).
+//
+// One CTA per read (reads handed out by an atomic ticket), 4 KB of bitstream per
+// step, one 128-bit sub-block per thread.  A thread does not know where the first
+// code of its sub-block starts, so it guesses "at bit 0", decodes, and hands the
+// position where it left its sub-block to the next thread; a thread whose entry
+// point changed decodes again.  Prefix codes re-synchronise after a few symbols,
+// so two or three rounds settle all 256 sub-blocks; the loop runs until nothing
+// changes, which makes the result exact whatever the data (worst case: serial).
+// The entry point into the next 4 KB step is carried by the CTA itself.
+
+constexpr int HD_SUB = 128;			// bits per sub-block
+constexpr int HD_CHUNK = NT * HD_SUB / 8;	// bytes per step
+
+// decode codes starting at stage bit `pos` until pos >= end; returns the new pos,
+// adds the symbols seen to cnt; when dst != nullptr stores symbol i at dst[i] for i < lim.
+__device__ __forceinline__ uint32_t hd_run(const uint32_t *sw, const uint16_t *lut, const int16_t *tree,
+					   uint32_t pos, uint32_t end, uint32_t &cnt, uint8_t *dst, int64_t lim)
+{
+	uint32_t c = 0;
+	while (pos < end) {
+		const uint32_t w = __funnelshift_r(sw[pos >> 5], sw[(pos >> 5) + 1], pos & 31);
+		uint32_t e = lut[w & 2047u];
+		if (e == 0) {	// code longer than 11 bits: walk the tree
+			int node = 0;
+			uint32_t l = 0;
+			for (;;) {
+				const int nx = tree[2 * node + ((w >> l) & 1u)];
+				l++;
+				if (nx <= 0) {
+					e = (l << 8) | (uint32_t) (-nx);
+					break;
+				}
+				node = nx;
+			}
+		}
+		if (dst && (int64_t) c < lim)
+			dst[c] = (uint8_t) e;
+		c++;
+		pos += e >> 8;
+	}
+	cnt = c;
+	return pos;
+}
+
+__global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__ ExDecArgs a)
+{
+	__shared__ uint32_t s_w[HD_CHUNK / 4 + 8];
+	__shared__ uint16_t s_lut[2048];
+	__shared__ uint32_t s_exit[NT];
+	__shared__ uint32_t s_warp[NW + 1];
+	__shared__ uint32_t s_read;
+	const int tid = threadIdx.x;
+	for (int i = tid; i < 2048; i += NT)
+		s_lut[i] = a.huff_dec[i];
+	for (;;) {
+		__syncthreads();
+		if (tid == 0)
+			s_read = atomicAdd(&a.hdr->ticket, 1u);
+		__syncthreads();
+		const uint64_t r = s_read;
+		if (r >= a.nreads)
+			break;
+		const uint64_t bs0 = a.r_pay[r];
+		if (bs0 == SENTINEL)
+			continue;
+		const uint64_t off0 = a.offsets[r], n = a.offsets[r + 1] - off0;
+		const uint64_t nbytes = a.in_offsets[r + 1] - bs0;
+		const int64_t count = (int64_t) (n - 1 - a.r_nex[r]);
+		uint8_t *dst = a.paybuf + off0;
+		const uint8_t *src = a.in + bs0, *limit = a.in + a.in_bytes;
+		uint32_t entry = 0;	// bit offset of the first code inside the step
+		int64_t done = 0;	// symbols out so far
+		for (uint64_t cb = 0; cb < nbytes && done < count; cb += HD_CHUNK) {
+			// stage HD_CHUNK + 32 bytes of the bitstream from byte cb, zero filled past its end
+			const uint64_t left = nbytes - cb;
+			{
+				const uint8_t *s = src + cb;
+				const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(s) & 3);
+				const uint32_t *gw = reinterpret_cast<const uint32_t *>(s - al);
+				for (uint32_t w = tid; w < HD_CHUNK / 4 + 8; w += NT) {
+					uint32_t v = 0;
+					if (4ull * w < left) {
+						const uint8_t *p0 = reinterpret_cast<const uint8_t *>(gw + w);
+						if (4ull * w + 8 <= left && p0 >= a.in && p0 + 8 <= limit) {
+							v = __funnelshift_r(__ldg(gw + w), __ldg(gw + w + 1), 8 * al);
+						} else {
+							for (uint32_t b = 0; b < 4 && 4ull * w + b < left; b++)
+								v |= (uint32_t) s[4ull * w + b] << (8 * b);
+						}
+					}
+					s_w[w] = v;
+				}
+			}
+			__syncthreads();
+			const uint32_t cbits = left < HD_CHUNK ? (uint32_t) left * 8 : HD_CHUNK * 8;
+			const uint32_t nsub = (cbits + HD_SUB - 1) / HD_SUB;
+			const bool act = (uint32_t) tid < nsub;
+			const uint32_t lo = tid * HD_SUB, hi = lo + HD_SUB;
+			uint32_t cur = tid == 0 ? entry : 0u, cnt = 0, ex = 0;
+			if (act)
+				ex = hd_run(s_w, s_lut, a.huff_tree, lo + cur, hi, cnt, nullptr, 0) - hi;
+			s_exit[tid] = ex;
+			for (;;) {
+				__syncthreads();
+				const uint32_t e = tid ? s_exit[tid - 1] : entry;
+				const bool ch = act && e != cur;
+				if (ch) {
+					cur = e;
+					// an entry point past the sub-block: no code starts here
+					if (lo + cur >= hi) {
+						cnt = 0;
+						ex = lo + cur - hi;
+					} else {
+						ex = hd_run(s_w, s_lut, a.huff_tree, lo + cur, hi, cnt, nullptr, 0) - hi;
+					}
+				}
+				const int any = __syncthreads_or(ch);
+				if (ch)
+					s_exit[tid] = ex;
+				if (!any)
+					break;
+			}
+			uint32_t c1[1] = {act ? cnt : 0u}, ex1[1], tot;
+			block_scan<1>(c1, ex1, tot, s_warp);
+			if (act && cnt) {
+				uint32_t dummy;
+				const int64_t first = done + ex1[0];
+				(void) hd_run(s_w, s_lut, a.huff_tree, lo + cur, hi, dummy, dst + first, count - first);
+			}
+			entry = s_exit[nsub - 1];
+			done += tot;
+			__syncthreads();
+		}
+		if (done < count && tid == 0)
+			atomicOr(&a.hdr->error, ERR_MALFORMED);	// bitstream shorter than its symbol count
+	}
+}
+
+// ---------------------------------------------------------------------------
+// tile sweeps
+
+// Stage global bytes [src, src + len) at stage[(src & 15) + i].  One CTA.
+__device__ __forceinline__ void block_copy_in(uint8_t *stage, const uint8_t *src, uint32_t len,
+					      const uint8_t *base, const uint8_t *limit)
+{
+	const uint32_t a = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
+	const uint8_t *gb = src - a;
+	const uint32_t end = a + len;
+	const uint32_t nw = (end + 15) >> 4;
+	for (uint32_t w = threadIdx.x; w < nw; w += NT) {
+		const uint8_t *gp = gb + 16 * w;
+		if (gp >= base && gp + 16 <= limit) {
+			reinterpret_cast<uint4 *>(stage)[w] = __ldg(reinterpret_cast<const uint4 *>(gp));
+		} else {
+			const uint32_t lo = 16 * w, b0 = lo < a ? a : lo, b1 = lo + 16 > end ? end : lo + 16;
+			for (uint32_t b = b0; b < b1; b++)
+				stage[b] = gb[b];
+		}
+	}
+}
+
+struct ExDecShared {
+	alignas(16) uint8_t stage[XT + 48];
+	uint32_t warp[NW + 1];
+	uint32_t e_lo, e_hi, carry;
+};
+
+// zd values of the thread's 16 elements (two per word, 0 for elements outside the
+// read); returns false when the tile's read is bad.  Contains CTA barriers.
+__device__ __forceinline__ bool ex_tile_values(const ExDecArgs &a, const ExTile &T, uint32_t g,
+					       ExDecShared &sm, bool want_carry, uint32_t (&zz)[8],
+					       uint32_t &valid, uint32_t &q)
+{
+	const int tid = threadIdx.x, lane = tid & 31;
+	const uint64_t pay0 = a.r_pay[T.r];
+	if (pay0 == SENTINEL)
+		return false;
+	const uint64_t n = T.rend - T.off0;
+	const uint32_t nex = a.r_nex[T.r];
+	const uint2 *ex = a.pool + a.r_pool[T.r];
+	q = a.r_q[T.r];
+	const uint32_t j_lo = ex_v_before(T.t, T.m, n), j_hi = ex_v_before(T.t + 1, T.m, n);
+	if (tid == 0)
+		sm.carry = 0;
+	__syncthreads();
+	if (tid < 2) {	// exceptions before the tile / before its end: lower_bound on the positions
+		const uint32_t key = tid ? j_hi : j_lo;
+		uint32_t lo = 0, hi = nex;
+		while (lo < hi) {
+			const uint32_t mid = (lo + hi) >> 1;
+			if (ex[mid].x < key)
+				lo = mid + 1;
+			else
+				hi = mid;
+		}
+		(tid ? sm.e_hi : sm.e_lo) = lo;
+	}
+	if (want_carry) {	// sum of the deltas of the read's earlier tiles
+		const uint32_t g0 = g - T.t;
+		uint32_t s = 0;
+		for (uint32_t h = g0 + tid; h < g; h += NT)
+			s += a.t_sum[h];
+		s = __reduce_add_sync(0xffffffffu, s);
+		if (lane == 0 && s)
+			atomicAdd(&sm.carry, s);
+	}
+	__syncthreads();
+	const uint32_t e_lo = sm.e_lo, e_hi = sm.e_hi;
+	const uint32_t p_lo = j_lo - e_lo, plen = (j_hi - e_hi) - p_lo;
+	const uint8_t *pbase = a.method == PRESS_GPU_SHUFF_VBE21_ZD ? a.paybuf + T.off0 : a.in + pay0;
+	const uint8_t *src = pbase + p_lo;
+	const bool shuff = a.method == PRESS_GPU_SHUFF_VBE21_ZD;
+	block_copy_in(sm.stage, src, plen, shuff ? a.paybuf : a.in,
+		      shuff ? a.paybuf + ((a.offsets[a.nreads] + 15) & ~15ull) : a.in + a.in_bytes);
+	__syncthreads();
+	const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
+	const uint64_t ka = T.k0 + 2 * tid;
+	valid = group_valid(ka, T.off0, T.rend) | (group_valid(ka + 1, T.off0, T.rend) << 8);
+	const int64_t i0 = (int64_t) (8 * ka) - (int64_t) T.off0;
+#pragma unroll
+	for (int j = 0; j < 8; j++)
+		zz[j] = 0;
+	if (valid) {
+		const int64_t jf = i0 + (__ffs(valid) - 1) - 1;	// v-index of the first valid element (-1: zd0)
+		uint32_t e = e_lo;
+		if (e_hi > e_lo) {
+			uint32_t lo = e_lo, hi = e_hi;
+			const int64_t key = jf < 0 ? 0 : jf;
+			while (lo < hi) {
+				const uint32_t mid = (lo + hi) >> 1;
+				if ((int64_t) ex[mid].x < key)
+					lo = mid + 1;
+				else
+					hi = mid;
+			}
+			e = lo;
+		}
+		uint32_t nextpos = e < e_hi ? ex[e].x : 0xffffffffu;
+		const uint8_t *st = sm.stage + al;
+#pragma unroll
+		for (int el = 0; el < 16; el++) {
+			if ((valid >> el) & 1) {
+				const int64_t j = i0 + el - 1;
+				uint32_t z;
+				if (j < 0) {
+					z = a.r_zd0[T.r];
+				} else if ((uint32_t) j == nextpos) {
+					z = ex[e].y;
+					e++;
+					nextpos = e < e_hi ? ex[e].x : 0xffffffffu;
+				} else {
+					z = st[(uint32_t) j - e - p_lo];
+				}
+				zz[el >> 1] |= (z & 0xffffu) << (16 * (el & 1));
+			}
+		}
+	}
+	return true;
+}
+
+__global__ void __launch_bounds__(NT) ex_sum_kernel(const __grid_constant__ ExDecArgs a)
+{
+	__shared__ ExDecShared sm;
+	__shared__ uint32_t s_sum;
+	const int tid = threadIdx.x, lane = tid & 31;
+	const uint32_t total = a.hdr->total_tiles;
+	for (uint32_t g = blockIdx.x; g < total; g += gridDim.x) {
+		ExTile T;
+		ex_tile_info(a.tile_start, a.tile_read, a.offsets, g, T);
+		if (T.ntiles == 1)
+			continue;	// nobody reads the sum of a single-tile read
+		if (tid == 0)
+			s_sum = 0;
+		uint32_t zz[8], valid, q;
+		if (!ex_tile_values(a, T, g, sm, false, zz, valid, q)) {
+			if (tid == 0)
+				a.t_sum[g] = 0;
+			continue;
+		}
+		uint32_t s = 0;
+#pragma unroll
+		for (int j = 0; j < 8; j++) {
+			const uint32_t d = unzigzag16x2(zz[j]);
+			s += (d & 0xffffu) + (d >> 16);
+		}
+		s = __reduce_add_sync(0xffffffffu, s);
+		if (lane == 0)
+			atomicAdd(&s_sum, s);
+		__syncthreads();
+		if (tid == 0)
+			a.t_sum[g] = s_sum & 0xffffu;
+		__syncthreads();
+	}
+}
+
+__global__ void __launch_bounds__(NT) ex_decode_kernel(const __grid_constant__ ExDecArgs a)
+{
+	__shared__ ExDecShared sm;
+	const int tid = threadIdx.x;
+	const uint32_t total = a.hdr->total_tiles;
+	uint4 *out4 = reinterpret_cast<uint4 *>(a.samples_out);
+	uint16_t *out16 = reinterpret_cast<uint16_t *>(a.samples_out);
+	for (uint32_t g = blockIdx.x; g < total; g += gridDim.x) {
+		ExTile T;
+		ex_tile_info(a.tile_start, a.tile_read, a.offsets, g, T);
+		uint32_t zz[8], valid, q;
+		if (!ex_tile_values(a, T, g, sm, T.t > 0, zz, valid, q))
+			continue;
+		// running sum inside the thread (mod 2^16 in each half), decode_scalar.hpp:10-13 + trans.c:260-270
+		uint32_t y[8], carry = 0;
+#pragma unroll
+		for (int j = 0; j < 8; j++) {
+			const uint32_t d = unzigzag16x2(zz[j]);
+			y[j] = add16x2(d * 0x00010001u, carry);
+			carry = __byte_perm(y[j], 0, 0x3232);
+		}
+		uint32_t c1[1] = {carry & 0xffffu}, ex1[1], tot;
+		block_scan<1>(c1, ex1, tot, sm.warp);
+		const uint32_t cw = ((ex1[0] + sm.carry) & 0xffffu) * 0x00010001u;
+		uint32_t o[8];
+#pragma unroll
+		for (int j = 0; j < 8; j++) {
+			o[j] = add16x2(y[j], cw);
+			if (q)
+				o[j] = shl16x2(o[j], q);	// ex_zd.c:396-401
+		}
+		const uint64_t ka = T.k0 + 2 * tid;
+#pragma unroll
+		for (int h = 0; h < 2; h++) {
+			const uint32_t vm = (valid >> (8 * h)) & 0xffu;
+			if (vm == 0xffu) {
+				out4[ka + h] = make_uint4(o[4 * h], o[4 * h + 1], o[4 * h + 2], o[4 * h + 3]);
+			} else if (vm) {
+#pragma unroll
+				for (int e = 0; e < 8; e++)
+					if ((vm >> e) & 1)
+						out16[8 * (ka + h) + e] = (uint16_t) (o[4 * h + (e >> 1)] >> (16 * (e & 1)));
+			}
+		}
+		__syncthreads();
+	}
+}
+
+}  // namespace pg

@@ -9,9 +9,15 @@ namespace pg {
 
 struct ScratchLayout {
 	size_t hdr, status, status2, status_blk, status2_blk, zero_bytes, tile_start, kx, tile_read, extra, total;
+	// exception-coded methods (exfam.cuh): per-tile / per-read tables, Huffman payload, exception pool
+	size_t x_t[6], x_r[4], x_r8[1], x_paybuf, x_pool;
+	uint64_t x_pool_cap;	// entries
 };
 
-ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples);
+// pool_frac: exception pool entries per sample (< 0: the library default)
+ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples, double pool_frac = -1);
+// the layout of a scratch buffer of `bytes` bytes: the pool takes what is left
+ScratchLayout scratch_layout_for(int method, uint64_t nreads, uint64_t nsamples, size_t bytes);
 uint64_t max_tiles(uint64_t nreads, uint64_t nsamples);
 
 // A device buffer that only ever grows (high-water mark), as the per-read

@@ -18,6 +18,8 @@
 #include "plan.cuh"
 #include "svb_zd.cuh"
 #include "svb_enc.cuh"
+#include "exfam.cuh"
+#include "exfam_dec.cuh"
 #include "synth.cuh"
 #include "host_ctx.h"
 
@@ -98,13 +100,43 @@ uint64_t max_tiles(uint64_t nreads, uint64_t nsamples)
 	return nsamples / WT + 2 * nreads + 2;
 }
 
-ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples)
+static double default_pool_frac();
+
+ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples, double pool_frac)
 {
-	(void) method;
-	ScratchLayout l;
+	ScratchLayout l = {};
 	const uint64_t mt = max_tiles(nreads, nsamples);
 	size_t o = 0;
 	l.hdr = o;		o += sizeof(Hdr);
+	if (method >= PRESS_GPU_VBE21_ZD) {
+		const uint64_t xt = nsamples / 4096 + 2 * nreads + 2;	// tiles of 4096 samples
+		l.zero_bytes = o;	// only the header is cleared
+		l.tile_start = o;	o += align_up((nreads + 1) * 4, 256);
+		l.kx = o;		o += align_up((nreads + 1) * 8, 256);
+		l.tile_read = o;	o += align_up(xt * 4, 256);
+		for (int i = 0; i < 6; i++) {
+			l.x_t[i] = o;
+			o += align_up(xt * 4, 256);
+		}
+		for (int i = 0; i < 4; i++) {
+			l.x_r[i] = o;
+			o += align_up((nreads + 1) * 4, 256);
+		}
+		l.x_r8[0] = o;		o += align_up((nreads + 1) * 8, 256);
+		l.x_paybuf = o;
+		if (method == PRESS_GPU_SHUFF_VBE21_ZD)
+			o += align_up(nsamples + 64, 256);
+		l.x_pool = o;
+		if (pool_frac < 0)
+			pool_frac = default_pool_frac();
+		uint64_t cap = (uint64_t) ((double) nsamples * pool_frac) + 4096;
+		if (cap > nsamples + 1)
+			cap = nsamples + 1;
+		l.x_pool_cap = cap;
+		o += align_up(cap * 8, 256);
+		l.total = o;
+		return l;
+	}
 	l.status = o;		o += align_up(mt * 8, 256);
 	l.status2 = o;		o += align_up(mt * 8, 256);
 	l.status_blk = o;	o += align_up((mt / 32 + 2) * 8, 256);
@@ -114,6 +146,21 @@ ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples)
 	l.kx = o;		o += align_up((nreads + 1) * 8, 256);
 	l.tile_read = o;	o += align_up(mt * 4, 256);
 	l.total = o;
+	return l;
+}
+
+ScratchLayout scratch_layout_for(int method, uint64_t nreads, uint64_t nsamples, size_t bytes)
+{
+	ScratchLayout l = scratch_layout(method, nreads, nsamples, 0.0);
+	if (method >= PRESS_GPU_VBE21_ZD && bytes > l.x_pool) {
+		uint64_t cap = (bytes - l.x_pool) / 8;
+		if (cap > nsamples + 1)
+			cap = nsamples + 1;
+		if (cap > l.x_pool_cap) {
+			l.total += (cap - l.x_pool_cap) * 8;
+			l.x_pool_cap = cap;
+		}
+	}
 	return l;
 }
 
@@ -162,7 +209,7 @@ const char *press_gpu_version(void) { return "press_gpu 0.1 sm_100a"; }
 uint64_t press_gpu_launch_count(void) { return g_launches; }
 int press_gpu_method_implemented(int method)
 {
-	return method >= PRESS_GPU_SVB16_ZD && method <= PRESS_GPU_VBZ_SVB_ZD;
+	return method >= PRESS_GPU_SVB16_ZD && method < PRESS_GPU_NMETHODS;
 }
 
 uint64_t press_gpu_batch_bound(int method, uint64_t nreads, uint64_t nsamples)
@@ -172,6 +219,11 @@ uint64_t press_gpu_batch_bound(int method, uint64_t nreads, uint64_t nsamples)
 	case PRESS_GPU_VBZ_SVB16_ZD: return 2 * nsamples + nsamples / 8 + 5 * nreads + 16;
 	case PRESS_GPU_SVB_ZD: return 2 * nsamples + nsamples / 4 + nreads + 16;
 	case PRESS_GPU_VBZ_SVB_ZD: return 2 * nsamples + nsamples / 4 + 5 * nreads + 16;
+	/* every sample an exception: 6 B (vbe21), <= 1.25 + 2.125 B (vbsse21) per sample */
+	case PRESS_GPU_VBE21_ZD: return 6 * nsamples + 16;
+	case PRESS_GPU_SHUFF_VBE21_ZD: return 6 * nsamples + 4 * nreads + 16;
+	case PRESS_GPU_VBSSE21_ZD: return 4 * nsamples + 16 * nreads + 16;
+	case PRESS_GPU_EX_ZD: return 2 * nsamples + 1024 * nreads + 16;	/* ex_zd.c:411 cap */
 	default: break;
 	}
 	return 0;
@@ -274,6 +326,12 @@ bool is_svb(int m) { return m >= PRESS_GPU_SVB16_ZD && m <= PRESS_GPU_VBZ_SVB_ZD
 
 }  // namespace
 
+#include "ex_host.inc"
+
+namespace pg {
+static double default_pool_frac() { return g_pool_frac; }
+}
+
 extern "C" {
 
 int press_gpu_batch_press(int method, const int16_t *d_samples, const uint64_t *d_offsets,
@@ -283,7 +341,7 @@ int press_gpu_batch_press(int method, const int16_t *d_samples, const uint64_t *
 	if (ensure_init())
 		return -1;
 	cudaStream_t st = (cudaStream_t) stream;	// NULL = the CUDA default stream
-	const ScratchLayout l = scratch_layout(method, nreads, nsamples);
+	const ScratchLayout l = scratch_layout_for(method, nreads, nsamples, scratch_bytes);
 	if (scratch_bytes < l.total) {
 		set_err("scratch too small: %zu < %zu", scratch_bytes, l.total);
 		return -1;
@@ -323,6 +381,9 @@ int press_gpu_batch_press(int method, const int16_t *d_samples, const uint64_t *
 		if (k2 && !frame) return launch_svb_encode<2, false>(a, st);
 		return launch_svb_encode<2, true>(a, st);
 	}
+	if (method >= PRESS_GPU_VBE21_ZD && method < PRESS_GPU_NMETHODS)
+		return ex_batch_press(method, d_samples, d_offsets, nreads, nsamples, d_out, out_capacity,
+				      d_out_offsets, l, scr, st);
 	set_err("batch_press: method %d not implemented", method);
 	return -1;
 }
@@ -335,7 +396,7 @@ int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_i
 	if (ensure_init())
 		return -1;
 	cudaStream_t st = (cudaStream_t) stream;	// NULL = the CUDA default stream
-	const ScratchLayout l = scratch_layout(method, nreads, nsamples);
+	const ScratchLayout l = scratch_layout_for(method, nreads, nsamples, scratch_bytes);
 	if (scratch_bytes < l.total) {
 		set_err("scratch too small: %zu < %zu", scratch_bytes, l.total);
 		return -1;
@@ -374,6 +435,9 @@ int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_i
 		if (k2 && !frame) return launch_svb_decode<2, false>(a, st);
 		return launch_svb_decode<2, true>(a, st);
 	}
+	if (method >= PRESS_GPU_VBE21_ZD && method < PRESS_GPU_NMETHODS)
+		return ex_batch_depress(method, d_in, d_in_offsets, in_bytes, d_offsets, nreads, nsamples,
+					d_samples_out, l, scr, st);
 	set_err("batch_depress: method %d not implemented", method);
 	return -1;
 }
@@ -473,4 +537,3 @@ void press_gpu_host_free(void *p)
 
 #include "host_paths.inc"
 #include "synth_host.inc"
-#include "todo_stubs.inc"

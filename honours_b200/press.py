@@ -75,6 +75,8 @@ def lib() -> C.CDLL:
         L.press_gpu_batch_bound.argtypes = [i32, u64, u64]
         L.press_gpu_batch_scratch_bytes.restype = sz
         L.press_gpu_batch_scratch_bytes.argtypes = [i32, u64, u64]
+        L.press_gpu_set_exception_capacity.restype = None
+        L.press_gpu_set_exception_capacity.argtypes = [C.c_double]
         L.press_gpu_batch_press.restype = i32
         L.press_gpu_batch_press.argtypes = [i32, vp, vp, u64, u64, vp, u64, vp, vp, sz, vp]
         L.press_gpu_batch_depress.restype = i32
@@ -121,6 +123,11 @@ def set_huffman_table(blob: bytes | None = None) -> None:
         blob = open(os.path.join(PKG, "data", "NA12878_zd.huffman"), "rb").read()
     if lib().press_gpu_set_huffman_table(blob, len(blob)) != 0:
         raise PressGpuError(last_error())
+
+
+def set_exception_capacity(entries_per_sample: float) -> None:
+    """Exception pool size used by batch_scratch_bytes() for methods 4-7."""
+    lib().press_gpu_set_exception_capacity(float(entries_per_sample))
 
 
 # ---------------------------------------------------------------------------

@@ -135,9 +135,20 @@ int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_i
 			    uint64_t nsamples, int16_t *d_samples_out, void *d_scratch,
 			    size_t scratch_bytes, void *stream);
 
+/* The exception-coded methods (4-7) collect the values > 255 in a pool inside
+ * d_scratch.  Its size is `entries_per_sample` x nsamples + 4096 entries of 8
+ * bytes (default 1/64; NA12878 signal has 4.3e-5 exceptions per sample;
+ * 1.0 = "every sample may be an exception").  Takes effect in
+ * press_gpu_batch_scratch_bytes(); the batch calls use whatever pool fits in the
+ * scratch they are given and report status bit 3 when it overflows (nothing is
+ * written then: call again with a larger scratch).  The host-buffer and per-read
+ * entry points retry with a full-size pool by themselves. */
+void press_gpu_set_exception_capacity(double entries_per_sample);
+
 /* Device-side error word of the last batch call that used d_scratch (blocks
  * until `stream` is idle).  0 = ok; bit 0 capacity exceeded, bit 1 malformed
- * input, bit 2 ex-zd scratch cap (the reference would have returned -1). */
+ * input, bit 2 ex-zd scratch cap (the reference would have returned -1; those reads
+ * get an empty stream), bit 3 exception pool overflow. */
 int press_gpu_batch_status(void *d_scratch, void *stream);
 
 /* Host-buffer batch (end-to-end path): pinned staging, H2D, kernels, D2H, all

@@ -11,13 +11,17 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
-IMPLEMENTED = ["svb16_zd", "svb_zd", "vbz_svb16_zd", "vbz_svb_zd"]
+IMPLEMENTED = ["svb16_zd", "svb_zd", "vbz_svb16_zd", "vbz_svb_zd",
+               "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd"]
+EXFAM = IMPLEMENTED[4:]
 
 
 @pytest.fixture(scope="module")
 def gpu():
     from honours_b200 import press
     press.init(0)
+    press.set_huffman_table()
+    assert press.implemented_methods() == IMPLEMENTED
     return press
 
 
@@ -61,13 +65,21 @@ def test_three_reads_per_read_dropin(gpu, oracle, three_reads, method):
 def test_edge_lengths_per_read(gpu, oracle, method):
     rng = np.random.default_rng(42)
     for n in [1, 2, 3, 7, 8, 9, 15, 16, 17, 63, 64, 65, 4095, 4096, 4097, 8191, 8192, 8193, 12289]:
-        for kind in ("walk", "noise"):
+        for kind in ("walk", "noise", "spiky", "q"):
             s = rand_read(rng, kind, n)
             rc, st = gpu.press(method, s)
             ro, so = oracle.press(method, s)
-            assert rc == 0 and ro == 0 and st == so, (method, kind, n)
+            # ex-zd gives up on streams longer than 2n + 1024 (ex_zd.c:411): same verdict expected
+            assert (rc == 0) == (ro == 0), (method, kind, n, rc, ro)
+            if ro != 0:
+                continue
+            assert st == so, (method, kind, n)
+            ro, bo = oracle.depress(method, so, n)
             rc, back = gpu.depress(method, so, n)
-            assert rc == 0 and np.array_equal(back, s), (method, kind, n)
+            # (the reference cannot decode a Huffman stream with no symbols, huffman.c:696-711)
+            assert (rc == 0) == (ro == 0), (method, kind, n, rc, ro)
+            if ro == 0:
+                assert np.array_equal(back, s), (method, kind, n)
 
 
 def make_batch(rng, nreads, lo, hi, kinds=("walk", "spiky", "q", "noise")):
@@ -82,7 +94,8 @@ def test_batch_host_matches_oracle(gpu, oracle, method):
     """tight container: stream r at out_offsets[r], all byte-identical to the oracle;
     reads are back to back so most start at a misaligned address."""
     rng = np.random.default_rng(7)
-    samples, offsets, reads = make_batch(rng, 300, 1, 30000)
+    kinds = ("walk", "spiky", "q") if method in ("ex_zd", "shuff_vbe21_zd") else ("walk", "spiky", "q", "noise")
+    samples, offsets, reads = make_batch(rng, 300, 2 if method in EXFAM else 1, 30000, kinds=kinds)
     rc, cont, oo = gpu.batch_press_host(method, samples, offsets)
     assert rc == 0
     expect = [oracle.press(method, s)[1] for s in reads]
@@ -96,7 +109,7 @@ def test_batch_host_matches_oracle(gpu, oracle, method):
 @pytest.mark.parametrize("method", IMPLEMENTED)
 def test_batch_with_empty_and_tiny_reads(gpu, oracle, method):
     rng = np.random.default_rng(9)
-    lens = [0, 1, 0, 5, 4096, 0, 4097, 8, 0]
+    lens = [0, 2 if method == "shuff_vbe21_zd" else 1, 0, 5, 4096, 0, 4097, 8, 0]
     reads = [rand_read(rng, "spiky", n) for n in lens]
     samples = np.concatenate(reads) if reads else np.zeros(0, np.int16)
     offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
@@ -113,27 +126,29 @@ def test_long_read_many_tiles(gpu, oracle):
     """one 3.3 M-sample read: > 800 tiles chained by look-back inside one read"""
     rng = np.random.default_rng(11)
     s = rand_read(rng, "spiky", 3_300_001)
-    for method in ("svb16_zd", "vbz_svb_zd"):
+    for method in ("svb16_zd", "vbz_svb_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd"):
         rc, st = gpu.press(method, s)
         assert rc == 0 and st == oracle.press(method, s)[1]
         rc, back = gpu.depress(method, st, s.size)
         assert rc == 0 and np.array_equal(back, s)
 
 
-def test_device_batch_api_torch_pointers(gpu, oracle):
+@pytest.mark.parametrize("method", ["svb16_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd"])
+def test_device_batch_api_torch_pointers(gpu, oracle, method):
     """the measured path: device-resident in/out, raw pointers through the C ABI"""
     import torch
     rng = np.random.default_rng(5)
-    samples, offsets, reads = make_batch(rng, 2000, 2000, 60000, kinds=("walk", "spiky"))
-    method = "svb16_zd"
+    samples, offsets, reads = make_batch(rng, 600, 2000, 60000, kinds=("walk", "spiky", "q"))
     dev = torch.device("cuda:0")
     d_s = torch.from_numpy(samples).to(dev)
     d_off = torch.from_numpy(offsets.astype(np.int64)).to(dev)
     nreads, ns = len(reads), samples.size
     cap = gpu.batch_bound(method, nreads, ns)
+    gpu.set_exception_capacity(1.0)     # the "q" reads are mostly exceptions for the methods without qts
     d_out = torch.empty(cap, dtype=torch.uint8, device=dev)
     d_oo = torch.empty(nreads + 1, dtype=torch.int64, device=dev)
     sb = gpu.batch_scratch_bytes(method, nreads, ns)
+    gpu.set_exception_capacity(1.0 / 64)
     d_scr = torch.empty(sb, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
     gpu.batch_press(method, d_s.data_ptr(), d_off.data_ptr(), nreads, ns, d_out.data_ptr(), cap,
@@ -161,3 +176,49 @@ def test_capacity_error_is_reported(gpu):
     rc = gpu.lib().press_gpu_batch_press_host(0, s.ctypes.data, offs.ctypes.data, 1,
                                               out.ctypes.data, 100, oo.ctypes.data)
     assert rc != 0
+
+
+def test_ex_zd_scratch_cap_failure_mirrors_reference(gpu, oracle):
+    """ex_zd.c:411: a stream longer than 2n + 1024 makes the reference return -1"""
+    rng = np.random.default_rng(13)
+    s = rand_read(rng, "noise", 20000)
+    assert oracle.press("ex_zd", s)[0] != 0
+    assert gpu.press("ex_zd", s)[0] != 0
+    # inside a batch the read gets an empty stream and the call reports 1
+    ok = rand_read(rng, "walk", 5000)
+    samples = np.concatenate([ok, s, ok])
+    offsets = np.array([0, 5000, 25000, 30000], dtype=np.uint64)
+    rc, cont, oo = gpu.batch_press_host("ex_zd", samples, offsets)
+    e = oracle.press("ex_zd", ok)[1]
+    assert rc == 1 and cont.tobytes() == e + e and int(oo[1]) == int(oo[2])
+
+
+@pytest.mark.parametrize("method", EXFAM)
+@pytest.mark.parametrize("p_ex", [0.0, 1e-3, 0.1, 0.5])
+def test_exception_rate_sweep(gpu, oracle, method, p_ex):
+    """config 3: exception-rate sweep on synthetic NA12878-like reads (host generator)"""
+    from honours_b200 import workload
+    lengths, x0, shift = workload.read_table(40, q_fraction=0.25)
+    lengths = np.minimum(lengths, 30000)
+    offsets = workload.offsets_of(lengths)
+    samples = workload.synth_host(offsets, x0, shift, p_ex=p_ex)
+    reads = [samples[int(offsets[r]):int(offsets[r + 1])] for r in range(len(lengths))]
+    rc, cont, oo = gpu.batch_press_host(method, samples, offsets)
+    assert rc == 0
+    expect = [oracle.press(method, s)[1] for s in reads]
+    assert np.diff(oo.astype(np.int64)).tolist() == [len(e) for e in expect]
+    assert cont.tobytes() == b"".join(expect)
+    back = gpu.batch_depress_host(method, cont, oo, offsets)
+    assert np.array_equal(back, samples)
+
+
+def test_huffman_decodes_oracle_streams_without_sidecar(gpu, oracle):
+    """config 4: streams written by the CPU reference path carry no sub-block offsets;
+    the self-synchronising decoder must recover them exactly"""
+    rng = np.random.default_rng(17)
+    for n in (2, 30, 1000, 4097, 70001, 300001):
+        s = rand_read(rng, "walk" if n % 2 else "spiky", n)
+        ro, so = oracle.press("shuff_vbe21_zd", s)
+        assert ro == 0
+        rc, back = gpu.depress("shuff_vbe21_zd", so, n)
+        assert rc == 0 and np.array_equal(back, s), n
