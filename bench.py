@@ -258,6 +258,12 @@ def run_ours(args):
     max_ns = max(c["ns"] for c in chunks)
     max_nr = max(c["nreads"] for c in chunks)
     cap = max(press.batch_bound(method, c["nreads"], c["ns"]) for c in chunks)
+    if press.METHODS[method] >= 4:
+        # batch_bound is "every sample an exception" (6 B/sample); the container and the
+        # exception pool are sized for this workload's exception rate instead (with slack) --
+        # an overflow of either is reported by batch_status, never silent
+        cap = min(cap, max(int((1.05 + 8.0 * p_ex) * c["ns"]) + 1100 * c["nreads"] + 4096 for c in chunks))
+        press.set_exception_capacity(max(1.0 / 64, 1.3 * p_ex))
     sb = max(press.batch_scratch_bytes(method, c["nreads"], c["ns"]) for c in chunks)
     d_s = torch.empty(max_ns + 64, dtype=torch.int16, device=dev)
     d_back = torch.empty(max_ns + 64, dtype=torch.int16, device=dev)

@@ -20,6 +20,7 @@
 #include "svb_enc.cuh"
 #include "exfam.cuh"
 #include "exfam_dec.cuh"
+#include "svb_dec.cuh"
 #include "synth.cuh"
 #include "host_ctx.h"
 
@@ -307,15 +308,12 @@ int launch_svb_encode(const SvbEncArgs &a, cudaStream_t st)
 }
 
 template <int KEYBITS, bool FRAME>
-int launch_svb_decode(const SvbDecArgs &a, cudaStream_t st)
+int launch_svb_decode(const SvbDec2Args &a, cudaStream_t st)
 {
-	int grid;
-	if (persistent_grid(svb_zd_decode_kernel<KEYBITS, FRAME>, &grid))
-		return -1;
+	const uint64_t cap = (uint64_t) g_ctx.sms * 8;
+	const unsigned grid = (unsigned) (a.nreads < cap ? (a.nreads ? a.nreads : 1) : cap);
 	EvPair *ev = prof_begin(1, st);
-	void *params[] = {const_cast<SvbDecArgs *>(&a)};
-	CK(cudaLaunchCooperativeKernel((const void *) svb_zd_decode_kernel<KEYBITS, FRAME>, dim3(grid),
-				       dim3(NT), params, 0, st));
+	svb_dec_kernel<KEYBITS, FRAME><<<grid, NT, 0, st>>>(a);
 	prof_end(ev, st);
 	g_launches++;
 	CK(cudaGetLastError());
@@ -414,9 +412,8 @@ int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_i
 	if (is_svb(method)) {
 		const bool frame = method == PRESS_GPU_VBZ_SVB16_ZD || method == PRESS_GPU_VBZ_SVB_ZD;
 		const bool k2 = method == PRESS_GPU_SVB_ZD || method == PRESS_GPU_VBZ_SVB_ZD;
-		if (run_plan(l, scr, d_offsets, nreads, TILING_ALIGNED, WT, frame ? 4 : 0, k2 ? 4 : 8, 0, st))
-			return -1;
-		SvbDecArgs a;
+		CK(cudaMemsetAsync(scr, 0, sizeof(Hdr), st));
+		SvbDec2Args a;
 		a.in = d_in;
 		a.in_bytes = in_bytes;
 		a.in_offsets = d_in_offsets;
@@ -424,12 +421,6 @@ int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_i
 		a.nreads = nreads;
 		a.samples_out = d_samples_out;
 		a.hdr = reinterpret_cast<Hdr *>(scr + l.hdr);
-		a.tile_start = reinterpret_cast<const uint32_t *>(scr + l.tile_start);
-		a.tile_read = reinterpret_cast<const uint32_t *>(scr + l.tile_read);
-		a.status_bytes = reinterpret_cast<uint64_t *>(scr + l.status);
-		a.status_sum = reinterpret_cast<uint64_t *>(scr + l.status2);
-		a.status_bytes_blk = reinterpret_cast<uint64_t *>(scr + l.status_blk);
-		a.status_sum_blk = reinterpret_cast<uint64_t *>(scr + l.status2_blk);
 		if (!k2 && !frame) return launch_svb_decode<1, false>(a, st);
 		if (!k2 && frame) return launch_svb_decode<1, true>(a, st);
 		if (k2 && !frame) return launch_svb_decode<2, false>(a, st);

@@ -1,0 +1,236 @@
+// svb_dec.cuh -- fused streamvbyte + inverse zigzag-delta DECODE, one pass over HBM.
+//
+//   KEYBITS = 1 : ONT svb16 (svb16/decode_scalar.hpp:31-71; press.c:1689-1694)
+//   KEYBITS = 2 : classical streamvbyte, codes 0/1 only (streamvbyte_decode.c:16-58; press.c:1600-1612)
+//   FRAME       : [n u32 LE] prefix of the pre-zstd VBZ stream (press.c:1887-1910, 2047-2070)
+//
+// The reference's decoder carries two values from one sample to the next: the
+// data pointer (advanced by 1 + key bit) and the running sum of the deltas.  Here
+// one CTA owns one READ (reads are handed out by an atomic ticket) and walks it
+// tile by tile (4096 samples), carrying both values itself, so no tile ever waits
+// for another CTA and nothing is read twice:
+//
+//   keys of tile t+2   -> registers        (their address does not depend on the data)
+//   keys of tile t+1   -> byte counts -> block scan -> the tile's data range is known
+//   data of tile t+1   -> registers        (aligned 128-bit loads, issued before ...)
+//   tile t             -> smem stage -> values -> unzigzag -> block scan + carry ->
+//                         smem -> aligned 128-bit stores
+//
+// so the loads of a tile are in flight for a whole tile time before they are
+// needed.  1184 reads are in flight on a B200 (8 CTAs per SM).
+#pragma once
+
+#include "common.cuh"
+#include "exfam.cuh"
+
+namespace pg {
+
+constexpr int DT = 4096;		// samples per tile
+constexpr int DPT = DT / NT;		// samples per thread (16)
+
+struct SvbDec2Args {
+	const uint8_t *in;		// container, 16-byte aligned
+	uint64_t in_bytes;
+	const uint64_t *in_offsets;	// [nreads + 1]
+	const uint64_t *offsets;	// [nreads + 1]
+	uint64_t nreads;
+	int16_t *samples_out;
+	Hdr *hdr;			// ticket = next read
+};
+
+// 16-byte word `w` of the 16-byte aligned region starting at `base16`, bytes outside [lo, hi) read as 0
+__device__ __forceinline__ uint4 load_word_guarded(const uint8_t *base16, uint32_t w, const uint8_t *lo, const uint8_t *hi)
+{
+	const uint8_t *p = base16 + 16ull * w;
+	if (p >= lo && p + 16 <= hi)
+		return __ldg(reinterpret_cast<const uint4 *>(p));
+	uint32_t v[4] = {0, 0, 0, 0};
+	for (int b = 0; b < 16; b++)
+		if (p + b >= lo && p + b < hi)
+			v[b >> 2] |= (uint32_t) p[b] << (8 * (b & 3));
+	return make_uint4(v[0], v[1], v[2], v[3]);
+}
+
+template <int KEYBITS>
+__device__ __forceinline__ uint32_t dec_thread_flags(const uint8_t *keys, uint64_t nkeys, uint32_t t, int tid)
+{
+	// the 16 samples of this thread are covered by 2 (svb16) / 4 (svb32) key bytes
+	constexpr int KPT = KEYBITS == 1 ? 2 : 4;
+	const uint64_t kb = ((uint64_t) t * NT + tid) * KPT;
+	uint32_t k = 0;
+#pragma unroll
+	for (int b = 0; b < KPT; b++)
+		if (kb + b < nkeys)
+			k |= (uint32_t) __ldg(keys + kb + b) << (8 * b);
+	if (KEYBITS == 2)	// codes 0/1 only (zd < 65536): low bit of every 2-bit code
+		k = squeeze16(k) | (squeeze16(k >> 16) << 8);
+	return k;
+}
+
+template <int KEYBITS, bool FRAME>
+__global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ SvbDec2Args a)
+{
+	__shared__ __align__(16) uint8_t s_in[2 * DT + 64];
+	__shared__ __align__(16) uint8_t s_out[2 * DT + 32];
+	__shared__ uint32_t s_warp[NW + 1], s_warp2[NW + 1];	// byte-count scans / value scans
+	__shared__ uint32_t s_read;
+	const int tid = threadIdx.x;
+	const uint8_t *limit = a.in + a.in_bytes;
+	for (;;) {
+		__syncthreads();
+		if (tid == 0)
+			s_read = atomicAdd(&a.hdr->ticket, 1u);
+		__syncthreads();
+		const uint64_t r = s_read;
+		if (r >= a.nreads)
+			break;
+		const uint64_t off0 = __ldg(a.offsets + r), n = __ldg(a.offsets + r + 1) - off0;
+		const uint64_t sbase = __ldg(a.in_offsets + r), send = __ldg(a.in_offsets + r + 1);
+		const uint64_t nkeys = KEYBITS == 1 ? (n + 7) / 8 : (n + 3) / 4;
+		const uint64_t fixed = (FRAME ? 4 : 0) + nkeys;
+		bool bad = send < sbase || send > a.in_bytes || send - sbase < fixed + n;	// >= 1 byte per value
+		if (FRAME && !bad && n) {	// press.c:2062 takes the count from the prefix
+			const uint8_t *p = a.in + sbase;
+			bad = (p[0] | (p[1] << 8) | (p[2] << 16) | ((uint32_t) p[3] << 24)) != (uint32_t) n;
+		}
+		if (bad) {
+			if (tid == 0)
+				atomicOr(&a.hdr->error, ERR_MALFORMED);
+			continue;
+		}
+		if (n == 0)
+			continue;
+		const uint8_t *keys = a.in + sbase + (FRAME ? 4 : 0);
+		const uint8_t *data = keys + nkeys;
+		const uint64_t ndata = send - sbase - fixed;
+		const uint32_t ntiles = (uint32_t) ((n + DT - 1) / DT);
+		uint8_t *dst = reinterpret_cast<uint8_t *>(a.samples_out + off0);
+
+		auto valid_of = [&](uint32_t t) -> uint32_t {
+			const uint64_t i0 = (uint64_t) t * DT + (uint64_t) tid * DPT;
+			return i0 >= n ? 0u : (n - i0 >= 16 ? 0xffffu : (0xffffu >> (16 - (uint32_t) (n - i0))));
+		};
+		// data bytes of a tile -> registers: word u, u + 256, (u + 512)
+		uint4 dreg[3];
+		auto issue_data = [&](uint64_t D, uint32_t L) {
+			const uint8_t *src = data + D;
+			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
+			const uint8_t *b16 = src - al;
+			const uint32_t nw = (al + L + 15) >> 4;
+#pragma unroll
+			for (int j = 0; j < 3; j++) {
+				const uint32_t w = tid + j * NT;
+				if (w < nw)
+					dreg[j] = load_word_guarded(b16, w, a.in, limit);
+			}
+		};
+
+		// ---- prologue: tile 0 scanned and its data requested, keys of tile 1 requested
+		uint32_t fl_cur = dec_thread_flags<KEYBITS>(keys, nkeys, 0, tid);
+		uint32_t va_cur = valid_of(0);
+		fl_cur &= va_cur;
+		uint32_t fl_next = ntiles > 1 ? dec_thread_flags<KEYBITS>(keys, nkeys, 1, tid) : 0u;
+		uint32_t ex_cur, L_cur;
+		{
+			uint32_t c1[1] = {(uint32_t) (__popc(va_cur) + __popc(fl_cur))}, e1[1];
+			block_scan<1>(c1, e1, L_cur, s_warp);
+			ex_cur = e1[0];
+		}
+		uint64_t D = 0;
+		uint32_t carry = 0;
+		bool overrun = L_cur > ndata;
+		if (!overrun)
+			issue_data(0, L_cur);
+		__syncthreads();	// s_warp is reused by the first scan-ahead
+
+		for (uint32_t t = 0; t < ntiles && !overrun; t++) {
+			// ---- data of tile t: registers -> stage (same 16-byte phase as in global memory)
+			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(data + D) & 15);
+			{
+				const uint32_t nw = (al + L_cur + 15) >> 4;
+#pragma unroll
+				for (int j = 0; j < 3; j++) {
+					const uint32_t w = tid + j * NT;
+					if (w < nw)
+						reinterpret_cast<uint4 *>(s_in)[w] = dreg[j];
+				}
+			}
+			// ---- scan ahead: tile t + 1's byte counts, then request its data and tile t + 2's keys
+			uint32_t fl_n = 0, va_n = 0, ex_n = 0, L_n = 0;
+			if (t + 1 < ntiles) {
+				va_n = valid_of(t + 1);
+				fl_n = fl_next & va_n;
+				uint32_t c1[1] = {(uint32_t) (__popc(va_n) + __popc(fl_n))}, e1[1];
+				block_scan<1>(c1, e1, L_n, s_warp);	// (its barriers also publish s_in)
+				ex_n = e1[0];
+				if (D + L_cur + L_n > ndata)
+					overrun = true;
+				else
+					issue_data(D + L_cur, L_n);
+				if (t + 2 < ntiles)
+					fl_next = dec_thread_flags<KEYBITS>(keys, nkeys, t + 2, tid);
+			} else {
+				__syncthreads();
+			}
+			// ---- bytes -> zd values, two per word
+			uint32_t zz[8];
+			const uint32_t p = al + ex_cur;
+			if (va_cur == 0xffffu && fl_cur == 0) {
+				const uint32_t *w32 = reinterpret_cast<const uint32_t *>(s_in) + (p >> 2);
+				const uint32_t sh = (p & 3) * 8;
+				uint32_t w[5];
+#pragma unroll
+				for (int j = 0; j < 5; j++)
+					w[j] = w32[j];
+#pragma unroll
+				for (int j = 0; j < 4; j++) {
+					const uint32_t v = __funnelshift_r(w[j], w[j + 1], sh);
+					zz[2 * j] = __byte_perm(v, 0, 0x4140);
+					zz[2 * j + 1] = __byte_perm(v, 0, 0x4342);
+				}
+			} else {
+				const uint8_t *q = s_in + p;
+#pragma unroll
+				for (int j = 0; j < 8; j++)
+					zz[j] = 0;
+#pragma unroll
+				for (int e = 0; e < 16; e++) {
+					if ((va_cur >> e) & 1) {
+						uint32_t v = *q++;
+						if ((fl_cur >> e) & 1)
+							v |= (uint32_t) (*q++) << 8;
+						zz[e >> 1] |= v << (16 * (e & 1));
+					}
+				}
+			}
+			// ---- unzigzag, running sum (mod 2^16 in each half): decode_scalar.hpp:10-13, 52-65
+			uint32_t y[8], c = 0;
+#pragma unroll
+			for (int j = 0; j < 8; j++) {
+				const uint32_t d = unzigzag16x2(zz[j]);
+				y[j] = add16x2(d * 0x00010001u, c);
+				c = __byte_perm(y[j], 0, 0x3232);
+			}
+			uint32_t c1[1] = {c & 0xffffu}, e1[1], tot;
+			block_scan<1>(c1, e1, tot, s_warp2);
+			const uint32_t cw = ((e1[0] + carry) & 0xffffu) * 0x00010001u;
+			uint4 *so = reinterpret_cast<uint4 *>(s_out) + 2 * tid;
+			so[0] = make_uint4(add16x2(y[0], cw), add16x2(y[1], cw), add16x2(y[2], cw), add16x2(y[3], cw));
+			so[1] = make_uint4(add16x2(y[4], cw), add16x2(y[5], cw), add16x2(y[6], cw), add16x2(y[7], cw));
+			__syncthreads();
+			const uint64_t left = n - (uint64_t) t * DT;
+			block_copy_out(s_out, dst + 2ull * t * DT, 2 * (uint32_t) (left < DT ? left : DT));
+			carry = (carry + tot) & 0xffffu;
+			D += L_cur;
+			fl_cur = fl_n;
+			va_cur = va_n;
+			ex_cur = ex_n;
+			L_cur = L_n;
+			__syncthreads();	// s_in / s_out are rewritten by the next tile
+		}
+		if (overrun && tid == 0)
+			atomicOr(&a.hdr->error, ERR_MALFORMED);
+	}
+}
+
+}  // namespace pg
