@@ -8,18 +8,20 @@
 //
 // Every stream is header first, and the header's length depends on ALL exceptions
 // of the read, so no byte of a read's payload can be placed before the whole read
-// has been seen: encode is two sweeps over the samples with small per-read steps
-// in between, every step a plain grid (no inter-CTA dependency anywhere):
+// has been seen: encode is two sweeps over the samples with one scan in between.
+// In both sweeps one CTA owns one READ (reads are handed out by an atomic ticket)
+// and walks it tile by tile, carrying the running values (exception index, payload
+// position, Huffman bit position and the bits of the last partial byte) itself, so
+// no CTA ever waits for another one; the next tile's samples are requested before
+// the current tile is processed.
 //
-//   ex_count   (tile)  zd in registers -> #exceptions, Huffman bits, OR of the samples;
-//                      exceptions captured in tile order into a pool
-//   ex_readq   (read)  ex-zd only: q = min(5, ctz(OR))  (ex_zd.c:358-381); reads with
-//                      q > 0 are re-counted on the shifted signal
-//   ex_size    (read)  per-tile prefixes (exception index, payload position), list
-//                      sizes, header length, stream size
+//   ex_count   (read)  zd in registers -> #exceptions, Huffman bits, OR of the samples
+//                      (ex-zd: q = min(5, ctz(OR)), ex_zd.c:358-381; reads with q > 0
+//                      are walked again on the shifted signal); exceptions captured in
+//                      order into a pool; list sizes -> header length, stream size
 //   ex_offsets (batch) exclusive scan of the sizes -> out_offsets
-//   ex_header  (read)  header + exception lists at the stream's final place
-//   ex_emit    (tile)  zd again -> payload bytes / Huffman bits to their final place
+//   ex_emit    (read)  header + exception lists, then zd again -> payload bytes /
+//                      Huffman bits to their final place
 //
 // Tile = 4096 samples of one read cut on 16-byte boundaries of the sample array
 // (aligned 128-bit loads), 16 contiguous samples per thread.
@@ -108,28 +110,41 @@ struct ExVals {
 	uint32_t orv;		// OR of the valid raw samples (both halves folded)
 };
 
-__device__ __forceinline__ void ex_load_zd(const uint4 *samples, uint64_t nsamples, const ExTile &T,
-					   uint32_t q, ExVals &v)
+// the thread's 32 bytes of a tile, requested ...
+struct ExRaw {
+	uint4 xa, xb;
+	uint32_t prev0;		// lane 0: the sample before the thread's first one
+};
+
+__device__ __forceinline__ void ex_issue(const uint4 *samples, uint64_t nsamples, uint64_t k0, ExRaw &w)
+{
+	const int tid = threadIdx.x;
+	const uint64_t ka = k0 + 2 * tid;
+	w.xa = load_group(samples, nsamples, ka);
+	w.xb = load_group(samples, nsamples, ka + 1);
+	w.prev0 = 0;
+	if ((tid & 31) == 0 && ka > 0 && 8 * ka - 1 < nsamples)
+		w.prev0 = __ldg(reinterpret_cast<const uint16_t *>(samples) + 8 * ka - 1);
+}
+
+// ... and turned into zd values one tile later
+__device__ __forceinline__ void ex_compute(const ExRaw &w, const ExTile &T, uint32_t q, ExVals &v)
 {
 	const int tid = threadIdx.x, lane = tid & 31;
 	const uint64_t ka = T.k0 + 2 * tid;
-	uint4 xa = load_group(samples, nsamples, ka);
-	uint4 xb = load_group(samples, nsamples, ka + 1);
+	uint4 xa = w.xa, xb = w.xb;
 	uint32_t prev = __shfl_up_sync(0xffffffffu, xb.w >> 16, 1);
-	if (lane == 0) {
-		prev = 0;
-		if (ka > 0 && 8 * ka - 1 < nsamples)
-			prev = __ldg(reinterpret_cast<const uint16_t *>(samples) + 8 * ka - 1);
-	}
+	if (lane == 0)
+		prev = w.prev0;
 	v.valid = group_valid(ka, T.off0, T.rend) | (group_valid(ka + 1, T.off0, T.rend) << 8);
 	{
 		// OR of the valid samples: mask out elements outside the read
-		uint32_t w[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w}, o = 0;
+		uint32_t x[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w}, o = 0;
 #pragma unroll
 		for (int j = 0; j < 8; j++) {
 			const uint32_t mk = ((v.valid >> (2 * j)) & 1u ? 0xffffu : 0u) |
 					    ((v.valid >> (2 * j + 1)) & 1u ? 0xffff0000u : 0u);
-			o |= w[j] & mk;
+			o |= x[j] & mk;
 		}
 		v.orv = (o | (o >> 16)) & 0xffffu;
 	}
@@ -156,98 +171,6 @@ __device__ __forceinline__ void ex_load_zd(const uint4 *samples, uint64_t nsampl
 __device__ __forceinline__ uint32_t ex_elem(const ExVals &v, int e)
 {
 	return (v.z[e >> 1] >> (16 * (e & 1))) & 0xffffu;
-}
-
-// ---------------------------------------------------------------------------
-// sweep 1: counts + exception capture
-
-template <bool HUFF, bool REQ>	// REQ: second counting sweep of the ex-zd reads with q > 0
-__global__ void __launch_bounds__(NT) ex_count_kernel(const __grid_constant__ ExArgs a)
-{
-	__shared__ uint32_t s_nex, s_bits, s_or, s_pool;
-	__shared__ uint32_t s_warp[NW + 1];
-	const int tid = threadIdx.x, lane = tid & 31;
-	const uint32_t total = a.hdr->total_tiles;
-	for (uint32_t g = blockIdx.x; g < total; g += gridDim.x) {
-		ExTile T;
-		ex_tile_info(a.tile_start, a.tile_read, a.offsets, g, T);
-		uint32_t q = 0;
-		if (REQ) {
-			q = a.r_q[T.r];
-			if (q == 0)
-				continue;
-		}
-		if (tid == 0)
-			s_nex = s_bits = s_or = 0;
-		__syncthreads();
-		ExVals v;
-		ex_load_zd(a.samples, a.nsamples, T, q, v);
-		const uint32_t cnt = __popc(v.exc);
-		uint32_t bits = 0;
-		if (HUFF) {
-			const uint32_t ne = v.valid & ~v.exc & ~v.first;
-#pragma unroll
-			for (int e = 0; e < 16; e++)
-				if ((ne >> e) & 1)
-					bits += __ldg(a.huff_enc + ex_elem(v, e)) >> 24;
-		}
-		const uint32_t wn = __reduce_add_sync(0xffffffffu, cnt);
-		const uint32_t wb = HUFF ? __reduce_add_sync(0xffffffffu, bits) : 0;
-		const uint32_t wo = __reduce_or_sync(0xffffffffu, v.orv);
-		if (lane == 0) {
-			if (wn)
-				atomicAdd(&s_nex, wn);
-			if (HUFF)
-				atomicAdd(&s_bits, wb);
-			if (!REQ && wo)
-				atomicOr(&s_or, wo);
-		}
-		__syncthreads();
-		const uint32_t nex = s_nex;
-		if (nex) {	// capture, in tile order
-			uint32_t c1[1] = {cnt}, ex1[1], tot;
-			block_scan<1>(c1, ex1, tot, s_warp);
-			if (tid == 0)
-				s_pool = (uint32_t) atomicAdd((unsigned long long *) &a.hdr->aux[0],
-							      (unsigned long long) nex);
-			__syncthreads();
-			const uint64_t base = s_pool;
-			if (base + nex <= a.pool_cap) {
-				uint2 *p = a.pool + base + ex1[0];
-				for (uint32_t m = v.exc; m; m &= m - 1) {
-					const int e = __ffs(m) - 1;
-					*p++ = make_uint2((uint32_t) (v.i0 + e - 1), ex_elem(v, e));
-				}
-			} else if (tid == 0) {
-				atomicOr(&a.hdr->error, ERR_SCRATCH);
-			}
-		}
-		if (tid == 0) {
-			a.t_nex[g] = nex;
-			a.t_pool[g] = nex ? s_pool : 0;
-			if (HUFF)
-				a.t_bits[g] = s_bits;
-			if (!REQ)
-				a.t_or[g] = s_or;
-		}
-		__syncthreads();
-	}
-}
-
-// ex-zd: q of every read from the OR of its samples (ex_zd.c:358-381).  One warp per read.
-__global__ void __launch_bounds__(NT) ex_readq_kernel(const __grid_constant__ ExArgs a)
-{
-	const uint64_t r = ((uint64_t) blockIdx.x * NT + threadIdx.x) >> 5;
-	const int lane = threadIdx.x & 31;
-	if (r >= a.nreads)
-		return;
-	const uint32_t g0 = a.tile_start[r], g1 = a.tile_start[r + 1];
-	uint32_t o = 0;
-	for (uint32_t g = g0 + lane; g < g1; g += 32)
-		o |= a.t_or[g];
-	o = __reduce_or_sync(0xffffffffu, o);
-	if (lane == 0)
-		a.r_q[r] = __ffs(o | 32u) - 1;	// a zero sample never lowers q; cap 5
 }
 
 // ---------------------------------------------------------------------------
@@ -357,71 +280,6 @@ __device__ __forceinline__ uint32_t ex_fixed_bytes(int method)
 	return method == PRESS_GPU_EX_ZD ? 16u : 6u;	// [ver][n u64][q] + [zd0 u16][nex u32]
 }
 
-// per-read sizes and per-tile prefixes.  One warp per read.
-__global__ void __launch_bounds__(NT) ex_size_kernel(const __grid_constant__ ExArgs a)
-{
-	const uint64_t r = ((uint64_t) blockIdx.x * NT + threadIdx.x) >> 5;
-	const int lane = threadIdx.x & 31;
-	if (r >= a.nreads)
-		return;
-	const bool huff = a.method == PRESS_GPU_SHUFF_VBE21_ZD;
-	const uint32_t g0 = a.tile_start[r], nt = a.tile_start[r + 1] - g0;
-	const uint64_t off0 = a.offsets[r], n = a.offsets[r + 1] - off0;
-	const uint32_t m = (uint32_t) (off0 & 7);
-	uint32_t eb = 0;
-	uint64_t bb = 0;
-	for (uint32_t t0 = 0; t0 < nt; t0 += 32) {
-		const uint32_t t = t0 + lane;
-		const uint32_t nx = t < nt ? a.t_nex[g0 + t] : 0u;
-		const uint32_t bt = huff && t < nt ? a.t_bits[g0 + t] : 0u;
-		const uint32_t ie = warp_inc_scan(nx, lane);
-		uint64_t ib = bt;
-		if (huff) {
-#pragma unroll
-			for (int o = 1; o < 32; o <<= 1) {
-				const uint64_t y = __shfl_up_sync(0xffffffffu, ib, o);
-				if (lane >= o)
-					ib += y;
-			}
-		}
-		if (t < nt) {
-			const uint32_t e0 = eb + ie - nx;
-			a.t_eb[g0 + t] = e0;
-			a.t_pb[g0 + t] = huff ? (uint32_t) (bb + ib - bt) : ex_v_before(t, m, n) - e0;
-		}
-		eb += __shfl_sync(0xffffffffu, ie, 31);
-		bb += __shfl_sync(0xffffffffu, ib, 31);
-	}
-	__syncwarp();
-	const uint32_t nex = eb;
-	uint32_t hdr = X_FAIL;
-	uint64_t size = 0;
-	if (n > 0 && !(a.hdr->error & ERR_SCRATCH)) {
-		const ExList L = {a.t_eb, a.t_pool, a.pool, g0, nt};
-		hdr = ex_fixed_bytes(a.method) + ex_lists<false>(a.method, L, nex, nullptr, lane);
-		const uint64_t mm = n - 1 - nex;
-		if (huff) {
-			hdr += 4;	// [count u32 BE], huffman.c:1199-1203
-			size = hdr + (bb + 7) / 8;
-			if (bb >> 32)
-				hdr = X_FAIL, size = 0;	// (cannot happen: 22 bits x 2^32 samples)
-		} else {
-			size = hdr + mm;
-		}
-		if (a.method == PRESS_GPU_EX_ZD && size > 2 * n + 1024) {	// ex_zd.c:411 scratch cap
-			if (lane == 0)
-				atomicOr(&a.hdr->error, ERR_EXZD_CAP);
-			hdr = X_FAIL;
-			size = 0;
-		}
-	}
-	if (lane == 0) {
-		a.r_nex[r] = nex;
-		a.r_hdr[r] = hdr;
-		a.r_size[r] = size;
-	}
-}
-
 // exclusive scan of the stream sizes -> out_offsets.  One CTA of 1024 threads.
 __global__ void __launch_bounds__(1024) ex_offsets_kernel(const uint64_t *size, uint64_t nreads,
 							  uint64_t *out_offsets, uint64_t out_cap, Hdr *hdr)
@@ -483,53 +341,6 @@ __global__ void __launch_bounds__(1024) ex_offsets_kernel(const uint64_t *size, 
 	}
 }
 
-// header of every read at its final place.  One warp per read.
-__global__ void __launch_bounds__(NT) ex_header_kernel(const __grid_constant__ ExArgs a)
-{
-	const uint64_t r = ((uint64_t) blockIdx.x * NT + threadIdx.x) >> 5;
-	const int lane = threadIdx.x & 31;
-	if (r >= a.nreads || (a.hdr->error & (ERR_CAPACITY | ERR_SCRATCH)))
-		return;
-	const uint32_t hdr = a.r_hdr[r];
-	if (hdr == X_FAIL)
-		return;
-	const uint32_t g0 = a.tile_start[r], nt = a.tile_start[r + 1] - g0;
-	const uint64_t off0 = a.offsets[r], n = a.offsets[r + 1] - off0;
-	const uint32_t nex = a.r_nex[r];
-	const uint32_t q = a.method == PRESS_GPU_EX_ZD ? a.r_q[r] : 0u;
-	uint8_t *dst = a.out + a.out_offsets[r];
-	if (lane == 0) {
-		const int16_t x0 = reinterpret_cast<const int16_t *>(a.samples)[off0];
-		const int16_t s0 = (int16_t) (x0 >> q);
-		const uint16_t zd0 = (uint16_t) ((uint16_t) (s0 << 1) ^ (uint16_t) (s0 >> 15));	// trans.c:75-78
-		uint8_t *p = dst;
-		if (a.method == PRESS_GPU_EX_ZD) {
-			*p++ = 0;		// ex_zd.c:420-423
-			put_le(p, n, 8);	// ex_zd.c:425-428
-			p += 8;
-			*p++ = (uint8_t) q;	// ex_zd.c:436-439
-		}
-		put_le(p, zd0, 2);
-		put_le(p + 2, nex, 4);
-	}
-	const ExList L = {a.t_eb, a.t_pool, a.pool, g0, nt};
-	const uint32_t fx = ex_fixed_bytes(a.method);
-	const uint32_t ll = ex_lists<true>(a.method, L, nex, dst + fx, lane);
-	if (a.method == PRESS_GPU_SHUFF_VBE21_ZD) {
-		const uint32_t cnt = (uint32_t) (n - 1 - nex);
-		uint8_t *p = dst + fx + ll;
-		if (lane < 4)
-			p[lane] = (uint8_t) (cnt >> (8 * (3 - lane)));	// htonl, huffman.c:1199
-		// bytes shared by two tiles' bit ranges are OR-ed in by the emit sweep: clear them
-		uint8_t *bs = p + 4;
-		for (uint32_t t = 1 + lane; t < nt; t += 32) {
-			const uint32_t b = a.t_pb[g0 + t];
-			if (b & 7)
-				bs[b >> 3] = 0;
-		}
-	}
-}
-
 // ---------------------------------------------------------------------------
 // sweep 2: payload
 
@@ -564,90 +375,285 @@ __device__ __forceinline__ void block_copy_out(const uint8_t *stage, uint8_t *ds
 	}
 }
 
-template <bool HUFF>
-__global__ void __launch_bounds__(NT) ex_emit_kernel(const __grid_constant__ ExArgs a)
+// per-read geometry of the walk
+__device__ __forceinline__ bool ex_read_tile0(const ExArgs &a, uint64_t r, ExTile &T, uint32_t &g0)
 {
-	__shared__ __align__(16) uint8_t s_stage[X_STAGE];
+	T.r = (uint32_t) r;
+	T.off0 = __ldg(a.offsets + r);
+	T.rend = __ldg(a.offsets + r + 1);
+	T.m = (uint32_t) (T.off0 & 7);
+	g0 = __ldg(a.tile_start + r);
+	T.ntiles = __ldg(a.tile_start + r + 1) - g0;
+	T.t = 0;
+	T.k0 = T.off0 >> 3;
+	return T.rend > T.off0;
+}
+
+// ---------------------------------------------------------------------------
+// sweep 1: counts, exception capture, stream size
+
+template <bool HUFF>
+__global__ void __launch_bounds__(NT, 4) ex_count_kernel(const __grid_constant__ ExArgs a)
+{
 	__shared__ uint32_t s_warp[NW + 1];
-	__shared__ uint32_t s_lut[HUFF ? 256 : 1];
-	const int tid = threadIdx.x;
-	if (a.hdr->error & (ERR_CAPACITY | ERR_SCRATCH))
-		return;
-	if (HUFF) {
-		s_lut[tid] = a.huff_enc[tid];
+	__shared__ uint32_t s_read, s_pool, s_or;
+	__shared__ unsigned long long s_bits;
+	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	for (;;) {
 		__syncthreads();
-	}
-	const uint32_t total = a.hdr->total_tiles;
-	for (uint32_t g = blockIdx.x; g < total; g += gridDim.x) {
+		if (tid == 0) {
+			s_read = atomicAdd(&a.hdr->ticket, 1u);
+			s_or = 0;
+			s_bits = 0;
+		}
+		__syncthreads();
+		const uint64_t r = s_read;
+		if (r >= a.nreads)
+			break;
 		ExTile T;
-		ex_tile_info(a.tile_start, a.tile_read, a.offsets, g, T);
-		const uint32_t hdr = a.r_hdr[T.r];
-		if (hdr == X_FAIL)
-			continue;
-		const uint32_t q = a.method == PRESS_GPU_EX_ZD ? a.r_q[T.r] : 0u;
-		ExVals v;
-		ex_load_zd(a.samples, a.nsamples, T, q, v);
-		const uint32_t ne = v.valid & ~v.exc & ~v.first;
-		uint8_t *pay = a.out + a.out_offsets[T.r] + hdr;	// first payload byte of the read
-		if (!HUFF) {
-			uint32_t c1[1] = {(uint32_t) __popc(ne)}, ex1[1], tot;
-			block_scan<1>(c1, ex1, tot, s_warp);
-			if (ne == 0xffffu && (ex1[0] & 7) == 0) {
-				uint2 *p = reinterpret_cast<uint2 *>(s_stage + ex1[0]);
-				p[0] = make_uint2(__byte_perm(v.z[0], v.z[1], 0x6420), __byte_perm(v.z[2], v.z[3], 0x6420));
-				p[1] = make_uint2(__byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420));
-			} else {
-				uint8_t *p = s_stage + ex1[0];
-				for (uint32_t mk = ne; mk; mk &= mk - 1)
-					*p++ = (uint8_t) ex_elem(v, __ffs(mk) - 1);
+		uint32_t g0;
+		if (!ex_read_tile0(a, r, T, g0)) {	// empty read: no stream (the reference underflows, press.c:3426)
+			if (tid == 0) {
+				a.r_nex[r] = 0;
+				a.r_q[r] = 0;
+				a.r_hdr[r] = X_FAIL;
+				a.r_size[r] = 0;
 			}
-			__syncthreads();
-			block_copy_out(s_stage, pay + a.t_pb[g], tot);
-		} else {
-			// code lengths -> bit position of every symbol (huffman.c:848-887: codes back
-			// to back, first bit of the stream in bit 0 of byte 0)
-			uint32_t bits = 0;
+			continue;
+		}
+		const uint64_t n = T.rend - T.off0, A = T.off0 >> 3;
+		const uint32_t nt = T.ntiles;
+		uint32_t q = 0, nex_run = 0, bits_thr = 0;
+		for (int pass = 0; pass < 2; pass++) {
+			nex_run = 0;
+			bits_thr = 0;
+			uint32_t or_thr = 0;
+			ExRaw W;
+			ex_issue(a.samples, a.nsamples, A, W);
+			for (uint32_t t = 0; t < nt; t++) {
+				T.t = t;
+				T.k0 = A + (uint64_t) t * XG;
+				const ExRaw C = W;
+				if (t + 1 < nt)
+					ex_issue(a.samples, a.nsamples, T.k0 + XG, W);
+				ExVals v;
+				ex_compute(C, T, q, v);
+				or_thr |= v.orv;
+				const uint32_t cnt = __popc(v.exc);
+				if (HUFF) {
+					const uint32_t ne = v.valid & ~v.exc & ~v.first;
 #pragma unroll
-			for (int e = 0; e < 16; e++)
-				if ((ne >> e) & 1)
-					bits += s_lut[ex_elem(v, e)] >> 24;
-			uint32_t c1[1] = {bits}, ex1[1], tot;
-			block_scan<1>(c1, ex1, tot, s_warp);
-			// the stage mirrors global memory from the 16-byte word holding the tile's first bit
-			const uint64_t G = 8 * (uint64_t) (pay - a.out) + a.t_pb[g];
-			const uint32_t s0 = (uint32_t) (G & 127);
-			const uint32_t nwords = (s0 + tot + 31) >> 5;
-			uint32_t *sw = reinterpret_cast<uint32_t *>(s_stage);
-			for (uint32_t w = tid; w < nwords + 4; w += NT)
-				sw[w] = 0;
-			__syncthreads();
-			uint32_t pos = s0 + ex1[0];
-			uint64_t acc = 0;	// bits not yet written, starting at bit (pos & ~31)
-			uint32_t nacc = pos & 31;	// bits of acc in use (the low `pos & 31` are other threads')
-			uint32_t word = pos >> 5;
-#pragma unroll
-			for (int e = 0; e < 16; e++) {
-				if ((ne >> e) & 1) {
-					const uint32_t c = s_lut[ex_elem(v, e)];
-					acc |= (uint64_t) (c & 0xffffffu) << nacc;
-					nacc += c >> 24;
-					if (nacc >= 32) {
-						atomicOr(sw + word, (uint32_t) acc);
-						acc >>= 32;
-						nacc -= 32;
-						word++;
+					for (int e = 0; e < 16; e++)
+						if ((ne >> e) & 1)
+							bits_thr += __ldg(a.huff_enc + ex_elem(v, e)) >> 24;
+				}
+				uint32_t tile_nex = 0;
+				if (__syncthreads_or(cnt)) {	// capture, in order
+					uint32_t c1[1] = {cnt}, ex1[1];
+					block_scan<1>(c1, ex1, tile_nex, s_warp);
+					if (tid == 0)
+						s_pool = (uint32_t) atomicAdd((unsigned long long *) &a.hdr->aux[0],
+									      (unsigned long long) tile_nex);
+					__syncthreads();
+					const uint64_t base = s_pool;
+					if (base + tile_nex <= a.pool_cap) {
+						uint2 *p = a.pool + base + ex1[0];
+						for (uint32_t mk = v.exc; mk; mk &= mk - 1) {
+							const int e = __ffs(mk) - 1;
+							*p++ = make_uint2((uint32_t) (v.i0 + e - 1), ex_elem(v, e));
+						}
+					} else if (tid == 0) {
+						atomicOr(&a.hdr->error, ERR_SCRATCH);
 					}
 				}
+				if (tid == 0) {
+					a.t_nex[g0 + t] = tile_nex;
+					a.t_pool[g0 + t] = tile_nex ? s_pool : 0;
+					a.t_eb[g0 + t] = nex_run;
+				}
+				nex_run += tile_nex;
 			}
-			if (acc)
-				atomicOr(sw + word, (uint32_t) acc);
+			if (a.method != PRESS_GPU_EX_ZD || pass == 1)
+				break;
+			// ex_zd.c:358-381: q from the OR of all samples (a zero sample never lowers q; cap 5)
+			or_thr = __reduce_or_sync(0xffffffffu, or_thr);
+			if (lane == 0 && or_thr)
+				atomicOr(&s_or, or_thr);
 			__syncthreads();
-			if (tot) {
+			q = __ffs(s_or | 32u) - 1;
+			if (q == 0)
+				break;
+		}
+		if (HUFF) {
+			const uint32_t wb = __reduce_add_sync(0xffffffffu, bits_thr);
+			if (lane == 0)
+				atomicAdd(&s_bits, (unsigned long long) wb);
+		}
+		__syncthreads();	// the tile records above are read by warp 0 below
+		if (warp == 0) {
+			const uint32_t nex = nex_run;
+			uint32_t hdr = X_FAIL;
+			uint64_t size = 0;
+			if (!(a.hdr->error & ERR_SCRATCH)) {
+				const ExList L = {a.t_eb, a.t_pool, a.pool, g0, nt};
+				hdr = ex_fixed_bytes(a.method) + ex_lists<false>(a.method, L, nex, nullptr, lane);
+				if (HUFF) {
+					hdr += 4;	// [count u32 BE], huffman.c:1199-1203
+					size = hdr + (s_bits + 7) / 8;
+				} else {
+					size = hdr + (n - 1 - nex);
+				}
+				if (a.method == PRESS_GPU_EX_ZD && size > 2 * n + 1024) {	// ex_zd.c:411 scratch cap
+					if (lane == 0)
+						atomicOr(&a.hdr->error, ERR_EXZD_CAP);
+					hdr = X_FAIL;
+					size = 0;
+				}
+			}
+			if (lane == 0) {
+				a.r_nex[r] = nex;
+				a.r_q[r] = q;
+				a.r_hdr[r] = hdr;
+				a.r_size[r] = size;
+			}
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------
+// sweep 2: header + payload
+
+template <bool HUFF>
+__global__ void __launch_bounds__(NT, 4) ex_emit_kernel(const __grid_constant__ ExArgs a)
+{
+	__shared__ __align__(16) uint8_t s_stage[HUFF ? X_STAGE : XT + 64];
+	__shared__ uint32_t s_warp[NW + 1];
+	__shared__ uint32_t s_lut[HUFF ? 256 : 1];
+	__shared__ uint32_t s_read;
+	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	if (a.hdr->error & (ERR_CAPACITY | ERR_SCRATCH))
+		return;
+	if (HUFF)
+		s_lut[tid] = a.huff_enc[tid];
+	for (;;) {
+		__syncthreads();
+		if (tid == 0)
+			s_read = atomicAdd(&a.hdr->ticket2, 1u);
+		__syncthreads();
+		const uint64_t r = s_read;
+		if (r >= a.nreads)
+			break;
+		const uint32_t hdr = a.r_hdr[r];
+		if (hdr == X_FAIL)
+			continue;
+		ExTile T;
+		uint32_t g0;
+		(void) ex_read_tile0(a, r, T, g0);
+		const uint64_t n = T.rend - T.off0, A = T.off0 >> 3;
+		const uint32_t nt = T.ntiles, nex = a.r_nex[r];
+		const uint32_t q = a.method == PRESS_GPU_EX_ZD ? a.r_q[r] : 0u;
+		uint8_t *dst = a.out + a.out_offsets[r];
+		ExRaw W;
+		ex_issue(a.samples, a.nsamples, A, W);
+		if (warp == 0) {	// the header, while the first tile is on its way
+			if (lane == 0) {
+				const int16_t x0 = reinterpret_cast<const int16_t *>(a.samples)[T.off0];
+				const uint16_t s0 = (uint16_t) (int16_t) (x0 >> q);
+				const uint16_t zd0 = (uint16_t) ((uint16_t) (s0 << 1) ^ (uint16_t) (0 - (s0 >> 15)));	// trans.c:75-78
+				uint8_t *p = dst;
+				if (a.method == PRESS_GPU_EX_ZD) {
+					*p++ = 0;		// ex_zd.c:420-423
+					put_le(p, n, 8);	// ex_zd.c:425-428
+					p += 8;
+					*p++ = (uint8_t) q;	// ex_zd.c:436-439
+				}
+				put_le(p, zd0, 2);
+				put_le(p + 2, nex, 4);
+			}
+			const ExList L = {a.t_eb, a.t_pool, a.pool, g0, nt};
+			const uint32_t fx = ex_fixed_bytes(a.method);
+			const uint32_t ll = ex_lists<true>(a.method, L, nex, dst + fx, lane);
+			if (HUFF && lane < 4) {
+				const uint32_t cnt = (uint32_t) (n - 1 - nex);
+				dst[fx + ll + lane] = (uint8_t) (cnt >> (8 * (3 - lane)));	// htonl, huffman.c:1199
+			}
+		}
+		uint8_t *pay = dst + hdr;	// first payload byte of the read
+		uint64_t pos = 0;		// payload bytes (bits when HUFF) written so far
+		uint32_t carryb = 0;		// HUFF: the bits of the last, still partial byte
+		for (uint32_t t = 0; t < nt; t++) {
+			T.t = t;
+			T.k0 = A + (uint64_t) t * XG;
+			const ExRaw C = W;
+			if (t + 1 < nt)
+				ex_issue(a.samples, a.nsamples, T.k0 + XG, W);
+			ExVals v;
+			ex_compute(C, T, q, v);
+			const uint32_t ne = v.valid & ~v.exc & ~v.first;
+			if (!HUFF) {
+				uint32_t c1[1] = {(uint32_t) __popc(ne)}, ex1[1], tot;
+				block_scan<1>(c1, ex1, tot, s_warp);
+				if (ne == 0xffffu && (ex1[0] & 7) == 0) {
+					uint2 *p = reinterpret_cast<uint2 *>(s_stage + ex1[0]);
+					p[0] = make_uint2(__byte_perm(v.z[0], v.z[1], 0x6420), __byte_perm(v.z[2], v.z[3], 0x6420));
+					p[1] = make_uint2(__byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420));
+				} else {
+					uint8_t *p = s_stage + ex1[0];
+#pragma unroll
+					for (int e = 0; e < 16; e++)
+						if ((ne >> e) & 1)
+							*p++ = (uint8_t) ex_elem(v, e);
+				}
+				__syncthreads();
+				block_copy_out(s_stage, pay + pos, tot);
+				pos += tot;
+			} else {
+				// code lengths -> bit position of every symbol (huffman.c:848-887: codes back
+				// to back, first bit of the stream in bit 0 of byte 0)
+				uint32_t bits = 0;
+#pragma unroll
+				for (int e = 0; e < 16; e++)
+					if ((ne >> e) & 1)
+						bits += s_lut[ex_elem(v, e)] >> 24;
+				uint32_t c1[1] = {bits}, ex1[1], tot;
+				block_scan<1>(c1, ex1, tot, s_warp);
+				// the stage mirrors global memory from the 16-byte word holding the tile's first bit
+				const uint64_t G = 8 * (uint64_t) (pay - a.out) + pos;
+				const uint32_t s0 = (uint32_t) (G & 127), e0 = s0 + tot;
+				const uint32_t nwords = (e0 + 31) >> 5;
+				uint32_t *sw = reinterpret_cast<uint32_t *>(s_stage);
+				for (uint32_t w = tid; w < nwords + 4; w += NT)
+					sw[w] = 0;
+				__syncthreads();
+				if (tid == 0 && carryb)	// the earlier tiles' bits of the first byte
+					atomicOr(sw + (s0 >> 5), carryb << (8 * ((s0 >> 3) & 3)));
+				uint32_t bp = s0 + ex1[0];
+				uint64_t acc = 0;	// bits not yet written, bit 0 = stage bit (bp & ~31)
+				uint32_t nacc = bp & 31, word = bp >> 5;
+#pragma unroll
+				for (int e = 0; e < 16; e++) {
+					if ((ne >> e) & 1) {
+						const uint32_t c = s_lut[ex_elem(v, e)];
+						acc |= (uint64_t) (c & 0xffffffu) << nacc;
+						nacc += c >> 24;
+						if (nacc >= 32) {
+							atomicOr(sw + word, (uint32_t) acc);
+							acc >>= 32;
+							nacc -= 32;
+							word++;
+						}
+					}
+				}
+				if (acc)
+					atomicOr(sw + word, (uint32_t) acc);
+				__syncthreads();
+				const bool last = t + 1 == nt;
 				uint8_t *gb = a.out + ((G >> 7) << 4);	// global address of stage byte 0
-				const uint32_t e0 = s0 + tot;		// stage bit range [s0, e0)
-				const uint32_t fb = (s0 + 7) >> 3, lb = e0 >> 3;	// wholly owned bytes [fb, lb)
+				// bytes [fb, lb) are complete: the first one thanks to the carried bits, the
+				// last partial one only at the end of the stream (zero padded, huffman.c:886)
+				const uint32_t fb = s0 >> 3, lb = (e0 >> 3) + ((last && (e0 & 7)) ? 1 : 0);
 				if (lb > fb) {
-					const uint32_t w0 = (fb + 15) >> 4, w1 = lb >> 4;	// wholly owned 16-byte words
+					const uint32_t w0 = (fb + 15) >> 4, w1 = lb >> 4;	// wholly covered 16-byte words
 					if (w1 > w0) {
 						for (uint32_t w = w0 + tid; w < w1; w += NT)
 							reinterpret_cast<uint4 *>(gb)[w] = reinterpret_cast<const uint4 *>(s_stage)[w];
@@ -660,28 +666,11 @@ __global__ void __launch_bounds__(NT) ex_emit_kernel(const __grid_constant__ ExA
 							gb[b] = s_stage[b];
 					}
 				}
-				if (tid == 0) {
-					// partial bytes: shared with the neighbouring tiles, OR-ed into bytes the
-					// header kernel cleared; the stream's last byte belongs to the last tile
-					const bool head = (s0 & 7) != 0, tail = (e0 & 7) != 0;
-					const uint32_t hb = s0 >> 3, tb = e0 >> 3;
-					auto or_byte = [&](uint32_t b) {
-						uint8_t *p = gb + b;
-						const uintptr_t al = reinterpret_cast<uintptr_t>(p) & 3;
-						atomicOr(reinterpret_cast<uint32_t *>(p - al), (uint32_t) s_stage[b] << (8 * al));
-					};
-					if (head)
-						or_byte(hb);
-					if (tail && !(head && tb == hb)) {
-						if (T.t + 1 == T.ntiles)
-							gb[tb] = s_stage[tb];
-						else
-							or_byte(tb);
-					}
-				}
+				carryb = (!last && (e0 & 7)) ? s_stage[e0 >> 3] : 0u;
+				pos += tot;
 			}
+			__syncthreads();
 		}
-		__syncthreads();
 	}
 }
 

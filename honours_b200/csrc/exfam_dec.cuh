@@ -5,12 +5,10 @@
 //                      decoded into a pool (sorted positions, values)
 //   huff_decode(read)  SHUFF only: bitstream -> one-byte symbols in a scratch payload
 //                      (self-synchronising parallel decode, see below)
-//   ex_sum     (tile)  payload + exceptions -> sum of the tile's deltas (mod 2^16)
-//   ex_decode  (tile)  payload + exceptions -> unzigzag -> running sum carried in from
-//                      the sums of the read's earlier tiles -> << q -> samples
-//
-// The inverse delta (trans.c:260-270, a serial running sum in the reference) is the
-// only loop-carried value; it costs one extra read of the 1-byte payload.
+//   ex_decode  (read)  one CTA walks one read tile by tile: payload + exceptions ->
+//                      unzigzag -> running sum (trans.c:260-270) carried by the CTA from
+//                      tile to tile -> << q -> samples; the next tile's payload bytes
+//                      are requested before the current tile is processed
 #pragma once
 
 #include "exfam.cuh"
@@ -27,7 +25,6 @@ struct ExDecArgs {
 	int16_t *samples_out;		// 16-byte aligned
 	Hdr *hdr;			// aux[0] = pool entries used, ticket = next read (huff_decode)
 	const uint32_t *tile_start, *tile_read;
-	uint32_t *t_sum;
 	uint32_t *r_nex, *r_q, *r_zd0, *r_pool;
 	uint64_t *r_pay;		// byte offset of the payload / bitstream in `in`; SENTINEL: bad read
 	uint2 *pool;
@@ -36,6 +33,19 @@ struct ExDecArgs {
 	const uint16_t *huff_dec;	// 2048 x (length << 8 | symbol), 0 = longer than 11 bits
 	const int16_t *huff_tree;	// child[node][bit]: > 0 node, <= 0 leaf -symbol... see huff.cuh
 };
+
+// 16-byte word `w` of the 16-byte aligned region starting at `base16`, bytes outside [lo, hi) read as 0
+__device__ __forceinline__ uint4 load_word_guarded(const uint8_t *base16, uint32_t w, const uint8_t *lo, const uint8_t *hi)
+{
+	const uint8_t *p = base16 + 16ull * w;
+	if (p >= lo && p + 16 <= hi)
+		return __ldg(reinterpret_cast<const uint4 *>(p));
+	uint32_t v[4] = {0, 0, 0, 0};
+	for (int b = 0; b < 16; b++)
+		if (p + b >= lo && p + b < hi)
+			v[b >> 2] |= (uint32_t) p[b] << (8 * (b & 3));
+	return make_uint4(v[0], v[1], v[2], v[3]);
+}
 
 __device__ __forceinline__ uint64_t get_le(const uint8_t *p, int nbytes)
 {
@@ -329,7 +339,9 @@ __global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__
 			if (act)
 				ex = hd_run(s_w, s_lut, a.huff_tree, lo + cur, hi, cnt, nullptr, 0) - hi;
 			s_exit[tid] = ex;
+			uint32_t rounds = 0;
 			for (;;) {
+				rounds++;
 				__syncthreads();
 				const uint32_t e = tid ? s_exit[tid - 1] : entry;
 				const bool ch = act && e != cur;
@@ -358,6 +370,10 @@ __global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__
 			}
 			entry = s_exit[nsub - 1];
 			done += tot;
+			if (tid == 0) {	// statistics: steps and re-synchronisation rounds (press_gpu_debug_aux)
+				atomicAdd((unsigned long long *) &a.hdr->aux[1], 1ull);
+				atomicAdd((unsigned long long *) &a.hdr->aux[2], (unsigned long long) rounds);
+			}
 			__syncthreads();
 		}
 		if (done < count && tid == 0)
@@ -366,207 +382,173 @@ __global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__
 }
 
 // ---------------------------------------------------------------------------
-// tile sweeps
+// payload + exceptions -> samples
 
-// Stage global bytes [src, src + len) at stage[(src & 15) + i].  One CTA.
-__device__ __forceinline__ void block_copy_in(uint8_t *stage, const uint8_t *src, uint32_t len,
-					      const uint8_t *base, const uint8_t *limit)
+__global__ void __launch_bounds__(NT, 4) ex_decode_kernel(const __grid_constant__ ExDecArgs a)
 {
-	const uint32_t a = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
-	const uint8_t *gb = src - a;
-	const uint32_t end = a + len;
-	const uint32_t nw = (end + 15) >> 4;
-	for (uint32_t w = threadIdx.x; w < nw; w += NT) {
-		const uint8_t *gp = gb + 16 * w;
-		if (gp >= base && gp + 16 <= limit) {
-			reinterpret_cast<uint4 *>(stage)[w] = __ldg(reinterpret_cast<const uint4 *>(gp));
-		} else {
-			const uint32_t lo = 16 * w, b0 = lo < a ? a : lo, b1 = lo + 16 > end ? end : lo + 16;
-			for (uint32_t b = b0; b < b1; b++)
-				stage[b] = gb[b];
-		}
-	}
-}
-
-struct ExDecShared {
-	alignas(16) uint8_t stage[XT + 48];
-	uint32_t warp[NW + 1];
-	uint32_t e_lo, e_hi, carry;
-};
-
-// zd values of the thread's 16 elements (two per word, 0 for elements outside the
-// read); returns false when the tile's read is bad.  Contains CTA barriers.
-__device__ __forceinline__ bool ex_tile_values(const ExDecArgs &a, const ExTile &T, uint32_t g,
-					       ExDecShared &sm, bool want_carry, uint32_t (&zz)[8],
-					       uint32_t &valid, uint32_t &q)
-{
-	const int tid = threadIdx.x, lane = tid & 31;
-	const uint64_t pay0 = a.r_pay[T.r];
-	if (pay0 == SENTINEL)
-		return false;
-	const uint64_t n = T.rend - T.off0;
-	const uint32_t nex = a.r_nex[T.r];
-	const uint2 *ex = a.pool + a.r_pool[T.r];
-	q = a.r_q[T.r];
-	const uint32_t j_lo = ex_v_before(T.t, T.m, n), j_hi = ex_v_before(T.t + 1, T.m, n);
-	if (tid == 0)
-		sm.carry = 0;
-	__syncthreads();
-	if (tid < 2) {	// exceptions before the tile / before its end: lower_bound on the positions
-		const uint32_t key = tid ? j_hi : j_lo;
-		uint32_t lo = 0, hi = nex;
-		while (lo < hi) {
-			const uint32_t mid = (lo + hi) >> 1;
-			if (ex[mid].x < key)
-				lo = mid + 1;
-			else
-				hi = mid;
-		}
-		(tid ? sm.e_hi : sm.e_lo) = lo;
-	}
-	if (want_carry) {	// sum of the deltas of the read's earlier tiles
-		const uint32_t g0 = g - T.t;
-		uint32_t s = 0;
-		for (uint32_t h = g0 + tid; h < g; h += NT)
-			s += a.t_sum[h];
-		s = __reduce_add_sync(0xffffffffu, s);
-		if (lane == 0 && s)
-			atomicAdd(&sm.carry, s);
-	}
-	__syncthreads();
-	const uint32_t e_lo = sm.e_lo, e_hi = sm.e_hi;
-	const uint32_t p_lo = j_lo - e_lo, plen = (j_hi - e_hi) - p_lo;
-	const uint8_t *pbase = a.method == PRESS_GPU_SHUFF_VBE21_ZD ? a.paybuf + T.off0 : a.in + pay0;
-	const uint8_t *src = pbase + p_lo;
-	const bool shuff = a.method == PRESS_GPU_SHUFF_VBE21_ZD;
-	block_copy_in(sm.stage, src, plen, shuff ? a.paybuf : a.in,
-		      shuff ? a.paybuf + ((a.offsets[a.nreads] + 15) & ~15ull) : a.in + a.in_bytes);
-	__syncthreads();
-	const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
-	const uint64_t ka = T.k0 + 2 * tid;
-	valid = group_valid(ka, T.off0, T.rend) | (group_valid(ka + 1, T.off0, T.rend) << 8);
-	const int64_t i0 = (int64_t) (8 * ka) - (int64_t) T.off0;
-#pragma unroll
-	for (int j = 0; j < 8; j++)
-		zz[j] = 0;
-	if (valid) {
-		const int64_t jf = i0 + (__ffs(valid) - 1) - 1;	// v-index of the first valid element (-1: zd0)
-		uint32_t e = e_lo;
-		if (e_hi > e_lo) {
-			uint32_t lo = e_lo, hi = e_hi;
-			const int64_t key = jf < 0 ? 0 : jf;
-			while (lo < hi) {
-				const uint32_t mid = (lo + hi) >> 1;
-				if ((int64_t) ex[mid].x < key)
-					lo = mid + 1;
-				else
-					hi = mid;
-			}
-			e = lo;
-		}
-		uint32_t nextpos = e < e_hi ? ex[e].x : 0xffffffffu;
-		const uint8_t *st = sm.stage + al;
-#pragma unroll
-		for (int el = 0; el < 16; el++) {
-			if ((valid >> el) & 1) {
-				const int64_t j = i0 + el - 1;
-				uint32_t z;
-				if (j < 0) {
-					z = a.r_zd0[T.r];
-				} else if ((uint32_t) j == nextpos) {
-					z = ex[e].y;
-					e++;
-					nextpos = e < e_hi ? ex[e].x : 0xffffffffu;
-				} else {
-					z = st[(uint32_t) j - e - p_lo];
-				}
-				zz[el >> 1] |= (z & 0xffffu) << (16 * (el & 1));
-			}
-		}
-	}
-	return true;
-}
-
-__global__ void __launch_bounds__(NT) ex_sum_kernel(const __grid_constant__ ExDecArgs a)
-{
-	__shared__ ExDecShared sm;
-	__shared__ uint32_t s_sum;
-	const int tid = threadIdx.x, lane = tid & 31;
-	const uint32_t total = a.hdr->total_tiles;
-	for (uint32_t g = blockIdx.x; g < total; g += gridDim.x) {
-		ExTile T;
-		ex_tile_info(a.tile_start, a.tile_read, a.offsets, g, T);
-		if (T.ntiles == 1)
-			continue;	// nobody reads the sum of a single-tile read
-		if (tid == 0)
-			s_sum = 0;
-		uint32_t zz[8], valid, q;
-		if (!ex_tile_values(a, T, g, sm, false, zz, valid, q)) {
-			if (tid == 0)
-				a.t_sum[g] = 0;
-			continue;
-		}
-		uint32_t s = 0;
-#pragma unroll
-		for (int j = 0; j < 8; j++) {
-			const uint32_t d = unzigzag16x2(zz[j]);
-			s += (d & 0xffffu) + (d >> 16);
-		}
-		s = __reduce_add_sync(0xffffffffu, s);
-		if (lane == 0)
-			atomicAdd(&s_sum, s);
-		__syncthreads();
-		if (tid == 0)
-			a.t_sum[g] = s_sum & 0xffffu;
-		__syncthreads();
-	}
-}
-
-__global__ void __launch_bounds__(NT) ex_decode_kernel(const __grid_constant__ ExDecArgs a)
-{
-	__shared__ ExDecShared sm;
+	__shared__ __align__(16) uint8_t s_stage[XT + 64];
+	__shared__ uint32_t s_warp[NW + 1];
+	__shared__ uint32_t s_read, s_e;
 	const int tid = threadIdx.x;
-	const uint32_t total = a.hdr->total_tiles;
+	const bool shuff = a.method == PRESS_GPU_SHUFF_VBE21_ZD;
+	const uint8_t *lim_lo = shuff ? a.paybuf : a.in;
+	const uint8_t *lim_hi = shuff ? a.paybuf + ((a.offsets[a.nreads] + 15) & ~15ull) : a.in + a.in_bytes;
 	uint4 *out4 = reinterpret_cast<uint4 *>(a.samples_out);
 	uint16_t *out16 = reinterpret_cast<uint16_t *>(a.samples_out);
-	for (uint32_t g = blockIdx.x; g < total; g += gridDim.x) {
-		ExTile T;
-		ex_tile_info(a.tile_start, a.tile_read, a.offsets, g, T);
-		uint32_t zz[8], valid, q;
-		if (!ex_tile_values(a, T, g, sm, T.t > 0, zz, valid, q))
-			continue;
-		// running sum inside the thread (mod 2^16 in each half), decode_scalar.hpp:10-13 + trans.c:260-270
-		uint32_t y[8], carry = 0;
-#pragma unroll
-		for (int j = 0; j < 8; j++) {
-			const uint32_t d = unzigzag16x2(zz[j]);
-			y[j] = add16x2(d * 0x00010001u, carry);
-			carry = __byte_perm(y[j], 0, 0x3232);
-		}
-		uint32_t c1[1] = {carry & 0xffffu}, ex1[1], tot;
-		block_scan<1>(c1, ex1, tot, sm.warp);
-		const uint32_t cw = ((ex1[0] + sm.carry) & 0xffffu) * 0x00010001u;
-		uint32_t o[8];
-#pragma unroll
-		for (int j = 0; j < 8; j++) {
-			o[j] = add16x2(y[j], cw);
-			if (q)
-				o[j] = shl16x2(o[j], q);	// ex_zd.c:396-401
-		}
-		const uint64_t ka = T.k0 + 2 * tid;
-#pragma unroll
-		for (int h = 0; h < 2; h++) {
-			const uint32_t vm = (valid >> (8 * h)) & 0xffu;
-			if (vm == 0xffu) {
-				out4[ka + h] = make_uint4(o[4 * h], o[4 * h + 1], o[4 * h + 2], o[4 * h + 3]);
-			} else if (vm) {
-#pragma unroll
-				for (int e = 0; e < 8; e++)
-					if ((vm >> e) & 1)
-						out16[8 * (ka + h) + e] = (uint16_t) (o[4 * h + (e >> 1)] >> (16 * (e & 1)));
-			}
-		}
+	for (;;) {
 		__syncthreads();
+		if (tid == 0)
+			s_read = atomicAdd(&a.hdr->ticket2, 1u);
+		__syncthreads();
+		const uint64_t r = s_read;
+		if (r >= a.nreads)
+			break;
+		const uint64_t pay0 = a.r_pay[r];
+		if (pay0 == SENTINEL)
+			continue;
+		const uint64_t off0 = __ldg(a.offsets + r), rend = __ldg(a.offsets + r + 1), n = rend - off0;
+		const uint32_t m = (uint32_t) (off0 & 7);
+		const uint64_t A = off0 >> 3;
+		const uint32_t nt = (uint32_t) ((m + n + XT - 1) / XT);
+		const uint32_t nex = a.r_nex[r], q = a.r_q[r], zd0 = a.r_zd0[r];
+		const uint2 *ex = a.pool + a.r_pool[r];
+		const uint8_t *pbase = shuff ? a.paybuf + off0 : a.in + pay0;
+
+		// payload bytes of a tile -> registers (word tid, and word 256 in thread 0)
+		uint4 dreg[2];
+		auto issue = [&](uint32_t t, uint32_t e_lo) {
+			const uint32_t j_lo = ex_v_before(t, m, n), j_hi = ex_v_before(t + 1, m, n);
+			const uint8_t *src = pbase + (j_lo - e_lo);
+			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
+			const uint32_t nw = (al + (j_hi - j_lo) + 15) >> 4;	// (a few bytes more than needed when
+			const uint8_t *b16 = src - al;				//  the tile holds exceptions)
+			if ((uint32_t) tid < nw)
+				dreg[0] = load_word_guarded(b16, tid, lim_lo, lim_hi);
+			if (tid == 0 && nw > NT)
+				dreg[1] = load_word_guarded(b16, NT, lim_lo, lim_hi);
+		};
+		uint32_t e_lo = 0, carry = 0;
+		issue(0, 0);
+		for (uint32_t t = 0; t < nt; t++) {
+			const uint32_t j_lo = ex_v_before(t, m, n), j_hi = ex_v_before(t + 1, m, n);
+			const uint32_t p_lo = j_lo - e_lo;
+			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(pbase + p_lo) & 15);
+			{
+				const uint32_t nw = (al + (j_hi - j_lo) + 15) >> 4;
+				if ((uint32_t) tid < nw)
+					reinterpret_cast<uint4 *>(s_stage)[tid] = dreg[0];
+				if (tid == 0 && nw > NT)
+					reinterpret_cast<uint4 *>(s_stage)[NT] = dreg[1];
+			}
+			if (nex && tid == 0) {	// exceptions before the end of this tile: lower_bound on the positions
+				uint32_t lo = e_lo, hi = nex;
+				while (lo < hi) {
+					const uint32_t mid = (lo + hi) >> 1;
+					if (ex[mid].x < j_hi)
+						lo = mid + 1;
+					else
+						hi = mid;
+				}
+				s_e = lo;
+			}
+			__syncthreads();
+			const uint32_t e_hi = nex ? s_e : 0u;
+			if (t + 1 < nt)
+				issue(t + 1, e_hi);
+			// ---- zd values of the thread's 16 elements
+			const uint64_t ka = A + (uint64_t) t * XG + 2 * tid;
+			const uint32_t valid = group_valid(ka, off0, rend) | (group_valid(ka + 1, off0, rend) << 8);
+			const int64_t i0 = (int64_t) (8 * ka) - (int64_t) off0;
+			uint32_t zz[8];
+			const uint8_t *st = s_stage + al;
+			if (valid == 0xffffu && e_hi == e_lo && i0 > 0) {
+				// 16 payload bytes from stage offset (i0 - 1 - e_lo) - p_lo
+				const uint32_t pp = al + ((uint32_t) (i0 - 1) - e_lo - p_lo);
+				const uint32_t *w32 = reinterpret_cast<const uint32_t *>(s_stage) + (pp >> 2);
+				const uint32_t sh = (pp & 3) * 8;
+				uint32_t w[5];
+#pragma unroll
+				for (int j = 0; j < 5; j++)
+					w[j] = w32[j];
+#pragma unroll
+				for (int j = 0; j < 4; j++) {
+					const uint32_t v = __funnelshift_r(w[j], w[j + 1], sh);
+					zz[2 * j] = __byte_perm(v, 0, 0x4140);
+					zz[2 * j + 1] = __byte_perm(v, 0, 0x4342);
+				}
+			} else {
+#pragma unroll
+				for (int j = 0; j < 8; j++)
+					zz[j] = 0;
+				if (valid) {
+					const int64_t jf = i0 + (__ffs(valid) - 1) - 1;	// v-index of the first valid element (-1: zd0)
+					uint32_t e = e_lo;
+					if (e_hi > e_lo) {
+						uint32_t lo = e_lo, hi = e_hi;
+						const int64_t key = jf < 0 ? 0 : jf;
+						while (lo < hi) {
+							const uint32_t mid = (lo + hi) >> 1;
+							if ((int64_t) ex[mid].x < key)
+								lo = mid + 1;
+							else
+								hi = mid;
+						}
+						e = lo;
+					}
+					uint32_t nextpos = e < e_hi ? ex[e].x : 0xffffffffu;
+#pragma unroll
+					for (int el = 0; el < 16; el++) {
+						if ((valid >> el) & 1) {
+							const int64_t j = i0 + el - 1;
+							uint32_t z;
+							if (j < 0) {
+								z = zd0;
+							} else if ((uint32_t) j == nextpos) {
+								z = ex[e].y;
+								e++;
+								nextpos = e < e_hi ? ex[e].x : 0xffffffffu;
+							} else {
+								z = st[(uint32_t) j - e - p_lo];
+							}
+							zz[el >> 1] |= (z & 0xffffu) << (16 * (el & 1));
+						}
+					}
+				}
+			}
+			// ---- unzigzag, running sum inside the thread (mod 2^16 in each half), then over the CTA
+			uint32_t y[8], c = 0;
+#pragma unroll
+			for (int j = 0; j < 8; j++) {
+				const uint32_t d = unzigzag16x2(zz[j]);
+				y[j] = add16x2(d * 0x00010001u, c);
+				c = __byte_perm(y[j], 0, 0x3232);
+			}
+			uint32_t c1[1] = {c & 0xffffu}, ex1[1], tot;
+			block_scan<1>(c1, ex1, tot, s_warp);
+			const uint32_t cw = ((ex1[0] + carry) & 0xffffu) * 0x00010001u;
+			uint32_t o[8];
+#pragma unroll
+			for (int j = 0; j < 8; j++) {
+				o[j] = add16x2(y[j], cw);
+				if (q)
+					o[j] = shl16x2(o[j], q);	// ex_zd.c:396-401
+			}
+#pragma unroll
+			for (int h = 0; h < 2; h++) {
+				const uint32_t vm = (valid >> (8 * h)) & 0xffu;
+				if (vm == 0xffu) {
+					out4[ka + h] = make_uint4(o[4 * h], o[4 * h + 1], o[4 * h + 2], o[4 * h + 3]);
+				} else if (vm) {
+#pragma unroll
+					for (int e = 0; e < 8; e++)
+						if ((vm >> e) & 1)
+							out16[8 * (ka + h) + e] = (uint16_t) (o[4 * h + (e >> 1)] >> (16 * (e & 1)));
+				}
+			}
+			carry = (carry + tot) & 0xffffu;
+			e_lo = e_hi;
+			__syncthreads();
+		}
 	}
 }
 

@@ -21,7 +21,7 @@
 #pragma once
 
 #include "common.cuh"
-#include "exfam.cuh"
+#include "exfam_dec.cuh"
 
 namespace pg {
 
@@ -37,19 +37,6 @@ struct SvbDec2Args {
 	int16_t *samples_out;
 	Hdr *hdr;			// ticket = next read
 };
-
-// 16-byte word `w` of the 16-byte aligned region starting at `base16`, bytes outside [lo, hi) read as 0
-__device__ __forceinline__ uint4 load_word_guarded(const uint8_t *base16, uint32_t w, const uint8_t *lo, const uint8_t *hi)
-{
-	const uint8_t *p = base16 + 16ull * w;
-	if (p >= lo && p + 16 <= hi)
-		return __ldg(reinterpret_cast<const uint4 *>(p));
-	uint32_t v[4] = {0, 0, 0, 0};
-	for (int b = 0; b < 16; b++)
-		if (p + b >= lo && p + b < hi)
-			v[b >> 2] |= (uint32_t) p[b] << (8 * (b & 3));
-	return make_uint4(v[0], v[1], v[2], v[3]);
-}
 
 template <int KEYBITS>
 __device__ __forceinline__ uint32_t dec_thread_flags(const uint8_t *keys, uint64_t nkeys, uint32_t t, int tid)
