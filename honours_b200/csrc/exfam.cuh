@@ -168,6 +168,55 @@ __device__ __forceinline__ void ex_compute(const ExRaw &w, const ExTile &T, uint
 	v.exc = f & v.valid & ~v.first;
 }
 
+// Interior tile (every element is a sample of the read past its first one): no
+// masks.  Returns nonzero iff one of the thread's values is an exception; orw = OR
+// of the raw sample words (for qts).  The instruction count of this path bounds
+// the encode sweeps: they are issue-bound, not HBM-bound, when it is long.
+__device__ __forceinline__ uint32_t ex_compute_fast(const ExRaw &w, uint32_t q, ExVals &v, uint32_t &orw)
+{
+	uint4 xa = w.xa, xb = w.xb;
+	uint32_t prev = __shfl_up_sync(0xffffffffu, xb.w >> 16, 1);
+	if ((threadIdx.x & 31) == 0)
+		prev = w.prev0;
+	orw = xa.x | xa.y | xa.z | xa.w | xb.x | xb.y | xb.z | xb.w;
+	if (q) {
+		xa.x = sar16x2(xa.x, q); xa.y = sar16x2(xa.y, q); xa.z = sar16x2(xa.z, q); xa.w = sar16x2(xa.w, q);
+		xb.x = sar16x2(xb.x, q); xb.y = sar16x2(xb.y, q); xb.z = sar16x2(xb.z, q); xb.w = sar16x2(xb.w, q);
+		prev = sar16x2(prev, q) & 0xffffu;
+	}
+	uint32_t za[4], zb[4];
+	zd_group(xa, prev, -1, za);
+	zd_group(xb, xa.w >> 16, -1, zb);
+#pragma unroll
+	for (int j = 0; j < 4; j++) {
+		v.z[j] = za[j];
+		v.z[4 + j] = zb[j];
+	}
+	v.valid = 0xffffu;
+	v.first = 0;
+	v.orv = 0;
+	const uint32_t hi = (any_high(za) | any_high(zb));
+	v.exc = hi ? (flags_group(za) | (flags_group(zb) << 8)) : 0u;
+	return hi;
+}
+
+// sum of the code lengths of the thread's non-exception values
+__device__ __forceinline__ uint32_t ex_code_bits(const ExVals &v, uint32_t ne, const uint32_t *lut)
+{
+	uint32_t bits = 0;
+	if (ne == 0xffffu) {
+#pragma unroll
+		for (int j = 0; j < 8; j++)
+			bits += (lut[v.z[j] & 0xffffu] >> 24) + (lut[v.z[j] >> 16] >> 24);
+	} else {
+#pragma unroll
+		for (int e = 0; e < 16; e++)
+			if ((ne >> e) & 1)
+				bits += lut[(v.z[e >> 1] >> (16 * (e & 1))) & 0xffffu] >> 24;
+	}
+	return bits;
+}
+
 __device__ __forceinline__ uint32_t ex_elem(const ExVals &v, int e)
 {
 	return (v.z[e >> 1] >> (16 * (e & 1))) & 0xffffu;
@@ -398,7 +447,10 @@ __global__ void __launch_bounds__(NT, 4) ex_count_kernel(const __grid_constant__
 	__shared__ uint32_t s_warp[NW + 1];
 	__shared__ uint32_t s_read, s_pool, s_or;
 	__shared__ unsigned long long s_bits;
+	__shared__ uint32_t s_len[HUFF ? 256 : 1];
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	if (HUFF)
+		s_len[tid] = a.huff_enc[tid];
 	for (;;) {
 		__syncthreads();
 		if (tid == 0) {
@@ -436,17 +488,21 @@ __global__ void __launch_bounds__(NT, 4) ex_count_kernel(const __grid_constant__
 				const ExRaw C = W;
 				if (t + 1 < nt)
 					ex_issue(a.samples, a.nsamples, T.k0 + XG, W);
+				const int64_t f = (int64_t) t * XT - T.m;	// read index of the tile's first element
+				const bool interior = f >= 1 && f + XT <= (int64_t) n;
 				ExVals v;
-				ex_compute(C, T, q, v);
-				or_thr |= v.orv;
-				const uint32_t cnt = __popc(v.exc);
-				if (HUFF) {
-					const uint32_t ne = v.valid & ~v.exc & ~v.first;
-#pragma unroll
-					for (int e = 0; e < 16; e++)
-						if ((ne >> e) & 1)
-							bits_thr += __ldg(a.huff_enc + ex_elem(v, e)) >> 24;
+				if (interior) {
+					uint32_t orw;
+					(void) ex_compute_fast(C, q, v, orw);
+					or_thr |= orw;
+					v.i0 = f + 16 * tid;
+				} else {
+					ex_compute(C, T, q, v);
+					or_thr |= v.orv;
 				}
+				const uint32_t cnt = __popc(v.exc);
+				if (HUFF)
+					bits_thr += ex_code_bits(v, v.valid & ~v.exc & ~v.first, s_len);
 				uint32_t tile_nex = 0;
 				if (__syncthreads_or(cnt)) {	// capture, in order
 					uint32_t c1[1] = {cnt}, ex1[1];
@@ -476,7 +532,7 @@ __global__ void __launch_bounds__(NT, 4) ex_count_kernel(const __grid_constant__
 			if (a.method != PRESS_GPU_EX_ZD || pass == 1)
 				break;
 			// ex_zd.c:358-381: q from the OR of all samples (a zero sample never lowers q; cap 5)
-			or_thr = __reduce_or_sync(0xffffffffu, or_thr);
+			or_thr = __reduce_or_sync(0xffffffffu, (or_thr | (or_thr >> 16)) & 0xffffu);
 			if (lane == 0 && or_thr)
 				atomicOr(&s_or, or_thr);
 			__syncthreads();
@@ -587,12 +643,23 @@ __global__ void __launch_bounds__(NT, 4) ex_emit_kernel(const __grid_constant__ 
 			const ExRaw C = W;
 			if (t + 1 < nt)
 				ex_issue(a.samples, a.nsamples, T.k0 + XG, W);
+			const int64_t f = (int64_t) t * XT - T.m;
+			const bool interior = f >= 1 && f + XT <= (int64_t) n;
 			ExVals v;
-			ex_compute(C, T, q, v);
+			uint32_t hi = 1;
+			if (interior) {
+				uint32_t orw;
+				hi = ex_compute_fast(C, q, v, orw);
+			} else {
+				ex_compute(C, T, q, v);
+			}
 			const uint32_t ne = v.valid & ~v.exc & ~v.first;
 			if (!HUFF) {
-				uint32_t c1[1] = {(uint32_t) __popc(ne)}, ex1[1], tot;
-				block_scan<1>(c1, ex1, tot, s_warp);
+				uint32_t ex1[1] = {16u * tid}, tot = XT;
+				if (__syncthreads_or(hi)) {	// exceptions or a read boundary in the tile: count
+					uint32_t c1[1] = {(uint32_t) __popc(ne)};
+					block_scan<1>(c1, ex1, tot, s_warp);
+				}
 				if (ne == 0xffffu && (ex1[0] & 7) == 0) {
 					uint2 *p = reinterpret_cast<uint2 *>(s_stage + ex1[0]);
 					p[0] = make_uint2(__byte_perm(v.z[0], v.z[1], 0x6420), __byte_perm(v.z[2], v.z[3], 0x6420));
@@ -610,11 +677,7 @@ __global__ void __launch_bounds__(NT, 4) ex_emit_kernel(const __grid_constant__ 
 			} else {
 				// code lengths -> bit position of every symbol (huffman.c:848-887: codes back
 				// to back, first bit of the stream in bit 0 of byte 0)
-				uint32_t bits = 0;
-#pragma unroll
-				for (int e = 0; e < 16; e++)
-					if ((ne >> e) & 1)
-						bits += s_lut[ex_elem(v, e)] >> 24;
+				const uint32_t bits = ex_code_bits(v, ne, s_lut);
 				uint32_t c1[1] = {bits}, ex1[1], tot;
 				block_scan<1>(c1, ex1, tot, s_warp);
 				// the stage mirrors global memory from the 16-byte word holding the tile's first bit

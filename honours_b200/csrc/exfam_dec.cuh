@@ -47,6 +47,27 @@ __device__ __forceinline__ uint4 load_word_guarded(const uint8_t *base16, uint32
 	return make_uint4(v[0], v[1], v[2], v[3]);
 }
 
+// 16 bytes at stage[al + 16 tid ...) (al < 16, the same in every thread) as zd values,
+// two per word: two conflict-free 128-bit loads and a byte shift
+__device__ __forceinline__ void stage_bytes16(const uint8_t *stage, uint32_t al, int tid, uint32_t (&zz)[8])
+{
+	const uint4 a = reinterpret_cast<const uint4 *>(stage)[tid], b = reinterpret_cast<const uint4 *>(stage)[tid + 1];
+	uint32_t u0, u1, u2, u3, u4;
+	switch (al >> 2) {
+	case 0: u0 = a.x; u1 = a.y; u2 = a.z; u3 = a.w; u4 = b.x; break;
+	case 1: u0 = a.y; u1 = a.z; u2 = a.w; u3 = b.x; u4 = b.y; break;
+	case 2: u0 = a.z; u1 = a.w; u2 = b.x; u3 = b.y; u4 = b.z; break;
+	default: u0 = a.w; u1 = b.x; u2 = b.y; u3 = b.z; u4 = b.w; break;
+	}
+	const uint32_t sh = (al & 3) * 8;
+	const uint32_t v0 = __funnelshift_r(u0, u1, sh), v1 = __funnelshift_r(u1, u2, sh);
+	const uint32_t v2 = __funnelshift_r(u2, u3, sh), v3 = __funnelshift_r(u3, u4, sh);
+	zz[0] = __byte_perm(v0, 0, 0x4140); zz[1] = __byte_perm(v0, 0, 0x4342);
+	zz[2] = __byte_perm(v1, 0, 0x4140); zz[3] = __byte_perm(v1, 0, 0x4342);
+	zz[4] = __byte_perm(v2, 0, 0x4140); zz[5] = __byte_perm(v2, 0, 0x4342);
+	zz[6] = __byte_perm(v3, 0, 0x4140); zz[7] = __byte_perm(v3, 0, 0x4342);
+}
+
 __device__ __forceinline__ uint64_t get_le(const uint8_t *p, int nbytes)
 {
 	uint64_t v = 0;
@@ -457,25 +478,16 @@ __global__ void __launch_bounds__(NT, 4) ex_decode_kernel(const __grid_constant_
 				issue(t + 1, e_hi);
 			// ---- zd values of the thread's 16 elements
 			const uint64_t ka = A + (uint64_t) t * XG + 2 * tid;
-			const uint32_t valid = group_valid(ka, off0, rend) | (group_valid(ka + 1, off0, rend) << 8);
-			const int64_t i0 = (int64_t) (8 * ka) - (int64_t) off0;
+			const int64_t f = (int64_t) t * XT - m;		// read index of the tile's first element
+			const bool interior = f >= 1 && f + XT <= (int64_t) n;
+			const uint32_t valid = interior ? 0xffffu
+							: group_valid(ka, off0, rend) | (group_valid(ka + 1, off0, rend) << 8);
+			const int64_t i0 = f + 16 * tid;
 			uint32_t zz[8];
 			const uint8_t *st = s_stage + al;
-			if (valid == 0xffffu && e_hi == e_lo && i0 > 0) {
-				// 16 payload bytes from stage offset (i0 - 1 - e_lo) - p_lo
-				const uint32_t pp = al + ((uint32_t) (i0 - 1) - e_lo - p_lo);
-				const uint32_t *w32 = reinterpret_cast<const uint32_t *>(s_stage) + (pp >> 2);
-				const uint32_t sh = (pp & 3) * 8;
-				uint32_t w[5];
-#pragma unroll
-				for (int j = 0; j < 5; j++)
-					w[j] = w32[j];
-#pragma unroll
-				for (int j = 0; j < 4; j++) {
-					const uint32_t v = __funnelshift_r(w[j], w[j + 1], sh);
-					zz[2 * j] = __byte_perm(v, 0, 0x4140);
-					zz[2 * j + 1] = __byte_perm(v, 0, 0x4342);
-				}
+			if (interior && e_hi == e_lo) {
+				// no exception in the tile: the thread's 16 payload bytes sit at stage[al + 16 tid]
+				stage_bytes16(s_stage, al, tid, zz);
 			} else {
 #pragma unroll
 				for (int j = 0; j < 8; j++)

@@ -162,19 +162,9 @@ __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ 
 			// ---- bytes -> zd values, two per word
 			uint32_t zz[8];
 			const uint32_t p = al + ex_cur;
-			if (va_cur == 0xffffu && fl_cur == 0) {
-				const uint32_t *w32 = reinterpret_cast<const uint32_t *>(s_in) + (p >> 2);
-				const uint32_t sh = (p & 3) * 8;
-				uint32_t w[5];
-#pragma unroll
-				for (int j = 0; j < 5; j++)
-					w[j] = w32[j];
-#pragma unroll
-				for (int j = 0; j < 4; j++) {
-					const uint32_t v = __funnelshift_r(w[j], w[j + 1], sh);
-					zz[2 * j] = __byte_perm(v, 0, 0x4140);
-					zz[2 * j + 1] = __byte_perm(v, 0, 0x4342);
-				}
+			if (L_cur == DT && n - (uint64_t) t * DT >= DT) {
+				// full tile without a two-byte value: the thread's 16 bytes sit at stage[al + 16 tid]
+				stage_bytes16(s_in, al, tid, zz);
 			} else {
 				const uint8_t *q = s_in + p;
 #pragma unroll
