@@ -55,6 +55,7 @@ def parse_args():
     ap.add_argument("--e2e-gb", type=float, default=2.0, help="raw GB of the host-buffer (e2e) sample")
     ap.add_argument("--cpu-reads", type=int, default=4000, help="reads of the CPU-baseline sample")
     ap.add_argument("--cpu-seconds", type=float, default=8.0)
+    ap.add_argument("--len-cap", type=int, default=0, help="diagnostic: clip read lengths (0 = off; not the BASELINE workload)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-verify", action="store_true")
@@ -235,6 +236,8 @@ def run_ours(args):
     # ---- this rank's reads, cut into device-resident chunks of whole reads ----
     first_read = rank * args.reads
     lengths, x0, shift = workload.read_table(args.reads, first_read=first_read)
+    if args.len_cap:
+        lengths = np.minimum(lengths, args.len_cap)
     total_samples = int(lengths.sum())
     nchunks = max(1, math.ceil(2.0 * total_samples / CHUNK_RAW_BYTES))
     cum = np.concatenate([[0], np.cumsum(lengths)])
