@@ -48,14 +48,57 @@ struct GrowBuf {
 	}
 };
 
+// One stage of the host-buffer pipeline (host_pipe.inc): its own stream, device
+// buffers and pinned staging for the chunk's offset tables.
+struct PipeSlot {
+	cudaStream_t st = nullptr;
+	cudaEvent_t ev = nullptr;
+	GrowBuf samples, offsets, in_offsets, out, out_offsets, scratch;
+	uint64_t *h_tab = nullptr;	// pinned: chunk-relative offsets (two tables) + the scratch header
+	size_t h_tab_cap = 0;
+	int reserve_tab(size_t words)
+	{
+		if (words <= h_tab_cap)
+			return 0;
+		if (h_tab)
+			cudaFreeHost(h_tab);
+		h_tab = nullptr;
+		h_tab_cap = 0;
+		if (cudaHostAlloc((void **) &h_tab, (words + 1024) * 8, cudaHostAllocDefault) != cudaSuccess)
+			return -1;
+		h_tab_cap = words + 1024;
+		return 0;
+	}
+	void release()
+	{
+		samples.release(); offsets.release(); in_offsets.release(); out.release();
+		out_offsets.release(); scratch.release();
+		if (h_tab)
+			cudaFreeHost(h_tab);
+		h_tab = nullptr;
+		h_tab_cap = 0;
+		if (ev)
+			cudaEventDestroy(ev);
+		if (st)
+			cudaStreamDestroy(st);
+		ev = nullptr;
+		st = nullptr;
+	}
+};
+
+constexpr int PIPE_SLOTS = 3;
+
 struct HostCtx {
 	bool ready = false;
 	int device = 0;
 	int sms = 0;
 	cudaStream_t stream = nullptr;
 	GrowBuf samples, offsets, out, out_offsets, scratch, misc;
+	PipeSlot slot[PIPE_SLOTS];
 	void release()
 	{
+		for (int i = 0; i < PIPE_SLOTS; i++)
+			slot[i].release();
 		samples.release();
 		offsets.release();
 		out.release();
