@@ -30,8 +30,9 @@ struct ExDecArgs {
 	uint2 *pool;
 	uint64_t pool_cap;
 	uint8_t *paybuf;		// SHUFF: symbols of read r at paybuf + offsets[r]
-	const uint16_t *huff_dec;	// 2048 x (length << 8 | symbol), 0 = longer than 11 bits
-	const int16_t *huff_tree;	// child[node][bit]: > 0 node, <= 0 leaf -symbol... see huff.cuh
+	const uint16_t *huff_dec;	// 4096 x (length << 8 | symbol), or 0x8000 | k: see hd_run
+	const uint16_t *huff_sub;	// second level: [k][1 << huff_sub_bits]
+	uint32_t huff_sub_bits, huff_minlen;
 };
 
 // 16-byte word `w` of the 16-byte aligned region starting at `base16`, bytes outside [lo, hi) read as 0
@@ -270,31 +271,34 @@ __global__ void __launch_bounds__(NT) ex_parse_kernel(const __grid_constant__ Ex
 
 constexpr int HD_SUB = 128;			// bits per sub-block
 constexpr int HD_CHUNK = NT * HD_SUB / 8;	// bytes per step
+constexpr int HD_SLOT = HD_SUB / 4;		// symbols a sub-block can hold when no code is shorter than 4 bits
+constexpr int HD_SYM = NT * HD_SLOT;		// symbol stage
+constexpr int HD_L1 = 12;			// first-level table: 12 bits
 
-// decode codes starting at stage bit `pos` until pos >= end; returns the new pos,
-// adds the symbols seen to cnt; when dst != nullptr stores symbol i at dst[i] for i < lim.
-__device__ __forceinline__ uint32_t hd_run(const uint32_t *sw, const uint16_t *lut, const int16_t *tree,
-					   uint32_t pos, uint32_t end, uint32_t &cnt, uint8_t *dst, int64_t lim)
+// Decode codes starting at stage bit `pos` until pos >= end; returns the new pos and
+// the number of symbols in cnt; stores symbol i at dst[i] for i < lim (dst may be null).
+// Two table levels, no tree walk (a walk taken by one lane stalls the other 31):
+// lut[w & 4095] = length << 8 | symbol for codes of <= 12 bits, else 0x8000 | k, and
+// sub[k][(w >> 12) & mask] resolves the rest of the code.
+// word j of the staged bitstream lives at hd_swz(j): the lanes of a warp work on
+// sub-blocks 4 words apart, this puts their current words in different banks
+constexpr int HD_ROW = NT + 8;
+__device__ __forceinline__ uint32_t hd_swz(uint32_t j) { return (j & 3u) * HD_ROW + (j >> 2); }
+
+template <int STRIDE>	// symbol i goes to dst[i * STRIDE]
+__device__ __forceinline__ uint32_t hd_run(const uint32_t *sw, const uint16_t *lut, const uint16_t *sub,
+					   uint32_t sub_bits, uint32_t pos, uint32_t end, uint32_t &cnt,
+					   uint8_t *dst, uint32_t lim)
 {
 	uint32_t c = 0;
 	while (pos < end) {
-		const uint32_t w = __funnelshift_r(sw[pos >> 5], sw[(pos >> 5) + 1], pos & 31);
-		uint32_t e = lut[w & 2047u];
-		if (e == 0) {	// code longer than 11 bits: walk the tree
-			int node = 0;
-			uint32_t l = 0;
-			for (;;) {
-				const int nx = tree[2 * node + ((w >> l) & 1u)];
-				l++;
-				if (nx <= 0) {
-					e = (l << 8) | (uint32_t) (-nx);
-					break;
-				}
-				node = nx;
-			}
-		}
-		if (dst && (int64_t) c < lim)
-			dst[c] = (uint8_t) e;
+		const uint32_t j = pos >> 5;
+		const uint32_t w = __funnelshift_r(sw[hd_swz(j)], sw[hd_swz(j + 1)], pos & 31);
+		uint32_t e = lut[w & ((1u << HD_L1) - 1)];
+		if (e & 0x8000u)
+			e = __ldg(sub + (((e & 0x7fffu) << sub_bits) | ((w >> HD_L1) & ((1u << sub_bits) - 1))));
+		if (dst && c < lim)
+			dst[c * STRIDE] = (uint8_t) e;
 		c++;
 		pos += e >> 8;
 	}
@@ -304,13 +308,23 @@ __device__ __forceinline__ uint32_t hd_run(const uint32_t *sw, const uint16_t *l
 
 __global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__ ExDecArgs a)
 {
-	__shared__ uint32_t s_w[HD_CHUNK / 4 + 8];
-	__shared__ uint16_t s_lut[2048];
+	__shared__ uint32_t s_w[4 * HD_ROW];
+	__shared__ uint16_t s_lut[1 << HD_L1];
 	__shared__ uint32_t s_exit[NT];
 	__shared__ uint32_t s_warp[NW + 1];
 	__shared__ uint32_t s_read;
+	// the step's symbols, in order, before they leave as aligned 128-bit stores (a byte
+	// store per symbol costs one L2 transaction each: that alone bounded the kernel)
+	__shared__ __align__(16) uint8_t s_sym[HD_SYM + 32];
+	// with no code shorter than 4 bits every pass leaves the sub-block's symbols in the
+	// thread's own slot, so nothing is decoded again once the entry points have settled
+	__shared__ __align__(16) uint8_t s_slot[HD_SYM];
 	const int tid = threadIdx.x;
-	for (int i = tid; i < 2048; i += NT)
+	const bool slots = a.huff_minlen >= 4;
+	const uint16_t *sub = a.huff_sub;
+	const uint32_t sub_bits = a.huff_sub_bits;
+	uint8_t *myslot = slots ? s_slot + tid : nullptr;	// symbol c of thread tid at s_slot[c * NT + tid]
+	for (int i = tid; i < (1 << HD_L1); i += NT)
 		s_lut[i] = a.huff_dec[i];
 	for (;;) {
 		__syncthreads();
@@ -348,7 +362,7 @@ __global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__
 								v |= (uint32_t) s[4ull * w + b] << (8 * b);
 						}
 					}
-					s_w[w] = v;
+					s_w[hd_swz(w)] = v;
 				}
 			}
 			__syncthreads();
@@ -358,7 +372,7 @@ __global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__
 			const uint32_t lo = tid * HD_SUB, hi = lo + HD_SUB;
 			uint32_t cur = tid == 0 ? entry : 0u, cnt = 0, ex = 0;
 			if (act)
-				ex = hd_run(s_w, s_lut, a.huff_tree, lo + cur, hi, cnt, nullptr, 0) - hi;
+				ex = hd_run<NT>(s_w, s_lut, sub, sub_bits, lo + cur, hi, cnt, myslot, HD_SLOT) - hi;
 			s_exit[tid] = ex;
 			uint32_t rounds = 0;
 			for (;;) {
@@ -373,7 +387,7 @@ __global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__
 						cnt = 0;
 						ex = lo + cur - hi;
 					} else {
-						ex = hd_run(s_w, s_lut, a.huff_tree, lo + cur, hi, cnt, nullptr, 0) - hi;
+						ex = hd_run<NT>(s_w, s_lut, sub, sub_bits, lo + cur, hi, cnt, myslot, HD_SLOT) - hi;
 					}
 				}
 				const int any = __syncthreads_or(ch);
@@ -384,10 +398,24 @@ __global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__
 			}
 			uint32_t c1[1] = {act ? cnt : 0u}, ex1[1], tot;
 			block_scan<1>(c1, ex1, tot, s_warp);
-			if (act && cnt) {
+			if (tot <= HD_SYM) {
+				if (act && cnt) {
+					if (slots) {
+						for (uint32_t c = 0; c < cnt; c++)
+							s_sym[ex1[0] + c] = myslot[c * NT];
+					} else {
+						uint32_t dummy;
+						(void) hd_run<1>(s_w, s_lut, sub, sub_bits, lo + cur, hi, dummy, s_sym + ex1[0], cnt);
+					}
+				}
+				__syncthreads();
+				const int64_t room = count - done;
+				block_copy_out(s_sym, dst + done, (uint32_t) ((int64_t) tot < room ? tot : room));
+			} else if (act && cnt) {	// a table with very short codes: more symbols than the stage holds
 				uint32_t dummy;
-				const int64_t first = done + ex1[0];
-				(void) hd_run(s_w, s_lut, a.huff_tree, lo + cur, hi, dummy, dst + first, count - first);
+				const int64_t first = done + ex1[0], room = count - first;
+				(void) hd_run<1>(s_w, s_lut, sub, sub_bits, lo + cur, hi, dummy, dst + first,
+						 room > 0 ? (uint32_t) (room < 0xffffffffll ? room : 0xffffffffll) : 0u);
 			}
 			entry = s_exit[nsub - 1];
 			done += tot;
