@@ -14,7 +14,8 @@
 //   keys of tile t+1   -> byte counts -> block scan -> the tile's data range is known
 //   data of tile t+1   -> registers        (aligned 128-bit loads, issued before ...)
 //   tile t             -> smem stage -> values -> unzigzag -> block scan + carry ->
-//                         smem -> aligned 128-bit stores
+//                         aligned 128-bit stores (tiles are cut on 16-byte boundaries
+//                         of the output array)
 //
 // so the loads of a tile are in flight for a whole tile time before they are
 // needed.  1184 reads are in flight on a B200 (8 CTAs per SM).
@@ -38,27 +39,38 @@ struct SvbDec2Args {
 	Hdr *hdr;			// ticket = next read
 };
 
+// "two bytes" flags of the 16 values with read indices i0 .. i0 + 15 (i0 > -8;
+// indices < 0 and >= n give 0).  svb16: bit i & 7 of key byte i >> 3; svb32: 2-bit
+// code at bit 2 (i & 3) of key byte i >> 2, codes 0/1 only (zd < 65536).
 template <int KEYBITS>
-__device__ __forceinline__ uint32_t dec_thread_flags(const uint8_t *keys, uint64_t nkeys, uint32_t t, int tid)
+__device__ __forceinline__ uint32_t dec_thread_flags(const uint8_t *keys, uint64_t nkeys, int64_t i0)
 {
-	// the 16 samples of this thread are covered by 2 (svb16) / 4 (svb32) key bytes
-	constexpr int KPT = KEYBITS == 1 ? 2 : 4;
-	const uint64_t kb = ((uint64_t) t * NT + tid) * KPT;
-	uint32_t k = 0;
+	const uint32_t skip = i0 < 0 ? (uint32_t) (-i0) : 0u;
+	const uint64_t ic = i0 < 0 ? 0 : (uint64_t) i0;
+	if (KEYBITS == 1) {
+		const uint64_t kb = ic >> 3;
+		uint32_t k = 0;
 #pragma unroll
-	for (int b = 0; b < KPT; b++)
-		if (kb + b < nkeys)
-			k |= (uint32_t) __ldg(keys + kb + b) << (8 * b);
-	if (KEYBITS == 2)	// codes 0/1 only (zd < 65536): low bit of every 2-bit code
-		k = squeeze16(k) | (squeeze16(k >> 16) << 8);
-	return k;
+		for (int b = 0; b < 3; b++)
+			if (kb + b < nkeys)
+				k |= (uint32_t) __ldg(keys + kb + b) << (8 * b);
+		return ((k >> (ic & 7)) << skip) & 0xffffu;
+	} else {
+		const uint64_t kb = ic >> 2;
+		uint64_t k = 0;
+#pragma unroll
+		for (int b = 0; b < 5; b++)
+			if (kb + b < nkeys)
+				k |= (uint64_t) __ldg(keys + kb + b) << (8 * b);
+		const uint32_t c = (uint32_t) (k >> (2 * (ic & 3)));
+		return ((squeeze16(c) | (squeeze16(c >> 16) << 8)) << skip) & 0xffffu;
+	}
 }
 
 template <int KEYBITS, bool FRAME>
 __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ SvbDec2Args a)
 {
 	__shared__ __align__(16) uint8_t s_in[2 * DT + 64];
-	__shared__ __align__(16) uint8_t s_out[2 * DT + 32];
 	__shared__ uint32_t s_warp[NW + 1], s_warp2[NW + 1];	// byte-count scans / value scans
 	__shared__ uint32_t s_read;
 	const int tid = threadIdx.x;
@@ -90,12 +102,25 @@ __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ 
 		const uint8_t *keys = a.in + sbase + (FRAME ? 4 : 0);
 		const uint8_t *data = keys + nkeys;
 		const uint64_t ndata = send - sbase - fixed;
-		const uint32_t ntiles = (uint32_t) ((n + DT - 1) / DT);
-		uint8_t *dst = reinterpret_cast<uint8_t *>(a.samples_out + off0);
+		// tiles are cut on 16-byte boundaries of the OUTPUT (aligned 128-bit stores): element e
+		// of thread tid in tile t is read index t * DT + 16 tid + e - m
+		const uint32_t m = (uint32_t) (off0 & 7);
+		const uint64_t A = off0 >> 3;
+		const uint32_t ntiles = (uint32_t) ((m + n + DT - 1) / DT);
+		uint4 *out4 = reinterpret_cast<uint4 *>(a.samples_out);
+		uint16_t *out16 = reinterpret_cast<uint16_t *>(a.samples_out);
 
+		auto first_of = [&](uint32_t t) -> int64_t { return (int64_t) t * DT + tid * DPT - (int64_t) m; };
+		auto interior_of = [&](uint32_t t) -> bool {
+			return (int64_t) t * DT - (int64_t) m >= 0 && (int64_t) (t + 1) * DT - (int64_t) m <= (int64_t) n;
+		};
 		auto valid_of = [&](uint32_t t) -> uint32_t {
-			const uint64_t i0 = (uint64_t) t * DT + (uint64_t) tid * DPT;
-			return i0 >= n ? 0u : (n - i0 >= 16 ? 0xffffu : (0xffffu >> (16 - (uint32_t) (n - i0))));
+			if (interior_of(t))
+				return 0xffffu;
+			const int64_t i0 = first_of(t), left = (int64_t) n - i0;
+			const int lo = i0 < 0 ? (int) (-i0 < 16 ? -i0 : 16) : 0;
+			const int hi = left >= 16 ? 16 : (left > 0 ? (int) left : 0);
+			return hi > lo ? (0xffffu >> (16 - hi)) & (0xffffu << lo) & 0xffffu : 0u;
 		};
 		// data bytes of a tile -> registers: word u, u + 256, (u + 512)
 		uint4 dreg[3];
@@ -113,10 +138,10 @@ __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ 
 		};
 
 		// ---- prologue: tile 0 scanned and its data requested, keys of tile 1 requested
-		uint32_t fl_cur = dec_thread_flags<KEYBITS>(keys, nkeys, 0, tid);
+		uint32_t fl_cur = dec_thread_flags<KEYBITS>(keys, nkeys, first_of(0));
 		uint32_t va_cur = valid_of(0);
 		fl_cur &= va_cur;
-		uint32_t fl_next = ntiles > 1 ? dec_thread_flags<KEYBITS>(keys, nkeys, 1, tid) : 0u;
+		uint32_t fl_next = ntiles > 1 ? dec_thread_flags<KEYBITS>(keys, nkeys, first_of(1)) : 0u;
 		uint32_t ex_cur, L_cur;
 		{
 			uint32_t c1[1] = {(uint32_t) (__popc(va_cur) + __popc(fl_cur))}, e1[1];
@@ -155,14 +180,14 @@ __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ 
 				else
 					issue_data(D + L_cur, L_n);
 				if (t + 2 < ntiles)
-					fl_next = dec_thread_flags<KEYBITS>(keys, nkeys, t + 2, tid);
+					fl_next = dec_thread_flags<KEYBITS>(keys, nkeys, first_of(t + 2));
 			} else {
 				__syncthreads();
 			}
 			// ---- bytes -> zd values, two per word
 			uint32_t zz[8];
 			const uint32_t p = al + ex_cur;
-			if (L_cur == DT && n - (uint64_t) t * DT >= DT) {
+			if (L_cur == DT && va_cur == 0xffffu && interior_of(t)) {
 				// full tile without a two-byte value: the thread's 16 bytes sit at stage[al + 16 tid]
 				stage_bytes16(s_in, al, tid, zz);
 			} else {
@@ -191,19 +216,30 @@ __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ 
 			uint32_t c1[1] = {c & 0xffffu}, e1[1], tot;
 			block_scan<1>(c1, e1, tot, s_warp2);
 			const uint32_t cw = ((e1[0] + carry) & 0xffffu) * 0x00010001u;
-			uint4 *so = reinterpret_cast<uint4 *>(s_out) + 2 * tid;
-			so[0] = make_uint4(add16x2(y[0], cw), add16x2(y[1], cw), add16x2(y[2], cw), add16x2(y[3], cw));
-			so[1] = make_uint4(add16x2(y[4], cw), add16x2(y[5], cw), add16x2(y[6], cw), add16x2(y[7], cw));
-			__syncthreads();
-			const uint64_t left = n - (uint64_t) t * DT;
-			block_copy_out(s_out, dst + 2ull * t * DT, 2 * (uint32_t) (left < DT ? left : DT));
+			uint32_t o[8];
+#pragma unroll
+			for (int j = 0; j < 8; j++)
+				o[j] = add16x2(y[j], cw);
+			const uint64_t ka = A + (uint64_t) t * (DT / 8) + 2 * tid;
+#pragma unroll
+			for (int h = 0; h < 2; h++) {
+				const uint32_t vm = (va_cur >> (8 * h)) & 0xffu;
+				if (vm == 0xffu) {
+					out4[ka + h] = make_uint4(o[4 * h], o[4 * h + 1], o[4 * h + 2], o[4 * h + 3]);
+				} else if (vm) {
+#pragma unroll
+					for (int e = 0; e < 8; e++)
+						if ((vm >> e) & 1)
+							out16[8 * (ka + h) + e] = (uint16_t) (o[4 * h + (e >> 1)] >> (16 * (e & 1)));
+				}
+			}
 			carry = (carry + tot) & 0xffffu;
 			D += L_cur;
 			fl_cur = fl_n;
 			va_cur = va_n;
 			ex_cur = ex_n;
 			L_cur = L_n;
-			__syncthreads();	// s_in / s_out are rewritten by the next tile
+			__syncthreads();	// s_in is rewritten by the next tile
 		}
 		if (overrun && tid == 0)
 			atomicOr(&a.hdr->error, ERR_MALFORMED);
