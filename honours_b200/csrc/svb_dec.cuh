@@ -39,32 +39,44 @@ struct SvbDec2Args {
 	Hdr *hdr;			// ticket = next read
 };
 
-// "two bytes" flags of the 16 values with read indices i0 .. i0 + 15 (i0 > -8;
-// indices < 0 and >= n give 0).  svb16: bit i & 7 of key byte i >> 3; svb32: 2-bit
-// code at bit 2 (i & 3) of key byte i >> 2, codes 0/1 only (zd < 65536).
+// Key bits of the 16 values with read indices i0 .. i0 + 15 (i0 > -8), requested as two
+// aligned 32-bit words and turned into "two bytes" flags one tile later (so nothing waits
+// on the loads).  svb16: bit i & 7 of key byte i >> 3; svb32: 2-bit code at bit 2 (i & 3)
+// of key byte i >> 2, codes 0/1 only (zd < 65536).  Bits of indices < 0 read as 0, bits
+// past the key section are garbage and masked by the caller's valid mask.
+struct KeyRaw {
+	uint32_t w0, w1, sh, skip;
+};
+
 template <int KEYBITS>
-__device__ __forceinline__ uint32_t dec_thread_flags(const uint8_t *keys, uint64_t nkeys, int64_t i0)
+__device__ __forceinline__ KeyRaw dec_keys_issue(const uint8_t *keys, int64_t i0, const uint8_t *lo, const uint8_t *hi)
 {
-	const uint32_t skip = i0 < 0 ? (uint32_t) (-i0) : 0u;
+	KeyRaw k;
+	k.skip = i0 < 0 ? (uint32_t) (-i0) : 0u;
 	const uint64_t ic = i0 < 0 ? 0 : (uint64_t) i0;
-	if (KEYBITS == 1) {
-		const uint64_t kb = ic >> 3;
-		uint32_t k = 0;
-#pragma unroll
-		for (int b = 0; b < 3; b++)
-			if (kb + b < nkeys)
-				k |= (uint32_t) __ldg(keys + kb + b) << (8 * b);
-		return ((k >> (ic & 7)) << skip) & 0xffffu;
-	} else {
-		const uint64_t kb = ic >> 2;
-		uint64_t k = 0;
-#pragma unroll
-		for (int b = 0; b < 5; b++)
-			if (kb + b < nkeys)
-				k |= (uint64_t) __ldg(keys + kb + b) << (8 * b);
-		const uint32_t c = (uint32_t) (k >> (2 * (ic & 3)));
-		return ((squeeze16(c) | (squeeze16(c >> 16) << 8)) << skip) & 0xffffu;
+	const uint8_t *p = keys + (KEYBITS == 1 ? ic >> 3 : ic >> 2);
+	const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(p) & 3);
+	const uint8_t *pw = p - al;
+	k.sh = 8 * al + (KEYBITS == 1 ? (uint32_t) (ic & 7) : 2 * (uint32_t) (ic & 3));
+	if (pw >= lo && pw + 8 <= hi) {
+		k.w0 = __ldg(reinterpret_cast<const uint32_t *>(pw));
+		k.w1 = __ldg(reinterpret_cast<const uint32_t *>(pw) + 1);
+	} else {	// the last bytes of the container
+		k.w0 = k.w1 = 0;
+		for (int b = 0; b < 8; b++)
+			if (pw + b >= lo && pw + b < hi)
+				(b < 4 ? k.w0 : k.w1) |= (uint32_t) pw[b] << (8 * (b & 3));
 	}
+	return k;
+}
+
+template <int KEYBITS>
+__device__ __forceinline__ uint32_t dec_keys_flags(const KeyRaw &k)
+{
+	const uint32_t c = __funnelshift_r(k.w0, k.w1, k.sh);	// sh <= 31
+	if (KEYBITS == 1)
+		return (c << k.skip) & 0xffffu;
+	return ((squeeze16(c) | (squeeze16(c >> 16) << 8)) << k.skip) & 0xffffu;
 }
 
 template <int KEYBITS, bool FRAME>
@@ -111,9 +123,9 @@ __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ 
 		uint16_t *out16 = reinterpret_cast<uint16_t *>(a.samples_out);
 
 		auto first_of = [&](uint32_t t) -> int64_t { return (int64_t) t * DT + tid * DPT - (int64_t) m; };
-		auto interior_of = [&](uint32_t t) -> bool {
-			return (int64_t) t * DT - (int64_t) m >= 0 && (int64_t) (t + 1) * DT - (int64_t) m <= (int64_t) n;
-		};
+		// tiles [t_lo, t_hi) are interior: every element is a sample of the read
+		const uint32_t t_lo = m ? 1u : 0u, t_hi = (uint32_t) ((m + n) / DT);
+		auto interior_of = [&](uint32_t t) -> bool { return t >= t_lo && t < t_hi; };
 		auto valid_of = [&](uint32_t t) -> uint32_t {
 			if (interior_of(t))
 				return 0xffffu;
@@ -129,19 +141,29 @@ __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ 
 			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
 			const uint8_t *b16 = src - al;
 			const uint32_t nw = (al + L + 15) >> 4;
+			if (b16 + 16ull * nw <= limit) {	// (b16 >= a.in: the container is 16-byte aligned)
 #pragma unroll
-			for (int j = 0; j < 3; j++) {
-				const uint32_t w = tid + j * NT;
-				if (w < nw)
-					dreg[j] = load_word_guarded(b16, w, a.in, limit);
+				for (int j = 0; j < 3; j++) {
+					const uint32_t w = tid + j * NT;
+					if (w < nw)
+						dreg[j] = __ldg(reinterpret_cast<const uint4 *>(b16) + w);
+				}
+			} else {
+#pragma unroll
+				for (int j = 0; j < 3; j++) {
+					const uint32_t w = tid + j * NT;
+					if (w < nw)
+						dreg[j] = load_word_guarded(b16, w, a.in, limit);
+				}
 			}
 		};
 
 		// ---- prologue: tile 0 scanned and its data requested, keys of tile 1 requested
-		uint32_t fl_cur = dec_thread_flags<KEYBITS>(keys, nkeys, first_of(0));
 		uint32_t va_cur = valid_of(0);
-		fl_cur &= va_cur;
-		uint32_t fl_next = ntiles > 1 ? dec_thread_flags<KEYBITS>(keys, nkeys, first_of(1)) : 0u;
+		uint32_t fl_cur = dec_keys_flags<KEYBITS>(dec_keys_issue<KEYBITS>(keys, first_of(0), a.in, limit)) & va_cur;
+		KeyRaw k_next = {0, 0, 0, 0};
+		if (ntiles > 1)
+			k_next = dec_keys_issue<KEYBITS>(keys, first_of(1), a.in, limit);
 		uint32_t ex_cur, L_cur;
 		{
 			uint32_t c1[1] = {(uint32_t) (__popc(va_cur) + __popc(fl_cur))}, e1[1];
@@ -171,7 +193,7 @@ __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ 
 			uint32_t fl_n = 0, va_n = 0, ex_n = 0, L_n = 0;
 			if (t + 1 < ntiles) {
 				va_n = valid_of(t + 1);
-				fl_n = fl_next & va_n;
+				fl_n = dec_keys_flags<KEYBITS>(k_next) & va_n;
 				uint32_t c1[1] = {(uint32_t) (__popc(va_n) + __popc(fl_n))}, e1[1];
 				block_scan<1>(c1, e1, L_n, s_warp);	// (its barriers also publish s_in)
 				ex_n = e1[0];
@@ -180,7 +202,7 @@ __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ 
 				else
 					issue_data(D + L_cur, L_n);
 				if (t + 2 < ntiles)
-					fl_next = dec_thread_flags<KEYBITS>(keys, nkeys, first_of(t + 2));
+					k_next = dec_keys_issue<KEYBITS>(keys, first_of(t + 2), a.in, limit);
 			} else {
 				__syncthreads();
 			}
@@ -190,6 +212,20 @@ __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ 
 			if (L_cur == DT && va_cur == 0xffffu && interior_of(t)) {
 				// full tile without a two-byte value: the thread's 16 bytes sit at stage[al + 16 tid]
 				stage_bytes16(s_in, al, tid, zz);
+			} else if (va_cur == 0xffffu && fl_cur == 0) {
+				// 16 one-byte values at an arbitrary stage offset
+				const uint32_t *w32 = reinterpret_cast<const uint32_t *>(s_in) + (p >> 2);
+				const uint32_t sh = (p & 3) * 8;
+				uint32_t w[5];
+#pragma unroll
+				for (int j = 0; j < 5; j++)
+					w[j] = w32[j];
+#pragma unroll
+				for (int j = 0; j < 4; j++) {
+					const uint32_t v = __funnelshift_r(w[j], w[j + 1], sh);
+					zz[2 * j] = __byte_perm(v, 0, 0x4140);
+					zz[2 * j + 1] = __byte_perm(v, 0, 0x4342);
+				}
 			} else {
 				const uint8_t *q = s_in + p;
 #pragma unroll
