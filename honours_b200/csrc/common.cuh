@@ -203,48 +203,38 @@ __device__ __forceinline__ uint64_t row_scan(uint64_t *tile, uint64_t *rowpref, 
 	return D;
 }
 
-// Exclusive scan over the CTA in (chunk, thread) order: element (c, tid) comes
-// before (c, tid + 1) and all of chunk c before chunk c + 1.
-// s_warp needs C * NW + 1 words.  Contains two __syncthreads().
+// Exclusive scan over the CTA in thread order (C must be 1; the template keeps the
+// call sites' array form).  s_warp: NW words, 16-byte aligned.  ONE __syncthreads():
+// every warp posts its total, then every thread adds up the totals of the warps
+// before its own.  The caller must put a barrier between this call's reads of s_warp
+// and the next write to the same array (every call site has one: the loop-end barrier).
 template <int C>
 __device__ __forceinline__ void block_scan(const uint32_t (&v)[C], uint32_t (&excl)[C],
 					   uint32_t &total, uint32_t *s_warp)
 {
-	static_assert(C * NW <= 32, "one warp scans the warp totals");
+	static_assert(C == 1 && NW == 8, "one value per thread, 8 warps");
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	uint32_t inc[C];
+	uint32_t x = v[0];
 #pragma unroll
-	for (int c = 0; c < C; c++) {
-		uint32_t x = v[c];
-#pragma unroll
-		for (int o = 1; o < 32; o <<= 1) {
-			uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-			if (lane >= o)
-				x += y;
-		}
-		inc[c] = x;
-		if (lane == 31)
-			s_warp[c * NW + warp] = x;
+	for (int o = 1; o < 32; o <<= 1) {
+		const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+		if (lane >= o)
+			x += y;
 	}
+	if (lane == 31)
+		s_warp[warp] = x;
 	__syncthreads();
-	if (warp == 0) {
-		uint32_t x = lane < C * NW ? s_warp[lane] : 0, orig = x;
+	const uint4 t0 = reinterpret_cast<const uint4 *>(s_warp)[0], t1 = reinterpret_cast<const uint4 *>(s_warp)[1];
+	const uint32_t w[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+	uint32_t before = 0, all = 0;
 #pragma unroll
-		for (int o = 1; o < 32; o <<= 1) {
-			uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-			if (lane >= o)
-				x += y;
-		}
-		if (lane < C * NW)
-			s_warp[lane] = x - orig;
-		if (lane == C * NW - 1)
-			s_warp[C * NW] = x;
+	for (int k = 0; k < 8; k++) {
+		all += w[k];
+		if (k < warp)
+			before += w[k];
 	}
-	__syncthreads();
-#pragma unroll
-	for (int c = 0; c < C; c++)
-		excl[c] = s_warp[c * NW + warp] + inc[c] - v[c];
-	total = s_warp[C * NW];
+	excl[0] = before + x - v[0];
+	total = all;
 }
 
 // ---- SWAR on two 16-bit lanes per 32-bit word -----------------------------

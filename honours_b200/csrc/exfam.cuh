@@ -444,7 +444,7 @@ __device__ __forceinline__ bool ex_read_tile0(const ExArgs &a, uint64_t r, ExTil
 template <bool HUFF>
 __global__ void __launch_bounds__(NT, 4) ex_count_kernel(const __grid_constant__ ExArgs a)
 {
-	__shared__ uint32_t s_warp[NW + 1];
+	__shared__ __align__(16) uint32_t s_warp[NW];
 	__shared__ uint32_t s_read, s_pool, s_or;
 	__shared__ unsigned long long s_bits;
 	__shared__ uint32_t s_len[HUFF ? 256 : 1];
@@ -583,7 +583,7 @@ template <bool HUFF>
 __global__ void __launch_bounds__(NT, 4) ex_emit_kernel(const __grid_constant__ ExArgs a)
 {
 	__shared__ __align__(16) uint8_t s_stage[HUFF ? X_STAGE : XT + 64];
-	__shared__ uint32_t s_warp[NW + 1];
+	__shared__ __align__(16) uint32_t s_warp[NW];
 	__shared__ uint32_t s_lut[HUFF ? 256 : 1];
 	__shared__ uint32_t s_read;
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;

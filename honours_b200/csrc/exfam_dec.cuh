@@ -311,7 +311,7 @@ __global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__
 	__shared__ uint32_t s_w[4 * HD_ROW];
 	__shared__ uint16_t s_lut[1 << HD_L1];
 	__shared__ uint32_t s_exit[NT];
-	__shared__ uint32_t s_warp[NW + 1];
+	__shared__ __align__(16) uint32_t s_warp[NW];
 	__shared__ uint32_t s_read;
 	// the step's symbols, in order, before they leave as aligned 128-bit stores (a byte
 	// store per symbol costs one L2 transaction each: that alone bounded the kernel)
@@ -436,7 +436,7 @@ __global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__
 __global__ void __launch_bounds__(NT, 4) ex_decode_kernel(const __grid_constant__ ExDecArgs a)
 {
 	__shared__ __align__(16) uint8_t s_stage[XT + 64];
-	__shared__ uint32_t s_warp[NW + 1];
+	__shared__ __align__(16) uint32_t s_warp[NW];
 	__shared__ uint32_t s_read, s_e;
 	const int tid = threadIdx.x;
 	const bool shuff = a.method == PRESS_GPU_SHUFF_VBE21_ZD;
@@ -471,11 +471,19 @@ __global__ void __launch_bounds__(NT, 4) ex_decode_kernel(const __grid_constant_
 			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
 			const uint32_t nw = (al + (j_hi - j_lo) + 15) >> 4;	// (a few bytes more than needed when
 			const uint8_t *b16 = src - al;				//  the tile holds exceptions)
-			if ((uint32_t) tid < nw)
-				dreg[0] = load_word_guarded(b16, tid, lim_lo, lim_hi);
-			if (tid == 0 && nw > NT)
-				dreg[1] = load_word_guarded(b16, NT, lim_lo, lim_hi);
+			if (b16 >= lim_lo && b16 + 16ull * nw <= lim_hi) {
+				if ((uint32_t) tid < nw)
+					dreg[0] = __ldg(reinterpret_cast<const uint4 *>(b16) + tid);
+				if (tid == 0 && nw > NT)
+					dreg[1] = __ldg(reinterpret_cast<const uint4 *>(b16) + NT);
+			} else {
+				if ((uint32_t) tid < nw)
+					dreg[0] = load_word_guarded(b16, tid, lim_lo, lim_hi);
+				if (tid == 0 && nw > NT)
+					dreg[1] = load_word_guarded(b16, NT, lim_lo, lim_hi);
+			}
 		};
+		const uint32_t t_hi = (uint32_t) ((m + n) / XT);	// tiles [1, t_hi) lie inside the read
 		uint32_t e_lo = 0, carry = 0;
 		issue(0, 0);
 		for (uint32_t t = 0; t < nt; t++) {
@@ -507,7 +515,7 @@ __global__ void __launch_bounds__(NT, 4) ex_decode_kernel(const __grid_constant_
 			// ---- zd values of the thread's 16 elements
 			const uint64_t ka = A + (uint64_t) t * XG + 2 * tid;
 			const int64_t f = (int64_t) t * XT - m;		// read index of the tile's first element
-			const bool interior = f >= 1 && f + XT <= (int64_t) n;
+			const bool interior = t >= 1 && t < t_hi;
 			const uint32_t valid = interior ? 0xffffu
 							: group_valid(ka, off0, rend) | (group_valid(ka + 1, off0, rend) << 8);
 			const int64_t i0 = f + 16 * tid;

@@ -83,7 +83,8 @@ template <int KEYBITS, bool FRAME>
 __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ SvbDec2Args a)
 {
 	__shared__ __align__(16) uint8_t s_in[2 * DT + 64];
-	__shared__ uint32_t s_warp[NW + 1], s_warp2[NW + 1];	// byte-count scans / value scans
+	__shared__ __align__(16) uint32_t s_warp[NW];	// byte-count scans
+	__shared__ __align__(16) uint32_t s_warp2[NW];	// value scans
 	__shared__ uint32_t s_read;
 	const int tid = threadIdx.x;
 	const uint8_t *limit = a.in + a.in_bytes;
