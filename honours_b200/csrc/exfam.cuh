@@ -50,7 +50,7 @@ struct ExArgs {
 	uint64_t *out_offsets;		// [nreads + 1]
 	Hdr *hdr;			// aux[0] = pool entries used
 	const uint32_t *tile_start, *tile_read;
-	uint32_t *t_nex, *t_pool, *t_bits, *t_or, *t_eb, *t_pb;	// per tile
+	uint32_t *t_nex, *t_pool, *t_eb;	// per (tile, warp): exceptions in the slice, pool position, prefix
 	uint32_t *r_nex, *r_q, *r_hdr;				// per read
 	uint64_t *r_size;
 	uint2 *pool;			// (position in v = sample index - 1, value)
@@ -225,22 +225,26 @@ __device__ __forceinline__ uint32_t ex_elem(const ExVals &v, int e)
 // ---------------------------------------------------------------------------
 // exception lists of a read, addressed by their index k inside the read
 
+// Exceptions are captured per warp slice (512 samples of a tile): record (tile, warp)
+// holds how many, where in the pool, and (after the read has been walked) how many
+// came before it in the read.
 struct ExList {
 	const uint32_t *t_eb, *t_pool;
 	const uint2 *pool;
-	uint32_t g0, ntiles;
+	uint64_t r0;		// first record of the read: 8 per tile
+	uint32_t nrec;
 	__device__ __forceinline__ uint2 at(uint32_t k) const
 	{
-		// last tile whose exclusive exception prefix is <= k
-		uint32_t lo = 0, hi = ntiles;	// invariant: eb[lo] <= k, eb[hi] > k (hi == ntiles: virtual)
+		// last record whose exclusive exception prefix is <= k
+		uint32_t lo = 0, hi = nrec;	// invariant: eb[lo] <= k, eb[hi] > k (hi == nrec: virtual)
 		while (hi - lo > 1) {
 			const uint32_t mid = (lo + hi) >> 1;
-			if (t_eb[g0 + mid] <= k)
+			if (t_eb[r0 + mid] <= k)
 				lo = mid;
 			else
 				hi = mid;
 		}
-		return pool[(uint64_t) t_pool[g0 + lo] + (k - t_eb[g0 + lo])];
+		return pool[(uint64_t) t_pool[r0 + lo] + (k - t_eb[r0 + lo])];
 	}
 };
 
@@ -445,7 +449,7 @@ template <bool HUFF>
 __global__ void __launch_bounds__(NT, 4) ex_count_kernel(const __grid_constant__ ExArgs a)
 {
 	__shared__ __align__(16) uint32_t s_warp[NW];
-	__shared__ uint32_t s_read, s_pool, s_or;
+	__shared__ uint32_t s_read, s_or, s_nex;
 	__shared__ unsigned long long s_bits;
 	__shared__ uint32_t s_len[HUFF ? 256 : 1];
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -456,6 +460,7 @@ __global__ void __launch_bounds__(NT, 4) ex_count_kernel(const __grid_constant__
 		if (tid == 0) {
 			s_read = atomicAdd(&a.hdr->ticket, 1u);
 			s_or = 0;
+			s_nex = 0;
 			s_bits = 0;
 		}
 		__syncthreads();
@@ -475,11 +480,13 @@ __global__ void __launch_bounds__(NT, 4) ex_count_kernel(const __grid_constant__
 		}
 		const uint64_t n = T.rend - T.off0, A = T.off0 >> 3;
 		const uint32_t nt = T.ntiles;
-		uint32_t q = 0, nex_run = 0, bits_thr = 0;
+		const uint64_t rec0 = (uint64_t) g0 * NW;
+		const uint32_t t_hi = (uint32_t) ((T.m + n) / XT);	// tiles [1, t_hi) lie inside the read
+		uint32_t q = 0, bits_thr = 0;
 		for (int pass = 0; pass < 2; pass++) {
-			nex_run = 0;
+			// the walk: no CTA barrier, every warp runs through its 512-sample slice of every tile
+			uint32_t nex_thr = 0, or_thr = 0;
 			bits_thr = 0;
-			uint32_t or_thr = 0;
 			ExRaw W;
 			ex_issue(a.samples, a.nsamples, A, W);
 			for (uint32_t t = 0; t < nt; t++) {
@@ -488,70 +495,93 @@ __global__ void __launch_bounds__(NT, 4) ex_count_kernel(const __grid_constant__
 				const ExRaw C = W;
 				if (t + 1 < nt)
 					ex_issue(a.samples, a.nsamples, T.k0 + XG, W);
-				const int64_t f = (int64_t) t * XT - T.m;	// read index of the tile's first element
-				const bool interior = f >= 1 && f + XT <= (int64_t) n;
 				ExVals v;
-				if (interior) {
+				if (t >= 1 && t < t_hi) {
 					uint32_t orw;
 					(void) ex_compute_fast(C, q, v, orw);
 					or_thr |= orw;
-					v.i0 = f + 16 * tid;
+					v.i0 = (int64_t) t * XT - T.m + 16 * tid;
 				} else {
 					ex_compute(C, T, q, v);
 					or_thr |= v.orv;
 				}
-				const uint32_t cnt = __popc(v.exc);
 				if (HUFF)
 					bits_thr += ex_code_bits(v, v.valid & ~v.exc & ~v.first, s_len);
-				uint32_t tile_nex = 0;
-				if (__syncthreads_or(cnt)) {	// capture, in order
-					uint32_t c1[1] = {cnt}, ex1[1];
-					block_scan<1>(c1, ex1, tile_nex, s_warp);
-					if (tid == 0)
-						s_pool = (uint32_t) atomicAdd((unsigned long long *) &a.hdr->aux[0],
-									      (unsigned long long) tile_nex);
-					__syncthreads();
-					const uint64_t base = s_pool;
-					if (base + tile_nex <= a.pool_cap) {
-						uint2 *p = a.pool + base + ex1[0];
+				uint32_t slice_nex = 0, base = 0;
+				if (__any_sync(0xffffffffu, v.exc)) {	// capture, in order
+					const uint32_t cnt = __popc(v.exc);
+					const uint32_t inc = warp_inc_scan(cnt, lane);
+					slice_nex = __shfl_sync(0xffffffffu, inc, 31);
+					unsigned long long b64 = 0;
+					if (lane == 0)
+						b64 = atomicAdd((unsigned long long *) &a.hdr->aux[0], (unsigned long long) slice_nex);
+					b64 = __shfl_sync(0xffffffffu, b64, 0);
+					base = (uint32_t) b64;
+					if (b64 + slice_nex <= a.pool_cap) {
+						uint2 *p = a.pool + b64 + inc - cnt;
 						for (uint32_t mk = v.exc; mk; mk &= mk - 1) {
 							const int e = __ffs(mk) - 1;
 							*p++ = make_uint2((uint32_t) (v.i0 + e - 1), ex_elem(v, e));
 						}
-					} else if (tid == 0) {
+					} else if (lane == 0) {
 						atomicOr(&a.hdr->error, ERR_SCRATCH);
 					}
+					nex_thr += cnt;
 				}
-				if (tid == 0) {
-					a.t_nex[g0 + t] = tile_nex;
-					a.t_pool[g0 + t] = tile_nex ? s_pool : 0;
-					a.t_eb[g0 + t] = nex_run;
+				if (lane == 0) {
+					a.t_nex[rec0 + (uint64_t) t * NW + warp] = slice_nex;
+					a.t_pool[rec0 + (uint64_t) t * NW + warp] = base;
 				}
-				nex_run += tile_nex;
 			}
+			nex_thr = __reduce_add_sync(0xffffffffu, nex_thr);
+			or_thr = __reduce_or_sync(0xffffffffu, (or_thr | (or_thr >> 16)) & 0xffffu);
+			if (lane == 0) {
+				if (nex_thr)
+					atomicAdd(&s_nex, nex_thr);
+				if (or_thr)
+					atomicOr(&s_or, or_thr);
+			}
+			__syncthreads();
 			if (a.method != PRESS_GPU_EX_ZD || pass == 1)
 				break;
 			// ex_zd.c:358-381: q from the OR of all samples (a zero sample never lowers q; cap 5)
-			or_thr = __reduce_or_sync(0xffffffffu, (or_thr | (or_thr >> 16)) & 0xffffu);
-			if (lane == 0 && or_thr)
-				atomicOr(&s_or, or_thr);
-			__syncthreads();
 			q = __ffs(s_or | 32u) - 1;
 			if (q == 0)
 				break;
+			__syncthreads();	// everybody has read s_or / s_nex
+			if (tid == 0)
+				s_nex = 0;
+			__syncthreads();
 		}
 		if (HUFF) {
 			const uint32_t wb = __reduce_add_sync(0xffffffffu, bits_thr);
 			if (lane == 0)
 				atomicAdd(&s_bits, (unsigned long long) wb);
 		}
-		__syncthreads();	// the tile records above are read by warp 0 below
+		const uint32_t nex = s_nex;
+		// exclusive prefix of the slice counts -> t_eb (all records of the read, in order)
+		const uint32_t nrec = nt * NW;
+		uint32_t run = 0;
+		if (nex) {
+			for (uint32_t b0 = 0; b0 < nrec; b0 += NT) {
+				__syncthreads();	// records written above / s_warp of the previous round
+				const uint32_t i = b0 + tid;
+				uint32_t c1[1] = {i < nrec ? a.t_nex[rec0 + i] : 0u}, e1[1], tot;
+				block_scan<1>(c1, e1, tot, s_warp);
+				if (i < nrec)
+					a.t_eb[rec0 + i] = run + e1[0];
+				run += tot;
+			}
+		} else {
+			for (uint32_t i = tid; i < nrec; i += NT)
+				a.t_eb[rec0 + i] = 0;
+		}
+		__syncthreads();	// t_eb and s_bits are read by warp 0 below
 		if (warp == 0) {
-			const uint32_t nex = nex_run;
 			uint32_t hdr = X_FAIL;
 			uint64_t size = 0;
 			if (!(a.hdr->error & ERR_SCRATCH)) {
-				const ExList L = {a.t_eb, a.t_pool, a.pool, g0, nt};
+				const ExList L = {a.t_eb, a.t_pool, a.pool, rec0, nrec};
 				hdr = ex_fixed_bytes(a.method) + ex_lists<false>(a.method, L, nex, nullptr, lane);
 				if (HUFF) {
 					hdr += 4;	// [count u32 BE], huffman.c:1199-1203
@@ -626,7 +656,7 @@ __global__ void __launch_bounds__(NT, 4) ex_emit_kernel(const __grid_constant__ 
 				put_le(p, zd0, 2);
 				put_le(p + 2, nex, 4);
 			}
-			const ExList L = {a.t_eb, a.t_pool, a.pool, g0, nt};
+			const ExList L = {a.t_eb, a.t_pool, a.pool, (uint64_t) g0 * NW, nt * NW};
 			const uint32_t fx = ex_fixed_bytes(a.method);
 			const uint32_t ll = ex_lists<true>(a.method, L, nex, dst + fx, lane);
 			if (HUFF && lane < 4) {
@@ -733,6 +763,148 @@ __global__ void __launch_bounds__(NT, 4) ex_emit_kernel(const __grid_constant__ 
 				pos += tot;
 			}
 			__syncthreads();
+		}
+	}
+}
+
+// sweep 2 for the byte payloads (vbe21 / vbsse21 / ex-zd): no CTA barrier in the walk.
+// A warp knows where its 512-sample slice goes from the record prefix alone
+// (values before the slice minus exceptions before the slice), so the eight warps
+// of the CTA run through the read independently.  A slice without exception inside
+// the read is 32 x 16 bytes: re-phased to the destination's 16-byte alignment with
+// shuffles and stored as aligned 128-bit words; anything else goes through a
+// per-warp staging line.
+__global__ void __launch_bounds__(NT, 4) ex_emit_bytes_kernel(const __grid_constant__ ExArgs a)
+{
+	__shared__ __align__(16) uint8_t s_line[NW][512 + 16];
+	__shared__ uint32_t s_read;
+	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	if (a.hdr->error & (ERR_CAPACITY | ERR_SCRATCH))
+		return;
+	for (;;) {
+		__syncthreads();
+		if (tid == 0)
+			s_read = atomicAdd(&a.hdr->ticket2, 1u);
+		__syncthreads();
+		const uint64_t r = s_read;
+		if (r >= a.nreads)
+			break;
+		const uint32_t hdr = a.r_hdr[r];
+		if (hdr == X_FAIL)
+			continue;
+		ExTile T;
+		uint32_t g0;
+		(void) ex_read_tile0(a, r, T, g0);
+		const uint64_t n = T.rend - T.off0, A = T.off0 >> 3;
+		const uint32_t nt = T.ntiles, nex = a.r_nex[r];
+		const uint32_t q = a.method == PRESS_GPU_EX_ZD ? a.r_q[r] : 0u;
+		const uint64_t rec0 = (uint64_t) g0 * NW + warp;
+		const uint32_t t_hi = (uint32_t) ((T.m + n) / XT);
+		uint8_t *dst = a.out + a.out_offsets[r];
+		ExRaw W;
+		ex_issue(a.samples, a.nsamples, A, W);
+		uint32_t eb_n = __ldg(a.t_eb + rec0), nx_n = __ldg(a.t_nex + rec0);
+		if (warp == 0) {	// the header, while the first tile is on its way
+			if (lane == 0) {
+				const int16_t x0 = reinterpret_cast<const int16_t *>(a.samples)[T.off0];
+				const uint16_t s0 = (uint16_t) (int16_t) (x0 >> q);
+				const uint16_t zd0 = (uint16_t) ((uint16_t) (s0 << 1) ^ (uint16_t) (0 - (s0 >> 15)));	// trans.c:75-78
+				uint8_t *p = dst;
+				if (a.method == PRESS_GPU_EX_ZD) {
+					*p++ = 0;		// ex_zd.c:420-423
+					put_le(p, n, 8);	// ex_zd.c:425-428
+					p += 8;
+					*p++ = (uint8_t) q;	// ex_zd.c:436-439
+				}
+				put_le(p, zd0, 2);
+				put_le(p + 2, nex, 4);
+			}
+			const ExList L = {a.t_eb, a.t_pool, a.pool, (uint64_t) g0 * NW, nt * NW};
+			(void) ex_lists<true>(a.method, L, nex, dst + ex_fixed_bytes(a.method), lane);
+		}
+		uint8_t *pay = dst + hdr;	// first payload byte of the read
+		const int64_t mm = (int64_t) n - 1;
+		for (uint32_t t = 0; t < nt; t++) {
+			T.t = t;
+			T.k0 = A + (uint64_t) t * XG;
+			const ExRaw C = W;
+			const uint32_t eb = eb_n, nx = nx_n;
+			if (t + 1 < nt) {
+				ex_issue(a.samples, a.nsamples, T.k0 + XG, W);
+				eb_n = __ldg(a.t_eb + rec0 + (uint64_t) (t + 1) * NW);
+				nx_n = __ldg(a.t_nex + rec0 + (uint64_t) (t + 1) * NW);
+			}
+			// values of the read before this slice, minus the exceptions among them
+			int64_t vb = (int64_t) t * XT - T.m + 512 * warp - 1;
+			vb = vb < 0 ? 0 : (vb < mm ? vb : mm);
+			uint8_t *D = pay + ((uint64_t) vb - eb);
+			const bool interior = t >= 1 && t < t_hi;
+			ExVals v;
+			if (interior) {
+				uint32_t orw;
+				(void) ex_compute_fast(C, q, v, orw);
+			} else {
+				ex_compute(C, T, q, v);
+			}
+			uint32_t qv[4] = {__byte_perm(v.z[0], v.z[1], 0x6420), __byte_perm(v.z[2], v.z[3], 0x6420),
+					  __byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420)};
+			if (interior && nx == 0) {
+				const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(D) & 15);
+				if (s == 0) {
+					reinterpret_cast<uint4 *>(D)[lane] = make_uint4(qv[0], qv[1], qv[2], qv[3]);
+				} else {
+					uint32_t c[8];
+#pragma unroll
+					for (int j = 0; j < 4; j++) {
+						c[j] = __shfl_up_sync(0xffffffffu, qv[j], 1);
+						c[4 + j] = qv[j];
+					}
+					// aligned word `lane` = bytes [16 - s, 32 - s) of (previous lane's, own) 32 bytes
+					const uint32_t sh = 16 - s, bs = (sh & 3) * 8;
+					uint32_t u0, u1, u2, u3, u4;
+					switch (sh >> 2) {
+					case 0: u0 = c[0]; u1 = c[1]; u2 = c[2]; u3 = c[3]; u4 = c[4]; break;
+					case 1: u0 = c[1]; u1 = c[2]; u2 = c[3]; u3 = c[4]; u4 = c[5]; break;
+					case 2: u0 = c[2]; u1 = c[3]; u2 = c[4]; u3 = c[5]; u4 = c[6]; break;
+					default: u0 = c[3]; u1 = c[4]; u2 = c[5]; u3 = c[6]; u4 = c[7]; break;
+					}
+					uint8_t *Wd = D - s;
+					if (lane > 0)
+						reinterpret_cast<uint4 *>(Wd)[lane] =
+							make_uint4(__funnelshift_r(u0, u1, bs), __funnelshift_r(u1, u2, bs),
+								   __funnelshift_r(u2, u3, bs), __funnelshift_r(u3, u4, bs));
+					// head: the first 16 - s bytes of lane 0; tail: the last s bytes of lane 31
+					uint32_t h[4], tl[4];
+#pragma unroll
+					for (int j = 0; j < 4; j++) {
+						h[j] = __shfl_sync(0xffffffffu, qv[j], 0);
+						tl[j] = __shfl_sync(0xffffffffu, qv[j], 31);
+					}
+					if ((uint32_t) lane < sh) {
+						const uint32_t wv = lane < 4 ? h[0] : lane < 8 ? h[1] : lane < 12 ? h[2] : h[3];
+						D[lane] = (uint8_t) (wv >> (8 * (lane & 3)));
+					}
+					if ((uint32_t) lane < s) {
+						const uint32_t b = sh + lane;	// byte of lane 31's 16
+						const uint32_t wv = b < 4 ? tl[0] : b < 8 ? tl[1] : b < 12 ? tl[2] : tl[3];
+						Wd[512 + lane] = (uint8_t) (wv >> (8 * (b & 3)));
+					}
+				}
+			} else {
+				const uint32_t ne = v.valid & ~v.exc & ~v.first;
+				const uint32_t cnt = __popc(ne);
+				const uint32_t inc = warp_inc_scan(cnt, lane);
+				const uint32_t L = __shfl_sync(0xffffffffu, inc, 31);
+				uint8_t *line = s_line[warp];
+				uint8_t *p = line + (reinterpret_cast<uintptr_t>(D) & 7) + inc - cnt;
+#pragma unroll
+				for (int e = 0; e < 16; e++)
+					if ((ne >> e) & 1)
+						*p++ = (uint8_t) ((qv[e >> 2] >> (8 * (e & 3))));
+				__syncwarp();
+				warp_copy_out(line, D, L, lane);
+				__syncwarp();
+			}
 		}
 	}
 }

@@ -115,9 +115,10 @@ ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples, dou
 		l.tile_start = o;	o += align_up((nreads + 1) * 4, 256);
 		l.kx = o;		o += align_up((nreads + 1) * 8, 256);
 		l.tile_read = o;	o += align_up(xt * 4, 256);
-		for (int i = 0; i < 6; i++) {
+		for (int i = 0; i < 6; i++) {	// [0..2]: 8 records (one per warp) per tile
 			l.x_t[i] = o;
-			o += align_up(xt * 4, 256);
+			if (i < 3)
+				o += align_up(xt * 8 * 4, 256);
 		}
 		for (int i = 0; i < 4; i++) {
 			l.x_r[i] = o;
