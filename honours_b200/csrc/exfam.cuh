@@ -446,7 +446,7 @@ __device__ __forceinline__ bool ex_read_tile0(const ExArgs &a, uint64_t r, ExTil
 // sweep 1: counts, exception capture, stream size
 
 template <bool HUFF>
-__global__ void __launch_bounds__(NT, 4) ex_count_kernel(const __grid_constant__ ExArgs a)
+__global__ void __launch_bounds__(NT, 5) ex_count_kernel(const __grid_constant__ ExArgs a)
 {
 	__shared__ __align__(16) uint32_t s_warp[NW];
 	__shared__ uint32_t s_read, s_or, s_nex;
@@ -610,7 +610,7 @@ __global__ void __launch_bounds__(NT, 4) ex_count_kernel(const __grid_constant__
 // sweep 2: header + payload
 
 template <bool HUFF>
-__global__ void __launch_bounds__(NT, 4) ex_emit_kernel(const __grid_constant__ ExArgs a)
+__global__ void __launch_bounds__(NT, 5) ex_emit_kernel(const __grid_constant__ ExArgs a)
 {
 	__shared__ __align__(16) uint8_t s_stage[HUFF ? X_STAGE : XT + 64];
 	__shared__ __align__(16) uint32_t s_warp[NW];
@@ -774,7 +774,7 @@ __global__ void __launch_bounds__(NT, 4) ex_emit_kernel(const __grid_constant__ 
 // the read is 32 x 16 bytes: re-phased to the destination's 16-byte alignment with
 // shuffles and stored as aligned 128-bit words; anything else goes through a
 // per-warp staging line.
-__global__ void __launch_bounds__(NT, 4) ex_emit_bytes_kernel(const __grid_constant__ ExArgs a)
+__global__ void __launch_bounds__(NT, 5) ex_emit_bytes_kernel(const __grid_constant__ ExArgs a)
 {
 	__shared__ __align__(16) uint8_t s_line[NW][512 + 16];
 	__shared__ uint32_t s_read;

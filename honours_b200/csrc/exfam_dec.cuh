@@ -433,7 +433,7 @@ __global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__
 // ---------------------------------------------------------------------------
 // payload + exceptions -> samples
 
-__global__ void __launch_bounds__(NT, 4) ex_decode_kernel(const __grid_constant__ ExDecArgs a)
+__global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant__ ExDecArgs a)
 {
 	__shared__ __align__(16) uint8_t s_stage[XT + 64];
 	__shared__ __align__(16) uint32_t s_warp[NW];

@@ -80,7 +80,7 @@ __device__ __forceinline__ uint32_t dec_keys_flags(const KeyRaw &k)
 }
 
 template <int KEYBITS, bool FRAME>
-__global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ SvbDec2Args a)
+__global__ void __launch_bounds__(NT, 5) svb_dec_kernel(const __grid_constant__ SvbDec2Args a)
 {
 	__shared__ __align__(16) uint8_t s_in[2 * DT + 64];
 	__shared__ __align__(16) uint32_t s_warp[NW];	// byte-count scans
