@@ -51,9 +51,10 @@ struct ExArgs {
 	Hdr *hdr;			// aux[0] = pool entries used
 	const uint32_t *tile_start, *tile_read;
 	uint32_t *t_nex, *t_pool, *t_eb;	// per (tile, warp): exceptions in the slice, pool position, prefix
-	uint32_t *r_nex, *r_q, *r_hdr;				// per read
-	uint64_t *r_size;
-	uint2 *pool;			// (position in v = sample index - 1, value)
+	uint32_t *r_nex, *r_q, *r_hdr, *r_pool;			// per read
+	uint64_t *r_size, *r_bits;
+	uint2 *pool;			// (position in v = sample index - 1, value), slice by slice as captured
+	uint2 *pool2;			// the same, one contiguous run per read (Hdr aux[3] = entries used)
 	uint64_t pool_cap;
 	const uint32_t *huff_enc;	// 256 x (code | length << 24)
 };
@@ -225,27 +226,10 @@ __device__ __forceinline__ uint32_t ex_elem(const ExVals &v, int e)
 // ---------------------------------------------------------------------------
 // exception lists of a read, addressed by their index k inside the read
 
-// Exceptions are captured per warp slice (512 samples of a tile): record (tile, warp)
-// holds how many, where in the pool, and (after the read has been walked) how many
-// came before it in the read.
+// the exceptions of one read, in order (a run of pool2)
 struct ExList {
-	const uint32_t *t_eb, *t_pool;
-	const uint2 *pool;
-	uint64_t r0;		// first record of the read: 8 per tile
-	uint32_t nrec;
-	__device__ __forceinline__ uint2 at(uint32_t k) const
-	{
-		// last record whose exclusive exception prefix is <= k
-		uint32_t lo = 0, hi = nrec;	// invariant: eb[lo] <= k, eb[hi] > k (hi == nrec: virtual)
-		while (hi - lo > 1) {
-			const uint32_t mid = (lo + hi) >> 1;
-			if (t_eb[r0 + mid] <= k)
-				lo = mid;
-			else
-				hi = mid;
-		}
-		return pool[(uint64_t) t_pool[r0 + lo] + (k - t_eb[r0 + lo])];
-	}
+	const uint2 *p;
+	__device__ __forceinline__ uint2 at(uint32_t k) const { return p[k]; }
 };
 
 // streamvbyte coding of `cnt` values by one warp: KB = 2 classical svb32
@@ -449,7 +433,7 @@ template <bool HUFF>
 __global__ void __launch_bounds__(NT, 5) ex_count_kernel(const __grid_constant__ ExArgs a)
 {
 	__shared__ __align__(16) uint32_t s_warp[NW];
-	__shared__ uint32_t s_read, s_or, s_nex;
+	__shared__ uint32_t s_read, s_or, s_nex, s_base2;
 	__shared__ unsigned long long s_bits;
 	__shared__ uint32_t s_len[HUFF ? 256 : 1];
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -559,50 +543,112 @@ __global__ void __launch_bounds__(NT, 5) ex_count_kernel(const __grid_constant__
 				atomicAdd(&s_bits, (unsigned long long) wb);
 		}
 		const uint32_t nex = s_nex;
-		// exclusive prefix of the slice counts -> t_eb (all records of the read, in order)
+		// exclusive prefix of the slice counts -> t_eb (all records of the read, in order), and
+		// the read's exceptions gathered into one contiguous run of pool2
 		const uint32_t nrec = nt * NW;
-		uint32_t run = 0;
 		if (nex) {
+			if (tid == 0)
+				s_base2 = (uint32_t) atomicAdd((unsigned long long *) &a.hdr->aux[3], (unsigned long long) nex);
+			uint32_t run = 0;
 			for (uint32_t b0 = 0; b0 < nrec; b0 += NT) {
-				__syncthreads();	// records written above / s_warp of the previous round
+				__syncthreads();	// records written above / s_warp of the previous round / s_base2
+				const uint64_t base2 = s_base2;
 				const uint32_t i = b0 + tid;
-				uint32_t c1[1] = {i < nrec ? a.t_nex[rec0 + i] : 0u}, e1[1], tot;
+				const uint32_t c = i < nrec ? a.t_nex[rec0 + i] : 0u;
+				uint32_t c1[1] = {c}, e1[1], tot;
 				block_scan<1>(c1, e1, tot, s_warp);
 				if (i < nrec)
 					a.t_eb[rec0 + i] = run + e1[0];
+				if (c && base2 + nex <= a.pool_cap && (uint64_t) a.t_pool[rec0 + i] + c <= a.pool_cap) {
+					const uint2 *src = a.pool + a.t_pool[rec0 + i];
+					uint2 *dst2 = a.pool2 + base2 + run + e1[0];
+					for (uint32_t j = 0; j < c; j++)
+						dst2[j] = src[j];
+				}
 				run += tot;
 			}
+			if (tid == 0 && (uint64_t) s_base2 + nex > a.pool_cap)
+				atomicOr(&a.hdr->error, ERR_SCRATCH);
 		} else {
 			for (uint32_t i = tid; i < nrec; i += NT)
 				a.t_eb[rec0 + i] = 0;
 		}
-		__syncthreads();	// t_eb and s_bits are read by warp 0 below
-		if (warp == 0) {
-			uint32_t hdr = X_FAIL;
-			uint64_t size = 0;
-			if (!(a.hdr->error & ERR_SCRATCH)) {
-				const ExList L = {a.t_eb, a.t_pool, a.pool, rec0, nrec};
-				hdr = ex_fixed_bytes(a.method) + ex_lists<false>(a.method, L, nex, nullptr, lane);
-				if (HUFF) {
-					hdr += 4;	// [count u32 BE], huffman.c:1199-1203
-					size = hdr + (s_bits + 7) / 8;
-				} else {
-					size = hdr + (n - 1 - nex);
-				}
-				if (a.method == PRESS_GPU_EX_ZD && size > 2 * n + 1024) {	// ex_zd.c:411 scratch cap
-					if (lane == 0)
-						atomicOr(&a.hdr->error, ERR_EXZD_CAP);
-					hdr = X_FAIL;
-					size = 0;
-				}
-			}
-			if (lane == 0) {
-				a.r_nex[r] = nex;
-				a.r_q[r] = q;
-				a.r_hdr[r] = hdr;
-				a.r_size[r] = size;
-			}
+		__syncthreads();
+		if (tid == 0) {
+			a.r_nex[r] = nex;
+			a.r_q[r] = q;
+			a.r_pool[r] = nex ? s_base2 : 0u;
+			a.r_bits[r] = HUFF ? s_bits : 0ull;
 		}
+	}
+}
+
+// header length and stream size of every read.  One warp per read.
+__global__ void __launch_bounds__(NT) ex_size_kernel(const __grid_constant__ ExArgs a)
+{
+	const uint64_t r = ((uint64_t) blockIdx.x * NT + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (r >= a.nreads)
+		return;
+	const uint64_t n = a.offsets[r + 1] - a.offsets[r];
+	uint32_t hdr = X_FAIL;
+	uint64_t size = 0;
+	if (n > 0 && !(a.hdr->error & ERR_SCRATCH)) {
+		const uint32_t nex = a.r_nex[r];
+		const ExList L = {a.pool2 + a.r_pool[r]};
+		hdr = ex_fixed_bytes(a.method) + ex_lists<false>(a.method, L, nex, nullptr, lane);
+		if (a.method == PRESS_GPU_SHUFF_VBE21_ZD) {
+			hdr += 4;	// [count u32 BE], huffman.c:1199-1203
+			size = hdr + (a.r_bits[r] + 7) / 8;
+		} else {
+			size = hdr + (n - 1 - nex);
+		}
+		if (a.method == PRESS_GPU_EX_ZD && size > 2 * n + 1024) {	// ex_zd.c:411 scratch cap
+			if (lane == 0)
+				atomicOr(&a.hdr->error, ERR_EXZD_CAP);
+			hdr = X_FAIL;
+			size = 0;
+		}
+	}
+	if (lane == 0) {
+		a.r_hdr[r] = hdr;
+		a.r_size[r] = size;
+	}
+}
+
+// header and exception lists of every read at their final place.  One warp per read.
+__global__ void __launch_bounds__(NT) ex_header_kernel(const __grid_constant__ ExArgs a)
+{
+	const uint64_t r = ((uint64_t) blockIdx.x * NT + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (r >= a.nreads || (a.hdr->error & (ERR_CAPACITY | ERR_SCRATCH)))
+		return;
+	if (a.r_hdr[r] == X_FAIL)
+		return;
+	const uint64_t off0 = a.offsets[r], n = a.offsets[r + 1] - off0;
+	const uint32_t nex = a.r_nex[r];
+	const uint32_t q = a.method == PRESS_GPU_EX_ZD ? a.r_q[r] : 0u;
+	uint8_t *dst = a.out + a.out_offsets[r];
+	if (lane == 0) {
+		const int16_t x0 = reinterpret_cast<const int16_t *>(a.samples)[off0];
+		const uint16_t s0 = (uint16_t) (int16_t) (x0 >> q);
+		const uint16_t zd0 = (uint16_t) ((uint16_t) (s0 << 1) ^ (uint16_t) (0 - (s0 >> 15)));	// trans.c:75-78
+		uint8_t *p = dst;
+		if (a.method == PRESS_GPU_EX_ZD) {
+			*p++ = 0;		// ex_zd.c:420-423
+			put_le(p, n, 8);	// ex_zd.c:425-428
+			p += 8;
+			*p++ = (uint8_t) q;	// ex_zd.c:436-439
+		}
+		put_le(p, zd0, 2);
+		put_le(p + 2, nex, 4);
+	}
+	const ExList L = {a.pool2 + a.r_pool[r]};
+	const uint32_t fx = ex_fixed_bytes(a.method);
+	const uint32_t ll = ex_lists<true>(a.method, L, nex, dst + fx, lane);
+	if (a.method == PRESS_GPU_SHUFF_VBE21_ZD && lane < 4) {
+		const uint32_t cnt = (uint32_t) (n - 1 - nex);
+		dst[fx + ll + lane] = (uint8_t) (cnt >> (8 * (3 - lane)));	// htonl, huffman.c:1199
 	}
 }
 
@@ -641,29 +687,6 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_kernel(const __grid_constant__ 
 		uint8_t *dst = a.out + a.out_offsets[r];
 		ExRaw W;
 		ex_issue(a.samples, a.nsamples, A, W);
-		if (warp == 0) {	// the header, while the first tile is on its way
-			if (lane == 0) {
-				const int16_t x0 = reinterpret_cast<const int16_t *>(a.samples)[T.off0];
-				const uint16_t s0 = (uint16_t) (int16_t) (x0 >> q);
-				const uint16_t zd0 = (uint16_t) ((uint16_t) (s0 << 1) ^ (uint16_t) (0 - (s0 >> 15)));	// trans.c:75-78
-				uint8_t *p = dst;
-				if (a.method == PRESS_GPU_EX_ZD) {
-					*p++ = 0;		// ex_zd.c:420-423
-					put_le(p, n, 8);	// ex_zd.c:425-428
-					p += 8;
-					*p++ = (uint8_t) q;	// ex_zd.c:436-439
-				}
-				put_le(p, zd0, 2);
-				put_le(p + 2, nex, 4);
-			}
-			const ExList L = {a.t_eb, a.t_pool, a.pool, (uint64_t) g0 * NW, nt * NW};
-			const uint32_t fx = ex_fixed_bytes(a.method);
-			const uint32_t ll = ex_lists<true>(a.method, L, nex, dst + fx, lane);
-			if (HUFF && lane < 4) {
-				const uint32_t cnt = (uint32_t) (n - 1 - nex);
-				dst[fx + ll + lane] = (uint8_t) (cnt >> (8 * (3 - lane)));	// htonl, huffman.c:1199
-			}
-		}
 		uint8_t *pay = dst + hdr;	// first payload byte of the read
 		uint64_t pos = 0;		// payload bytes (bits when HUFF) written so far
 		uint32_t carryb = 0;		// HUFF: the bits of the last, still partial byte
@@ -804,24 +827,6 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_bytes_kernel(const __grid_const
 		ExRaw W;
 		ex_issue(a.samples, a.nsamples, A, W);
 		uint32_t eb_n = __ldg(a.t_eb + rec0), nx_n = __ldg(a.t_nex + rec0);
-		if (warp == 0) {	// the header, while the first tile is on its way
-			if (lane == 0) {
-				const int16_t x0 = reinterpret_cast<const int16_t *>(a.samples)[T.off0];
-				const uint16_t s0 = (uint16_t) (int16_t) (x0 >> q);
-				const uint16_t zd0 = (uint16_t) ((uint16_t) (s0 << 1) ^ (uint16_t) (0 - (s0 >> 15)));	// trans.c:75-78
-				uint8_t *p = dst;
-				if (a.method == PRESS_GPU_EX_ZD) {
-					*p++ = 0;		// ex_zd.c:420-423
-					put_le(p, n, 8);	// ex_zd.c:425-428
-					p += 8;
-					*p++ = (uint8_t) q;	// ex_zd.c:436-439
-				}
-				put_le(p, zd0, 2);
-				put_le(p + 2, nex, 4);
-			}
-			const ExList L = {a.t_eb, a.t_pool, a.pool, (uint64_t) g0 * NW, nt * NW};
-			(void) ex_lists<true>(a.method, L, nex, dst + ex_fixed_bytes(a.method), lane);
-		}
 		uint8_t *pay = dst + hdr;	// first payload byte of the read
 		const int64_t mm = (int64_t) n - 1;
 		for (uint32_t t = 0; t < nt; t++) {

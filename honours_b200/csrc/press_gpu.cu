@@ -125,6 +125,7 @@ ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples, dou
 			o += align_up((nreads + 1) * 4, 256);
 		}
 		l.x_r8[0] = o;		o += align_up((nreads + 1) * 8, 256);
+		l.x_r8[1] = o;		o += align_up((nreads + 1) * 8, 256);
 		l.x_paybuf = o;
 		if (method == PRESS_GPU_SHUFF_VBE21_ZD)
 			o += align_up(nsamples + 64, 256);
@@ -135,7 +136,8 @@ ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples, dou
 		if (cap > nsamples + 1)
 			cap = nsamples + 1;
 		l.x_pool_cap = cap;
-		o += align_up(cap * 8, 256);
+		l.x_pool2 = o + align_up(cap * 8, 256);	// two pools: as captured, and gathered per read
+		o += 2 * align_up(cap * 8, 256);
 		l.total = o;
 		return l;
 	}
@@ -154,14 +156,13 @@ ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples, dou
 ScratchLayout scratch_layout_for(int method, uint64_t nreads, uint64_t nsamples, size_t bytes)
 {
 	ScratchLayout l = scratch_layout(method, nreads, nsamples, 0.0);
-	if (method >= PRESS_GPU_VBE21_ZD && bytes > l.x_pool) {
-		uint64_t cap = (bytes - l.x_pool) / 8;
+	if (method >= PRESS_GPU_VBE21_ZD && bytes > l.total) {
+		uint64_t cap = l.x_pool_cap + (bytes - l.total) / 16 / 256 * 256;	// the two pools share what is left
 		if (cap > nsamples + 1)
 			cap = nsamples + 1;
-		if (cap > l.x_pool_cap) {
-			l.total += (cap - l.x_pool_cap) * 8;
-			l.x_pool_cap = cap;
-		}
+		l.x_pool_cap = cap;
+		l.x_pool2 = l.x_pool + align_up(cap * 8, 256);
+		l.total = l.x_pool + 2 * align_up(cap * 8, 256);
 	}
 	return l;
 }
