@@ -473,6 +473,7 @@ __global__ void __launch_bounds__(NT, 5) ex_count_kernel(const __grid_constant__
 			bits_thr = 0;
 			ExRaw W;
 			ex_issue(a.samples, a.nsamples, A, W);
+#pragma unroll 2
 			for (uint32_t t = 0; t < nt; t++) {
 				T.t = t;
 				T.k0 = A + (uint64_t) t * XG;
@@ -503,10 +504,10 @@ __global__ void __launch_bounds__(NT, 5) ex_count_kernel(const __grid_constant__
 					base = (uint32_t) b64;
 					if (b64 + slice_nex <= a.pool_cap) {
 						uint2 *p = a.pool + b64 + inc - cnt;
-						for (uint32_t mk = v.exc; mk; mk &= mk - 1) {
-							const int e = __ffs(mk) - 1;
-							*p++ = make_uint2((uint32_t) (v.i0 + e - 1), ex_elem(v, e));
-						}
+#pragma unroll
+						for (int e = 0; e < 16; e++)	// (static indices: v.z stays in registers)
+							if ((v.exc >> e) & 1)
+								*p++ = make_uint2((uint32_t) (v.i0 + e - 1), ex_elem(v, e));
 					} else if (lane == 0) {
 						atomicOr(&a.hdr->error, ERR_SCRATCH);
 					}
@@ -829,6 +830,7 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_bytes_kernel(const __grid_const
 		uint32_t eb_n = __ldg(a.t_eb + rec0), nx_n = __ldg(a.t_nex + rec0);
 		uint8_t *pay = dst + hdr;	// first payload byte of the read
 		const int64_t mm = (int64_t) n - 1;
+#pragma unroll 2
 		for (uint32_t t = 0; t < nt; t++) {
 			T.t = t;
 			T.k0 = A + (uint64_t) t * XG;
