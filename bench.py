@@ -391,10 +391,16 @@ def run_ours(args):
                     "traffic": None, "peak_source": peak_src,
                     "alg_bytes_per_launch": kern[dom]["alg_bytes_per_launch"],
                     "ms_per_launch": kern[dom]["ms_per_launch"]}
+        # DRAM bytes of that kernel from the committed ncu --set full capture (profiles/traffic.json,
+        # taken on a shorter run of this same command), scaled to this run's launch by the
+        # algorithmic bytes of the two launches
         tr = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tr):
             try:
-                roofline["traffic"] = json.load(open(tr)).get(f"{method}_{dom}")
+                ent = json.load(open(tr)).get(f"{method}_{dom}")
+                if ent:
+                    roofline["traffic"] = ent["dram_bytes"] * kern[dom]["alg_bytes_per_launch"] / ent["alg_bytes"]
+                    roofline["traffic_source"] = ent.get("source")
             except Exception:
                 pass
 

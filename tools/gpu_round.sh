@@ -1,29 +1,28 @@
 #!/bin/bash
-# One gpurun call: GPU parity tests, the bench line, then ncu (launch list + one
-# full capture of the codec kernels) on a short configuration of the same bench.
-#   gpurun --timeout 1700 -- 'bash tools/gpu_round.sh [method] [tag]'
-# Everything lands in gpurun_out/ (scratch); copy what should be judged into profiles/.
-METHOD=${1:-svb16_zd}
-TAG=${2:-r1}
-KREGEX=${3:-svb_zd}
+# One gpurun call for the round's evidence: GPU tests, smoke, the default bench line and
+# the reference arm, the other methods on one chunk, then ncu (launch list + full capture of
+# the two svb16 kernels) on a short configuration of the same bench command.
+#   gpurun --timeout 1700 -- 'bash tools/gpu_round.sh TAG'
+# Everything lands in gpurun_out/ (scratch); tools/profile_digest.py copies digests to profiles/.
+TAG=${1:-r01b}
 O=gpurun_out
 mkdir -p $O
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw,memory.total --format=csv > $O/smi_$TAG.csv 2>&1
-python -m pytest tests -m gpu -x -q > $O/pytest_gpu_$TAG.log 2>&1
-echo "pytest exit $?" | tee -a $O/pytest_gpu_$TAG.log
-tail -3 $O/pytest_gpu_$TAG.log
-python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke_$TAG.log 2>&1
-echo "smoke exit $?" | tee -a $O/smoke_$TAG.log
-python bench.py --method $METHOD --steps 3 --warmup 3 > $O/bench_${METHOD}_$TAG.json 2> $O/bench_${METHOD}_$TAG.err
-echo "bench exit $?"
-cat $O/bench_${METHOD}_$TAG.json
-SHORT="python bench.py --method $METHOD --reads 5000 --steps 1 --warmup 1 --no-e2e --no-cpu-baseline"
+python -m pytest tests -m gpu -x -q > $O/pytest_gpu_$TAG.log 2>&1; echo "pytest exit $?"; tail -2 $O/pytest_gpu_$TAG.log
+python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke_$TAG.log 2>&1; echo "smoke exit $?"; tail -2 $O/smoke_$TAG.log
+python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_ref_$TAG.json 2> $O/bench_ref_$TAG.err; echo "ref exit $?"
+python bench.py > $O/bench_svb16_zd_$TAG.json 2> $O/bench_svb16_zd_$TAG.err; echo "bench exit $?"; tail -2 $O/bench_svb16_zd_$TAG.err
+for m in svb_zd vbz_svb16_zd vbz_svb_zd vbe21_zd vbsse21_zd ex_zd shuff_vbe21_zd; do
+  python bench.py --method $m --reads 125000 --steps 3 --warmup 3 --e2e-gb 1.0 --cpu-reads 1500 --cpu-seconds 4 \
+      > $O/bench_${m}_$TAG.json 2> $O/bench_${m}_$TAG.err; echo "$m exit $?"
+done
+SHORT="python bench.py --reads 8000 --steps 1 --warmup 1 --no-e2e --no-cpu-baseline"
 $SHORT > $O/plain_$TAG.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
-    --log-file $O/launches_${METHOD}_$TAG.csv $SHORT > $O/ncu_list_$TAG.log 2>&1
+    --log-file $O/launches_svb16_zd_$TAG.csv $SHORT > $O/ncu_list_$TAG.log 2>&1
 echo "ncu list exit $?"
 $SHORT > $O/plain2_$TAG.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:$KREGEX -s 2 -c 2 \
-    -f -o $O/prof_${METHOD}_$TAG $SHORT > $O/ncu_full_$TAG.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:svb_ -s 2 -c 2 \
+    -f -o $O/prof_svb16_zd_$TAG $SHORT > $O/ncu_full_$TAG.log 2>&1
 echo "ncu full exit $?"
-ls -la $O
+ls $O | grep $TAG
