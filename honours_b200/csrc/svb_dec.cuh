@@ -48,6 +48,22 @@ struct KeyRaw {
 	uint32_t w0, w1, sh, skip;
 };
 
+// interior tiles of a read whose key section ends >= 8 bytes before the container does:
+// i0 >= 0 and both words are readable, so no guard is needed
+template <int KEYBITS>
+__device__ __forceinline__ KeyRaw dec_keys_issue_fast(const uint8_t *keys, uint64_t i0)
+{
+	KeyRaw k;
+	k.skip = 0;
+	const uint8_t *p = keys + (KEYBITS == 1 ? i0 >> 3 : i0 >> 2);
+	const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(p) & 3);
+	const uint32_t *pw = reinterpret_cast<const uint32_t *>(p - al);
+	k.sh = 8 * al + (KEYBITS == 1 ? (uint32_t) (i0 & 7) : 2 * (uint32_t) (i0 & 3));
+	k.w0 = __ldg(pw);
+	k.w1 = __ldg(pw + 1);
+	return k;
+}
+
 template <int KEYBITS>
 __device__ __forceinline__ KeyRaw dec_keys_issue(const uint8_t *keys, int64_t i0, const uint8_t *lo, const uint8_t *hi)
 {
@@ -80,7 +96,7 @@ __device__ __forceinline__ uint32_t dec_keys_flags(const KeyRaw &k)
 }
 
 template <int KEYBITS, bool FRAME>
-__global__ void __launch_bounds__(NT, 5) svb_dec_kernel(const __grid_constant__ SvbDec2Args a)
+__global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ SvbDec2Args a)
 {
 	__shared__ __align__(16) uint8_t s_in[2 * DT + 64];
 	__shared__ __align__(16) uint32_t s_warp[NW];	// byte-count scans
@@ -159,12 +175,18 @@ __global__ void __launch_bounds__(NT, 5) svb_dec_kernel(const __grid_constant__ 
 			}
 		};
 
+		const bool keys_safe = keys + nkeys + 8 <= limit;
+		auto keys_of = [&](uint32_t t) -> KeyRaw {
+			if (keys_safe && t >= 1)	// (tile 0 may start before the read: i0 < 0)
+				return dec_keys_issue_fast<KEYBITS>(keys, (uint64_t) first_of(t));
+			return dec_keys_issue<KEYBITS>(keys, first_of(t), a.in, limit);
+		};
 		// ---- prologue: tile 0 scanned and its data requested, keys of tile 1 requested
 		uint32_t va_cur = valid_of(0);
 		uint32_t fl_cur = dec_keys_flags<KEYBITS>(dec_keys_issue<KEYBITS>(keys, first_of(0), a.in, limit)) & va_cur;
 		KeyRaw k_next = {0, 0, 0, 0};
 		if (ntiles > 1)
-			k_next = dec_keys_issue<KEYBITS>(keys, first_of(1), a.in, limit);
+			k_next = keys_of(1);
 		uint32_t ex_cur, L_cur;
 		{
 			uint32_t c1[1] = {(uint32_t) (__popc(va_cur) + __popc(fl_cur))}, e1[1];
@@ -195,15 +217,21 @@ __global__ void __launch_bounds__(NT, 5) svb_dec_kernel(const __grid_constant__ 
 			if (t + 1 < ntiles) {
 				va_n = valid_of(t + 1);
 				fl_n = dec_keys_flags<KEYBITS>(k_next) & va_n;
-				uint32_t c1[1] = {(uint32_t) (__popc(va_n) + __popc(fl_n))}, e1[1];
-				block_scan<1>(c1, e1, L_n, s_warp);	// (its barriers also publish s_in)
-				ex_n = e1[0];
+				// (the barrier inside either branch also publishes s_in)
+				if (!__syncthreads_or(fl_n != 0 || va_n != 0xffffu)) {
+					ex_n = 16 * tid;	// 4096 one-byte values: no scan needed
+					L_n = DT;
+				} else {
+					uint32_t c1[1] = {(uint32_t) (__popc(va_n) + __popc(fl_n))}, e1[1];
+					block_scan<1>(c1, e1, L_n, s_warp);
+					ex_n = e1[0];
+				}
 				if (D + L_cur + L_n > ndata)
 					overrun = true;
 				else
 					issue_data(D + L_cur, L_n);
 				if (t + 2 < ntiles)
-					k_next = dec_keys_issue<KEYBITS>(keys, first_of(t + 2), a.in, limit);
+					k_next = keys_of(t + 2);
 			} else {
 				__syncthreads();
 			}
