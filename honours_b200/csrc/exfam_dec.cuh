@@ -438,6 +438,7 @@ __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant_
 	__shared__ __align__(16) uint8_t s_stage[XT + 64];
 	__shared__ __align__(16) uint32_t s_warp[NW];
 	__shared__ uint32_t s_read, s_e;
+	__shared__ uint2 s_ex[NT];	// the next 256 exceptions of the read (position, value)
 	const int tid = threadIdx.x;
 	const bool shuff = a.method == PRESS_GPU_SHUFF_VBE21_ZD;
 	const uint8_t *lim_lo = shuff ? a.paybuf : a.in;
@@ -484,8 +485,16 @@ __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant_
 			}
 		};
 		const uint32_t t_hi = (uint32_t) ((m + n) / XT);	// tiles [1, t_hi) lie inside the read
+		// the read's next 256 exceptions travel with the payload: requested one tile ahead,
+		// staged in shared memory, so the per-tile and per-thread searches never go to HBM
+		uint2 exreg = make_uint2(0xffffffffu, 0u);
+		auto issue_ex = [&](uint32_t e0) {
+			exreg = e0 + tid < nex ? ex[e0 + tid] : make_uint2(0xffffffffu, 0u);
+		};
 		uint32_t e_lo = 0, carry = 0;
 		issue(0, 0);
+		if (nex)
+			issue_ex(0);
 		for (uint32_t t = 0; t < nt; t++) {
 			const uint32_t j_lo = ex_v_before(t, m, n), j_hi = ex_v_before(t + 1, m, n);
 			const uint32_t p_lo = j_lo - e_lo;
@@ -497,21 +506,38 @@ __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant_
 				if (tid == 0 && nw > NT)
 					reinterpret_cast<uint4 *>(s_stage)[NT] = dreg[1];
 			}
-			if (nex && tid == 0) {	// exceptions before the end of this tile: lower_bound on the positions
-				uint32_t lo = e_lo, hi = nex;
-				while (lo < hi) {
-					const uint32_t mid = (lo + hi) >> 1;
-					if (ex[mid].x < j_hi)
-						lo = mid + 1;
-					else
-						hi = mid;
+			uint32_t e_hi = 0;
+			const uint2 *xs = ex;	// where exceptions [e_lo, e_hi) are read from
+			if (!nex) {
+				__syncthreads();
+			} else {
+				s_ex[tid] = exreg;
+				// exceptions before the end of this tile = staged positions below j_hi
+				const uint32_t k = (uint32_t) __syncthreads_count(exreg.x < j_hi);
+				if (k < NT) {
+					e_hi = e_lo + k;
+					xs = s_ex - e_lo;
+				} else {	// more than 255 in one tile: lower_bound over the whole list
+					if (tid == 0) {
+						uint32_t lo = e_lo, hi = nex;
+						while (lo < hi) {
+							const uint32_t mid = (lo + hi) >> 1;
+							if (ex[mid].x < j_hi)
+								lo = mid + 1;
+							else
+								hi = mid;
+						}
+						s_e = lo;
+					}
+					__syncthreads();
+					e_hi = s_e;
 				}
-				s_e = lo;
 			}
-			__syncthreads();
-			const uint32_t e_hi = nex ? s_e : 0u;
-			if (t + 1 < nt)
+			if (t + 1 < nt) {
 				issue(t + 1, e_hi);
+				if (nex)
+					issue_ex(e_hi);
+			}
 			// ---- zd values of the thread's 16 elements
 			const uint64_t ka = A + (uint64_t) t * XG + 2 * tid;
 			const int64_t f = (int64_t) t * XT - m;		// read index of the tile's first element
@@ -536,14 +562,30 @@ __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant_
 						const int64_t key = jf < 0 ? 0 : jf;
 						while (lo < hi) {
 							const uint32_t mid = (lo + hi) >> 1;
-							if ((int64_t) ex[mid].x < key)
+							if ((int64_t) xs[mid].x < key)
 								lo = mid + 1;
 							else
 								hi = mid;
 						}
 						e = lo;
 					}
-					uint32_t nextpos = e < e_hi ? ex[e].x : 0xffffffffu;
+					uint32_t nextpos = e < e_hi ? xs[e].x : 0xffffffffu;
+					if (valid == 0xffffu && jf >= 0 && (uint64_t) nextpos >= (uint64_t) jf + 16) {
+						// no exception among the thread's 16 values: 16 payload bytes in a row
+						const uint32_t pp = al + ((uint32_t) jf - e - p_lo);
+						const uint32_t *w32 = reinterpret_cast<const uint32_t *>(s_stage) + (pp >> 2);
+						const uint32_t sh = (pp & 3) * 8;
+						uint32_t w[5];
+#pragma unroll
+						for (int j = 0; j < 5; j++)
+							w[j] = w32[j];
+#pragma unroll
+						for (int j = 0; j < 4; j++) {
+							const uint32_t v = __funnelshift_r(w[j], w[j + 1], sh);
+							zz[2 * j] = __byte_perm(v, 0, 0x4140);
+							zz[2 * j + 1] = __byte_perm(v, 0, 0x4342);
+						}
+					} else
 #pragma unroll
 					for (int el = 0; el < 16; el++) {
 						if ((valid >> el) & 1) {
@@ -552,9 +594,9 @@ __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant_
 							if (j < 0) {
 								z = zd0;
 							} else if ((uint32_t) j == nextpos) {
-								z = ex[e].y;
+								z = xs[e].y;
 								e++;
-								nextpos = e < e_hi ? ex[e].x : 0xffffffffu;
+								nextpos = e < e_hi ? xs[e].x : 0xffffffffu;
 							} else {
 								z = st[(uint32_t) j - e - p_lo];
 							}
