@@ -30,7 +30,7 @@ struct ExDecArgs {
 	uint2 *pool;
 	uint64_t pool_cap;
 	uint8_t *paybuf;		// SHUFF: symbols of read r at paybuf + offsets[r]
-	const uint16_t *huff_dec;	// 4096 x (length << 8 | symbol), or 0x8000 | k: see hd_run
+	const uint32_t *huff_dec;	// 4096 two-symbol entries: see hd_run
 	const uint16_t *huff_sub;	// second level: [k][1 << huff_sub_bits]
 	uint32_t huff_sub_bits, huff_minlen;
 };
@@ -275,55 +275,115 @@ constexpr int HD_SLOT = HD_SUB / 4;		// symbols a sub-block can hold when no cod
 constexpr int HD_SYM = NT * HD_SLOT;		// symbol stage
 constexpr int HD_L1 = 12;			// first-level table: 12 bits
 
-// Decode codes starting at stage bit `pos` until pos >= end; returns the new pos and
-// the number of symbols in cnt; stores symbol i at dst[i] for i < lim (dst may be null).
-// Two table levels, no tree walk (a walk taken by one lane stalls the other 31):
-// lut[w & 4095] = length << 8 | symbol for codes of <= 12 bits, else 0x8000 | k, and
-// sub[k][(w >> 12) & mask] resolves the rest of the code.
-// word j of the staged bitstream lives at hd_swz(j): the lanes of a warp work on
-// sub-blocks 4 words apart, this puts their current words in different banks
-constexpr int HD_ROW = NT + 8;
-__device__ __forceinline__ uint32_t hd_swz(uint32_t j) { return (j & 3u) * HD_ROW + (j >> 2); }
+// Decode the codes of one sub-block that start at bit `pos` (relative to the sub-block)
+// or later; returns the position of the first code of the NEXT sub-block (>= HD_SUB) and
+// the number of symbols in cnt.  MODE 0 counts only; 1 stores symbol i at dst[i * STRIDE]
+// (the caller knows they fit); 2 stores those with i < lim.  Table levels, no tree walk
+// (a walk taken by one lane stalls the other 31):
+//   lut[w & 4095]: codes of <= 12 bits: symbol | symbol2 << 8 | length2 << 16 | length << 24,
+//                  where symbol2 is the NEXT code when it also fits in the 12 bits
+//                  (length2 = 0 if not) -- two symbols per lookup on most of the stream;
+//                  longer codes: bit 31 | k, and sub[k][(w >> 12) & mask] = length << 8 | symbol.
+// The staged bitstream is transposed: word j of thread t's sub-block at sw[j * NT + t],
+// j = 0..4 (row 4 = the next sub-block's first word), so whatever words the lanes of a warp
+// are at, they read 32 different banks, and the second word of a window is one row further.
+constexpr int HD_ROW = NT;
 
-template <int STRIDE>	// symbol i goes to dst[i * STRIDE]
-__device__ __forceinline__ uint32_t hd_run(const uint32_t *sw, const uint16_t *lut, const uint16_t *sub,
-					   uint32_t sub_bits, uint32_t pos, uint32_t end, uint32_t &cnt,
-					   uint8_t *dst, uint32_t lim)
+// a code longer than the first-level table (rare; kept out of line so that its instructions
+// do not ride, predicated off, through every turn of the decode loops)
+__device__ __noinline__ uint32_t hd_long(uint32_t e, uint32_t w, const uint16_t *sub, uint32_t sub_bits)
+{
+	const uint32_t e1 = __ldg(sub + (((e & 0x7fffu) << sub_bits) | ((w >> HD_L1) & ((1u << sub_bits) - 1))));
+	return (e1 & 0xffu) | ((e1 >> 8) << 24);
+}
+
+__device__ __forceinline__ uint32_t hd_lookup(uint32_t swt_sa, uint32_t lut_sa, const uint16_t *sub, uint32_t sub_bits,
+					      uint32_t pos)
+{
+	// shared-window addresses by hand: word (pos >> 5) of the thread's column and the next row
+	const uint32_t wa = swt_sa + ((pos & 0x60u) << 5);
+	uint32_t w0, w1, e;
+	asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w0) : "r"(wa));
+	asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(w1) : "r"(wa), "n"(HD_ROW * 4));
+	const uint32_t w = __funnelshift_r(w0, w1, pos);
+	asm volatile("ld.shared.u32 %0, [%1];" : "=r"(e) : "r"(lut_sa + ((w & ((1u << HD_L1) - 1)) << 2)));
+	if (__builtin_expect((int32_t) e < 0, 0))
+		e = hd_long(e, w, sub, sub_bits);
+	return e;
+}
+
+// The slot pass (tables with >= 4-bit codes): turn i of the loop leaves its one or two
+// symbols as a 16-bit pair at pairs[i * NT] (i is the same in every lane, so the lanes'
+// stores fall into different banks) and bit i of `two` says whether the second one counts.
+__device__ __forceinline__ uint32_t hd_run_pairs(uint32_t swt_sa, uint32_t lut_sa, const uint16_t *sub, uint32_t sub_bits,
+						 uint32_t pos, uint32_t &turns, uint32_t &two, uint16_t *pairs)
+{
+	uint32_t i = 0, bit = 1u, m = 0;
+	while (pos < (uint32_t) HD_SUB) {
+		const uint32_t e = hd_lookup(swt_sa, lut_sa, sub, sub_bits, pos);
+		pairs[i * NT] = (uint16_t) e;
+		pos += e >> 24;
+		const uint32_t l2 = (e >> 16) & 0xffu;
+		if (l2 && pos < (uint32_t) HD_SUB) {	// the second code starts inside the sub-block as well
+			pos += l2;
+			m |= bit;
+		}
+		bit <<= 1;
+		i++;
+	}
+	turns = i;
+	two = m;
+	return pos;
+}
+
+// The generic pass: MODE 0 counts the symbols only; 2 stores symbol i at dst[i] for i < lim.
+template <int MODE>
+__device__ __forceinline__ uint32_t hd_run(uint32_t swt_sa, uint32_t lut_sa, const uint16_t *sub, uint32_t sub_bits,
+					   uint32_t pos, uint32_t &cnt, uint8_t *dst, uint32_t lim)
 {
 	uint32_t c = 0;
-	while (pos < end) {
-		const uint32_t j = pos >> 5;
-		const uint32_t w = __funnelshift_r(sw[hd_swz(j)], sw[hd_swz(j + 1)], pos & 31);
-		uint32_t e = lut[w & ((1u << HD_L1) - 1)];
-		if (e & 0x8000u)
-			e = __ldg(sub + (((e & 0x7fffu) << sub_bits) | ((w >> HD_L1) & ((1u << sub_bits) - 1))));
-		if (dst && c < lim)
-			dst[c * STRIDE] = (uint8_t) e;
+	while (pos < (uint32_t) HD_SUB) {
+		const uint32_t e = hd_lookup(swt_sa, lut_sa, sub, sub_bits, pos);
+		if (MODE == 2 && c < lim)
+			dst[c] = (uint8_t) e;
 		c++;
-		pos += e >> 8;
+		pos += e >> 24;
+		const uint32_t l2 = (e >> 16) & 0xffu;
+		if (l2 && pos < (uint32_t) HD_SUB) {
+			if (MODE == 2 && c < lim)
+				dst[c] = (uint8_t) (e >> 8);
+			c++;
+			pos += l2;
+		}
 	}
 	cnt = c;
 	return pos;
 }
 
-__global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__ ExDecArgs a)
+__global__ void __launch_bounds__(NT, 6) huff_decode_kernel(const __grid_constant__ ExDecArgs a)
 {
-	__shared__ uint32_t s_w[4 * HD_ROW];
-	__shared__ uint16_t s_lut[1 << HD_L1];
-	__shared__ uint32_t s_exit[NT];
+	__shared__ uint32_t s_lut[1 << HD_L1];
+	__shared__ uint32_t s_exit[2][NT];
 	__shared__ __align__(16) uint32_t s_warp[NW];
 	__shared__ uint32_t s_read;
 	// the step's symbols, in order, before they leave as aligned 128-bit stores (a byte
 	// store per symbol costs one L2 transaction each: that alone bounded the kernel)
 	__shared__ __align__(16) uint8_t s_sym[HD_SYM + 32];
 	// with no code shorter than 4 bits every pass leaves the sub-block's symbols in the
-	// thread's own slot, so nothing is decoded again once the entry points have settled
-	__shared__ __align__(16) uint8_t s_slot[HD_SYM];
+	// thread's own slots (hd_run_pairs: at most 32 turns), so nothing is decoded again once
+	// the entry points have settled.  (Tables with shorter codes take counting passes and one
+	// more storing pass.)
+	__shared__ __align__(16) uint16_t s_pair[HD_SLOT * NT];
 	const int tid = threadIdx.x;
 	const bool slots = a.huff_minlen >= 4;
 	const uint16_t *sub = a.huff_sub;
 	const uint32_t sub_bits = a.huff_sub_bits;
-	uint8_t *myslot = slots ? s_slot + tid : nullptr;	// symbol c of thread tid at s_slot[c * NT + tid]
+	uint16_t *mypairs = s_pair + tid;
+	// the staged bitstream (5 * HD_ROW words) lives in whichever of the two is idle while
+	// codes are decoded: the symbol stage with slots, the slots without
+	uint32_t *s_w = reinterpret_cast<uint32_t *>(slots ? s_sym : reinterpret_cast<uint8_t *>(s_pair));
+	const uint32_t swt_sa = (uint32_t) __cvta_generic_to_shared(s_w + tid);
+	const uint32_t lut_sa = (uint32_t) __cvta_generic_to_shared(s_lut);
 	for (int i = tid; i < (1 << HD_L1); i += NT)
 		s_lut[i] = a.huff_dec[i];
 	for (;;) {
@@ -344,14 +404,15 @@ __global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__
 		const uint8_t *src = a.in + bs0, *limit = a.in + a.in_bytes;
 		uint32_t entry = 0;	// bit offset of the first code inside the step
 		int64_t done = 0;	// symbols out so far
+		uint64_t steps = 0, rounds = 0;
 		for (uint64_t cb = 0; cb < nbytes && done < count; cb += HD_CHUNK) {
-			// stage HD_CHUNK + 32 bytes of the bitstream from byte cb, zero filled past its end
+			// stage HD_CHUNK + 4 bytes of the bitstream from byte cb, zero filled past its end
 			const uint64_t left = nbytes - cb;
 			{
 				const uint8_t *s = src + cb;
 				const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(s) & 3);
 				const uint32_t *gw = reinterpret_cast<const uint32_t *>(s - al);
-				for (uint32_t w = tid; w < HD_CHUNK / 4 + 8; w += NT) {
+				for (uint32_t w = tid; w <= HD_CHUNK / 4; w += NT) {
 					uint32_t v = 0;
 					if (4ull * w < left) {
 						const uint8_t *p0 = reinterpret_cast<const uint8_t *>(gw + w);
@@ -362,71 +423,82 @@ __global__ void __launch_bounds__(NT) huff_decode_kernel(const __grid_constant__
 								v |= (uint32_t) s[4ull * w + b] << (8 * b);
 						}
 					}
-					s_w[hd_swz(w)] = v;
+					if (w < HD_CHUNK / 4)
+						s_w[(w & 3u) * HD_ROW + (w >> 2)] = v;
+					if ((w & 3u) == 0 && w)
+						s_w[4 * HD_ROW + (w >> 2) - 1] = v;
 				}
 			}
 			__syncthreads();
 			const uint32_t cbits = left < HD_CHUNK ? (uint32_t) left * 8 : HD_CHUNK * 8;
 			const uint32_t nsub = (cbits + HD_SUB - 1) / HD_SUB;
 			const bool act = (uint32_t) tid < nsub;
-			const uint32_t lo = tid * HD_SUB, hi = lo + HD_SUB;
-			uint32_t cur = tid == 0 ? entry : 0u, cnt = 0, ex = 0;
-			if (act)
-				ex = hd_run<NT>(s_w, s_lut, sub, sub_bits, lo + cur, hi, cnt, myslot, HD_SLOT) - hi;
-			s_exit[tid] = ex;
-			uint32_t rounds = 0;
-			for (;;) {
-				rounds++;
-				__syncthreads();
-				const uint32_t e = tid ? s_exit[tid - 1] : entry;
-				const bool ch = act && e != cur;
-				if (ch) {
+			uint32_t cur = tid == 0 ? entry : 0u, cnt = 0, two = 0, ex = 0;	// (cnt: turns with slots)
+			if (act) {
+				if (slots)
+					ex = hd_run_pairs(swt_sa, lut_sa, sub, sub_bits, cur, cnt, two, mypairs) - HD_SUB;
+				else
+					ex = hd_run<0>(swt_sa, lut_sa, sub, sub_bits, cur, cnt, nullptr, 0) - HD_SUB;
+			}
+			s_exit[0][tid] = ex;
+			__syncthreads();
+			uint32_t rd = 0;
+			for (;;) {	// until no exit moved (exits double buffered: one barrier per round)
+				rd++;
+				const uint32_t e = tid ? s_exit[(rd - 1) & 1][tid - 1] : entry;
+				bool moved = false;
+				if (act && e != cur) {
 					cur = e;
-					// an entry point past the sub-block: no code starts here
-					if (lo + cur >= hi) {
-						cnt = 0;
-						ex = lo + cur - hi;
-					} else {
-						ex = hd_run<NT>(s_w, s_lut, sub, sub_bits, lo + cur, hi, cnt, myslot, HD_SLOT) - hi;
-					}
+					uint32_t x;
+					if (slots)
+						x = hd_run_pairs(swt_sa, lut_sa, sub, sub_bits, cur, cnt, two, mypairs) - HD_SUB;
+					else
+						x = hd_run<0>(swt_sa, lut_sa, sub, sub_bits, cur, cnt, nullptr, 0) - HD_SUB;
+					moved = x != ex;
+					ex = x;
 				}
-				const int any = __syncthreads_or(ch);
-				if (ch)
-					s_exit[tid] = ex;
-				if (!any)
+				s_exit[rd & 1][tid] = ex;
+				if (!__syncthreads_or(moved))
 					break;
 			}
-			uint32_t c1[1] = {act ? cnt : 0u}, ex1[1], tot;
+			const uint32_t nsym = slots ? cnt + __popc(two) : cnt;
+			uint32_t c1[1] = {act ? nsym : 0u}, ex1[1], tot;
 			block_scan<1>(c1, ex1, tot, s_warp);
 			if (tot <= HD_SYM) {
-				if (act && cnt) {
+				if (act && nsym) {
 					if (slots) {
-						for (uint32_t c = 0; c < cnt; c++)
-							s_sym[ex1[0] + c] = myslot[c * NT];
+						uint8_t *o = s_sym + ex1[0];
+						for (uint32_t i = 0; i < cnt; i++) {
+							const uint32_t pr = mypairs[i * NT];
+							*o++ = (uint8_t) pr;
+							if ((two >> i) & 1u)
+								*o++ = (uint8_t) (pr >> 8);
+						}
 					} else {
 						uint32_t dummy;
-						(void) hd_run<1>(s_w, s_lut, sub, sub_bits, lo + cur, hi, dummy, s_sym + ex1[0], cnt);
+						(void) hd_run<2>(swt_sa, lut_sa, sub, sub_bits, cur, dummy, s_sym + ex1[0], nsym);
 					}
 				}
 				__syncthreads();
 				const int64_t room = count - done;
 				block_copy_out(s_sym, dst + done, (uint32_t) ((int64_t) tot < room ? tot : room));
-			} else if (act && cnt) {	// a table with very short codes: more symbols than the stage holds
+			} else if (act && nsym) {	// a table with very short codes: more symbols than the stage holds
 				uint32_t dummy;
 				const int64_t first = done + ex1[0], room = count - first;
-				(void) hd_run<1>(s_w, s_lut, sub, sub_bits, lo + cur, hi, dummy, dst + first,
+				(void) hd_run<2>(swt_sa, lut_sa, sub, sub_bits, cur, dummy, dst + first,
 						 room > 0 ? (uint32_t) (room < 0xffffffffll ? room : 0xffffffffll) : 0u);
 			}
-			entry = s_exit[nsub - 1];
+			entry = s_exit[rd & 1][nsub - 1];
 			done += tot;
-			if (tid == 0) {	// statistics: steps and re-synchronisation rounds (press_gpu_debug_aux)
-				atomicAdd((unsigned long long *) &a.hdr->aux[1], 1ull);
-				atomicAdd((unsigned long long *) &a.hdr->aux[2], (unsigned long long) rounds);
-			}
+			steps++, rounds += rd;
 			__syncthreads();
 		}
-		if (done < count && tid == 0)
-			atomicOr(&a.hdr->error, ERR_MALFORMED);	// bitstream shorter than its symbol count
+		if (tid == 0) {	// statistics: steps and re-synchronisation rounds (press_gpu_debug_aux)
+			atomicAdd((unsigned long long *) &a.hdr->aux[1], (unsigned long long) steps);
+			atomicAdd((unsigned long long *) &a.hdr->aux[2], (unsigned long long) rounds);
+			if (done < count)
+				atomicOr(&a.hdr->error, ERR_MALFORMED);	// bitstream shorter than its symbol count
+		}
 	}
 }
 

@@ -222,3 +222,72 @@ def test_huffman_decodes_oracle_streams_without_sidecar(gpu, oracle):
         assert ro == 0
         rc, back = gpu.depress("shuff_vbe21_zd", so, n)
         assert rc == 0 and np.array_equal(back, s), n
+
+
+def _huffman_table_blob(freq):
+    """A code-table file image (huffman.c:440-480 layout) of the Huffman code of `freq`:
+    [count u32 BE][data bytes u32 BE] then per symbol [sym][nbits][code bytes, bit k of the
+    code at bit k % 8 of byte k / 8]."""
+    import heapq
+    import struct
+    heap = [(float(f), i, (i,)) for i, f in enumerate(freq)]
+    heapq.heapify(heap)
+    lens = [0] * 256
+    tick = 256
+    while len(heap) > 1:
+        fa, _, sa = heapq.heappop(heap)
+        fb, _, sb = heapq.heappop(heap)
+        for s in sa + sb:
+            lens[s] += 1
+        heapq.heappush(heap, (fa + fb, tick, sa + sb))
+        tick += 1
+    assert max(lens) <= 24 and min(lens) >= 1
+    blob = struct.pack(">II", 256, 0)
+    code = 0
+    prev = 0
+    for ln, sym in sorted((lens[s], s) for s in range(256)):    # canonical codes, first bit = MSB
+        code <<= ln - prev
+        prev = ln
+        bits = [(code >> (ln - 1 - k)) & 1 for k in range(ln)]
+        raw = bytearray((ln + 7) // 8)
+        for k, b in enumerate(bits):
+            raw[k // 8] |= b << (k % 8)
+        blob += bytes([sym, ln]) + bytes(raw)
+        code += 1
+    return blob, lens
+
+
+@pytest.mark.parametrize("shape", ["short_codes", "long_codes"])
+def test_huffman_custom_tables(gpu, oracle, shape):
+    """other code tables than NA12878_zd.huffman: one whose shortest code has 1 bit (more
+    symbols per 4 KB step than the symbol stage holds: the generic decoder) and one with
+    >= 4-bit codes and a long tail beyond the 12-bit first-level table"""
+    if shape == "short_codes":
+        freq = [2.0 ** -min(k, 22) + 1e-9 * (256 - k) for k in range(256)]
+    else:
+        freq = [1.0] * 16 + [2.0 ** -(3 + k / 20) for k in range(240)]
+    blob, lens = _huffman_table_blob(freq)
+    assert (min(lens) < 4) == (shape == "short_codes") and max(lens) > 12
+    na12878 = open(os.path.join(os.path.dirname(GOLD), "..", "honours_b200", "data", "NA12878_zd.huffman"), "rb").read()
+    rng = np.random.default_rng(99)
+    try:
+        oracle.set_huffman_table(blob)
+        gpu.set_huffman_table(blob)
+        reads = [np.full(40000, 7, np.int16), rand_read(rng, "walk", 50001), rand_read(rng, "spiky", 9000),
+                 (500 + np.cumsum(rng.integers(-1, 2, 120000))).astype(np.int16), rand_read(rng, "noise", 3000)]
+        for s in reads:
+            ro, so = oracle.press("shuff_vbe21_zd", s)
+            rc, st = gpu.press("shuff_vbe21_zd", s)
+            assert rc == ro == 0 and st == so
+            rc, back = gpu.depress("shuff_vbe21_zd", so, s.size)
+            assert rc == 0 and np.array_equal(back, s)
+        lengths = [r.size for r in reads]
+        offsets = np.concatenate([[0], np.cumsum(lengths)]).astype(np.uint64)
+        samples = np.concatenate(reads)
+        rc, cont, oo = gpu.batch_press_host("shuff_vbe21_zd", samples, offsets)
+        assert rc == 0
+        assert cont.tobytes() == b"".join(oracle.press("shuff_vbe21_zd", s)[1] for s in reads)
+        assert np.array_equal(gpu.batch_depress_host("shuff_vbe21_zd", cont, oo, offsets), samples)
+    finally:
+        oracle.set_huffman_table(na12878)
+        gpu.set_huffman_table(na12878)
