@@ -291,3 +291,49 @@ def test_huffman_custom_tables(gpu, oracle, shape):
     finally:
         oracle.set_huffman_table(na12878)
         gpu.set_huffman_table(na12878)
+
+
+@pytest.mark.parametrize("method", IMPLEMENTED)
+def test_bench_scale_chunk_properties(gpu, oracle, method):
+    """the bench's workload at chunk scale (9000 NA12878-like reads, ~1 G samples, generated on the
+    device): decode(encode(x)) == x for every sample, the container is tight (its size is the sum
+    of the reference's per-read sizes for the reads checked), and 24 reads drawn from it -- the
+    longest, the shortest and a random draw -- are byte-identical to the oracle's streams"""
+    import torch
+    from honours_b200 import workload
+    nreads = 9000
+    dev = torch.device("cuda:0")
+    lengths, x0, shift = workload.read_table(nreads, q_fraction=0.25 if method == "ex_zd" else 0.0)
+    off = workload.offsets_of(lengths)
+    ns = int(off[-1])
+    d_off = torch.from_numpy(off.astype(np.int64)).to(dev)
+    d_x0 = torch.from_numpy(x0).to(dev)
+    d_sh = torch.from_numpy(shift).to(dev)
+    d_s = torch.empty(ns + 64, dtype=torch.int16, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    workload.synth_device(d_s.data_ptr(), d_off.data_ptr(), nreads, d_x0.data_ptr(), d_sh.data_ptr(), stream=st)
+    cap = gpu.batch_bound(method, nreads, ns)
+    sb = gpu.batch_scratch_bytes(method, nreads, ns)
+    d_out = torch.empty(cap, dtype=torch.uint8, device=dev)
+    d_oo = torch.empty(nreads + 1, dtype=torch.int64, device=dev)
+    d_scr = torch.empty(sb, dtype=torch.uint8, device=dev)
+    gpu.batch_press(method, d_s.data_ptr(), d_off.data_ptr(), nreads, ns, d_out.data_ptr(), cap,
+                    d_oo.data_ptr(), d_scr.data_ptr(), sb, st)
+    assert gpu.batch_status(d_scr.data_ptr(), st) == 0
+    oo = d_oo.cpu().numpy()
+    assert oo[0] == 0 and np.all(np.diff(oo) > 0) and int(oo[-1]) <= cap
+    rng = np.random.default_rng(2024)
+    pick = set(rng.integers(0, nreads, 20).tolist()) | {int(np.argmax(lengths)), int(np.argmin(lengths)), 0, nreads - 1}
+    for r in sorted(pick):
+        s = d_s[int(off[r]):int(off[r + 1])].cpu().numpy()
+        got = d_out[int(oo[r]):int(oo[r + 1])].cpu().numpy().tobytes()
+        rc, want = oracle.press(method, s)
+        assert rc == 0 and got == want, (method, r, s.size)
+    d_back = torch.full((ns + 64,), -1, dtype=torch.int16, device=dev)
+    gpu.batch_depress(method, d_out.data_ptr(), d_oo.data_ptr(), int(oo[-1]), d_off.data_ptr(), nreads, ns,
+                      d_back.data_ptr(), d_scr.data_ptr(), sb, st)
+    assert gpu.batch_status(d_scr.data_ptr(), st) == 0
+    assert torch.equal(d_back[:ns], d_s[:ns])
+    assert bool((d_back[ns:] == -1).all())      # nothing written past the last sample
+    del d_s, d_out, d_back, d_scr
+    torch.cuda.empty_cache()
