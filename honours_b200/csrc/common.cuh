@@ -224,15 +224,18 @@ __device__ __forceinline__ void block_scan(const uint32_t (&v)[C], uint32_t (&ex
 	if (lane == 31)
 		s_warp[warp] = x;
 	__syncthreads();
-	const uint4 t0 = reinterpret_cast<const uint4 *>(s_warp)[0], t1 = reinterpret_cast<const uint4 *>(s_warp)[1];
-	const uint32_t w[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
-	uint32_t before = 0, all = 0;
+	// the 8 warp totals scanned by shuffles in every warp (a third of the instructions of
+	// adding them up under per-warp predicates)
+	const uint32_t t = s_warp[lane & 7];
+	uint32_t s = t;
 #pragma unroll
-	for (int k = 0; k < 8; k++) {
-		all += w[k];
-		if (k < warp)
-			before += w[k];
+	for (int o = 1; o < 8; o <<= 1) {
+		const uint32_t y = __shfl_up_sync(0xffffffffu, s, o);
+		if ((lane & 7) >= o)
+			s += y;
 	}
+	const uint32_t before = __shfl_sync(0xffffffffu, s - t, warp);
+	const uint32_t all = __shfl_sync(0xffffffffu, s, 7);
 	excl[0] = before + x - v[0];
 	total = all;
 }

@@ -709,7 +709,8 @@ __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant_
 			}
 			carry = (carry + tot) & 0xffffu;
 			e_lo = e_hi;
-			__syncthreads();
+			// (no barrier here: the stage and s_ex are read before the scan's barrier and
+			//  rewritten after it; s_warp is rewritten after the next tile's first barrier)
 		}
 	}
 }

@@ -304,7 +304,9 @@ __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ 
 			va_cur = va_n;
 			ex_cur = ex_n;
 			L_cur = L_n;
-			__syncthreads();	// s_in is rewritten by the next tile
+			// (no barrier here: every read of s_in above precedes the value scan's barrier, every
+			//  read of s_warp / s_warp2 is followed by the next tile's first barrier before the
+			//  array is written again)
 		}
 		if (overrun && tid == 0)
 			atomicOr(&a.hdr->error, ERR_MALFORMED);
