@@ -536,15 +536,20 @@ __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant_
 		const uint2 *ex = a.pool + a.r_pool[r];
 		const uint8_t *pbase = shuff ? a.paybuf + off0 : a.in + pay0;
 
+		// v-indices of the read before tile t (ex_v_before), in 32 bits: 0 for the first tile,
+		// everything for t >= nt, t * XT - m - 1 in between (below n - 1 there)
+		const uint32_t nm1 = (uint32_t) (n - 1);
+		auto vb = [&](uint32_t t) { return t == 0 ? 0u : t >= nt ? nm1 : t * (uint32_t) XT - m - 1u; };
+		// may every 16-byte word the walk can touch be loaded without a look at the limits?
+		const bool safe = pbase - 16 >= lim_lo && pbase + (uint64_t) nm1 + 48 <= lim_hi;
 		// payload bytes of a tile -> registers (word tid, and word 256 in thread 0)
 		uint4 dreg[2];
-		auto issue = [&](uint32_t t, uint32_t e_lo) {
-			const uint32_t j_lo = ex_v_before(t, m, n), j_hi = ex_v_before(t + 1, m, n);
+		auto issue = [&](uint32_t j_lo, uint32_t j_hi, uint32_t e_lo) {
 			const uint8_t *src = pbase + (j_lo - e_lo);
 			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
 			const uint32_t nw = (al + (j_hi - j_lo) + 15) >> 4;	// (a few bytes more than needed when
 			const uint8_t *b16 = src - al;				//  the tile holds exceptions)
-			if (b16 >= lim_lo && b16 + 16ull * nw <= lim_hi) {
+			if (safe || (b16 >= lim_lo && b16 + 16ull * nw <= lim_hi)) {
 				if ((uint32_t) tid < nw)
 					dreg[0] = __ldg(reinterpret_cast<const uint4 *>(b16) + tid);
 				if (tid == 0 && nw > NT)
@@ -564,11 +569,11 @@ __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant_
 			exreg = e0 + tid < nex ? ex[e0 + tid] : make_uint2(0xffffffffu, 0u);
 		};
 		uint32_t e_lo = 0, carry = 0;
-		issue(0, 0);
+		uint32_t j_lo = 0, j_hi = vb(1), j_nx = vb(2);	// v-indices before tiles t, t + 1, t + 2
+		issue(j_lo, j_hi, 0);
 		if (nex)
 			issue_ex(0);
-		for (uint32_t t = 0; t < nt; t++) {
-			const uint32_t j_lo = ex_v_before(t, m, n), j_hi = ex_v_before(t + 1, m, n);
+		for (uint32_t t = 0; t < nt; t++, j_lo = j_hi, j_hi = j_nx, j_nx = vb(t + 2)) {
 			const uint32_t p_lo = j_lo - e_lo;
 			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(pbase + p_lo) & 15);
 			{
@@ -606,7 +611,7 @@ __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant_
 				}
 			}
 			if (t + 1 < nt) {
-				issue(t + 1, e_hi);
+				issue(j_hi, j_nx, e_hi);
 				if (nex)
 					issue_ex(e_hi);
 			}
