@@ -57,7 +57,7 @@ constexpr int EN_THREADS = (EN_W_PROD + 1) * 32;
 constexpr int EN_STAGES = 12;
 constexpr int EN_STAGE_BYTES = (EN_TG + 2) * 16 + 96;	// slots 0 .. TG+1, padded to 128
 constexpr int EN_LINE_BYTES = 2 * 8 * EN_EG + 16;	// per worker staging line (general path)
-constexpr int EN_PD = 4;				// look-back windows in flight (prefix warp)
+constexpr int EN_WS = 4;				// window sums in flight between the window and the prefix warp
 constexpr int EN_WW = 5;				// window words per lane: grid <= 32 * EN_WW + 1
 constexpr int EN_MAX_GRID = 32 * EN_WW + 1;
 constexpr int EN_WIN_WORDS = 32 * EN_WW + 4;	// window + alignment slack
@@ -85,9 +85,8 @@ struct EnSmem {
 	uint32_t blkL[EN_STAGES][EN_NB];	// data bytes of each 1024-sample block (phase A)
 	uint32_t blkF[EN_STAGES][EN_NB];	// 1: the block's data bytes are packed in its stage (phase A)
 	uint32_t ajob, bjob;			// next (tile, block) job of the A / B warps
-	alignas(16) uint64_t win[EN_PD][EN_WIN_WORDS];	// look-back windows (prefix warp)
-	uint64_t win_full[EN_PD], wsum_done[EN_PD], wsum_free[EN_PD];
-	uint2 wsum[EN_PD];				// window sum, sum of its last t words
+	uint64_t wsum_done[EN_WS], wsum_free[EN_WS];
+	uint2 wsum[EN_WS];				// window sum, sum of its last t words
 };
 
 // word holding the sample before each of x's words' low halves
@@ -344,8 +343,7 @@ __global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_con
 			mbar_init(&sm.scan_done[s], 1);
 			mbar_init(&sm.empty[s], EN_NB);
 		}
-		for (int u = 0; u < EN_PD; u++) {
-			mbar_init(&sm.win_full[u], 1);
+		for (int u = 0; u < EN_WS; u++) {
 			mbar_init(&sm.wsum_done[u], 1);
 			mbar_init(&sm.wsum_free[u], 1);
 		}
@@ -448,59 +446,49 @@ __global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_con
 
 	if (warp == EN_W_SCAN + 2) {
 		// ---- window warp: for every tile of the CTA the sum of the G - 1 aggregates between
-		// it and the CTA's previous tile (other CTAs' tiles only), requested EN_PD tiles ahead
-		// by a bulk copy into shared memory (in registers the pending loads would sit on the
-		// scoreboards every LDS / SHFL of the warp waits on).
+		// it and the CTA's previous tile (other CTAs' tiles only).  Plain relaxed loads, five
+		// words per lane, requested the moment the CTA's own count of that tile is out: the
+		// other CTAs run the same round at about the same time, so a window fetched earlier
+		// (a bulk copy several tiles ahead was tried) is stale and has to be fetched again --
+		// one more L2 round trip on the chain every emit of the CTA waits for.
 		RT_DECL;
-		// window of the CTA's i-th tile: words [lo, g) of the status array; the copy covers
-		// the 16-byte aligned superset starting at lo & ~1
-		auto issue = [&](uint32_t i) {
+		uint64_t w[EN_WW];
+		auto request = [&](uint32_t i) {	// window of the CTA's i-th tile: words [g - wl, g)
 			const uint64_t g = blockIdx.x + (uint64_t) i * G;
-			const uint64_t lo = i == 0 ? 0 : g - G + 1;
-			const uint64_t la = lo & ~1ull;
-			const uint32_t bytes = (uint32_t) ((g - la + 1) & ~1ull) * 8;
-			const uint32_t u = i % EN_PD;
-			if (lane == 0) {
-				if (bytes) {
-					mbar_arrive_expect_tx(&sm.win_full[u], bytes);
-					tma_load_1d(sm.win[u], a.status + la, bytes, &sm.win_full[u]);
-				} else {
-					mbar_arrive(&sm.win_full[u]);
-				}
+			const uint32_t wl = g_window(i, G);
+			const uint64_t *p = a.status + (g - wl);
+#pragma unroll
+			for (int q = 0; q < EN_WW; q++) {
+				const uint32_t j = 32 * q + lane;
+				w[q] = j < wl ? ld_relaxed(p + j) : LB_AGG;
 			}
 		};
-		for (uint32_t i = 0; i < EN_PD && i < nt; i++)
-			issue(i);
-		uint32_t wphase = 0;	// bit u: parity of the next completion of win_full[u]
+		RT_BEGIN();
+		mbar_wait(&sm.pub_done[0], 0);
+		RT_END(0);
+		request(0);
 		for (uint32_t i = 0; i < nt; i++) {
-			const uint32_t s = i % EN_STAGES, u = i % EN_PD;
-			RT_BEGIN();
-			mbar_wait(&sm.pub_done[s], (i / EN_STAGES) & 1);	// the tile's info is there
-			RT_END(0);
+			const uint32_t s = i % EN_STAGES, v = i % EN_WS;
 			RT_BEGIN();
 			const uint32_t t = sm.info[s].t;
-			const uint32_t wl = g_window(i, G);	// window words: tiles [g - wl, g)
-			const uint32_t skew = (uint32_t) ((blockIdx.x + (uint64_t) i * G - wl) & 1);	// lo - (lo & ~1)
+			const uint32_t wl = g_window(i, G);
 			uint32_t W, Wt;
 			for (;;) {
-				mbar_wait(&sm.win_full[u], (wphase >> u) & 1);
-				wphase ^= 1u << u;
 				uint32_t sum = 0, sumt = 0;
 				bool ok = true;
 #pragma unroll
 				for (int q = 0; q < EN_WW; q++) {
 					const uint32_t j = 32 * q + lane;	// word j of the window
-					const uint64_t w = j < wl ? sm.win[u][j + skew] : LB_AGG;
-					ok = ok && (w >> 62) != 0;
-					sum += (uint32_t) w;			// a tile holds < 2^15 bytes
-					sumt += j + t >= wl ? (uint32_t) w : 0u;
+					ok = ok && (w[q] >> 62) != 0;
+					sum += (uint32_t) w[q];			// a tile holds < 2^15 bytes
+					sumt += j + t >= wl ? (uint32_t) w[q] : 0u;
 				}
 				if (__all_sync(0xffffffffu, ok)) {
 					W = __reduce_add_sync(0xffffffffu, sum);
 					Wt = __reduce_add_sync(0xffffffffu, sumt);
 					break;
 				}
-				issue(i);	// some counts were not out yet: fetch the window again
+				request(i);	// some counts were not out yet: fetch the window again
 #ifdef PG_ROLE_TIMING
 				if (lane == 0)
 					atomicAdd((unsigned long long *) &a.hdr->aux[24], 1ull);
@@ -508,13 +496,17 @@ __global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_con
 			}
 			RT_END(1);
 			RT_BEGIN();
-			if (i + EN_PD < nt)	// (the __all_sync above: every lane has read win[u])
-				issue(i + EN_PD);
-			if (i >= EN_PD)		// the prefix warp has taken the sums of tile i - EN_PD
-				mbar_wait(&sm.wsum_free[u], ((i / EN_PD) & 1) ^ 1);
+			if (i + 1 < nt) {	// the next tile's count is out (its info with it): request its window
+				mbar_wait(&sm.pub_done[(i + 1) % EN_STAGES], ((i + 1) / EN_STAGES) & 1);
+				request(i + 1);
+			}
+			RT_END(0);
+			RT_BEGIN();
+			if (i >= EN_WS)		// the prefix warp has taken the sums of tile i - EN_WS
+				mbar_wait(&sm.wsum_free[v], ((i / EN_WS) & 1) ^ 1);
 			if (lane == 0) {
-				sm.wsum[u] = make_uint2(W, Wt);
-				mbar_arrive(&sm.wsum_done[u]);
+				sm.wsum[v] = make_uint2(W, Wt);
+				mbar_arrive(&sm.wsum_done[v]);
 			}
 			__syncwarp();
 			RT_END(2);
@@ -532,7 +524,7 @@ __global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_con
 		uint32_t r_prev = 0xffffffffu;
 		uint64_t base_prev = 0;
 		for (uint32_t i = 0; i < nt; i++) {
-			const uint32_t s = i % EN_STAGES, u = i % EN_PD;
+			const uint32_t s = i % EN_STAGES, u = i % EN_WS;
 			RT_BEGIN();
 			mbar_wait(&sm.pub_done[s], (i / EN_STAGES) & 1);
 			RT_END(0);
@@ -550,7 +542,7 @@ __global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_con
 				base = base_prev;
 			else if (far && lane == 0)
 				base = ld_relaxed(a.out_offsets + r);
-			mbar_wait(&sm.wsum_done[u], (i / EN_PD) & 1);
+			mbar_wait(&sm.wsum_done[u], (i / EN_WS) & 1);
 			const uint2 ws = sm.wsum[u];
 			__syncwarp();
 			if (lane == 0)
