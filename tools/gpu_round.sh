@@ -26,3 +26,9 @@ ncu --set full --clock-control none --import-source on -k regex:svb_ -s 2 -c 2 \
     -f -o $O/prof_svb16_zd_$TAG $SHORT > $O/ncu_full_$TAG.log 2>&1
 echo "ncu full exit $?"
 ls $O | grep $TAG
+# the exception / Huffman methods: launch lists and one full capture per kernel (20 k reads)
+bash tools/ncu_list.sh $TAG 20000 vbe21_zd shuff_vbe21_zd > $O/ncu_list_ex_$TAG.log 2>&1
+bash tools/ncu_full.sh $TAG 20000 vbe21_zd ex_count ex_emit_bytes ex_decode > $O/ncu_full_vbe21_$TAG.log 2>&1
+bash tools/ncu_full.sh $TAG 20000 shuff_vbe21_zd ex_count ex_emit_kernel huff_decode ex_decode > $O/ncu_full_shuff_$TAG.log 2>&1
+bash tools/sweep.sh $TAG 20000 > $O/sweep_$TAG.log 2>&1
+ls $O | grep -c $TAG
