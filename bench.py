@@ -75,7 +75,7 @@ def cpu_leg(method: str, nreads: int, p_ex: float, seconds: float, steps: int | 
     if kind == "oracle" and not cpu_impl.available("oracle"):
         cpu_impl.build(ref=False)
     impl = cpu_impl.load(kind)
-    if method == "shuff_vbe21_zd":
+    if method.startswith("shuff_"):
         impl.set_huffman_table(open(os.path.join(ROOT, "honours_b200", "data", "NA12878_zd.huffman"), "rb").read())
     lengths, x0, shift = workload.read_table(nreads)
     offsets = workload.offsets_of(lengths)
@@ -227,7 +227,7 @@ def run_ours(args):
     method = args.method
     if method not in press.implemented_methods():
         raise SystemExit(f"method {method} is not implemented in this build of libpress_gpu (no CPU fallback)")
-    if method == "shuff_vbe21_zd":
+    if method.startswith("shuff_"):
         press.set_huffman_table()
     p_ex = workload.P_EX if args.p_ex is None else args.p_ex
     K, W = args.steps, args.warmup

@@ -39,6 +39,12 @@ constexpr int X_STAGE = 22 * XT / 8 + 64;	// payload stage: 4096 x 22-bit codes,
 
 enum : uint32_t { ERR_SCRATCH = 8 };	// exception pool too small (press_gpu_set_exception_capacity)
 
+// payload = static Huffman bitstream (else: the low bytes themselves)
+__host__ __device__ __forceinline__ bool ex_is_huff(int method)
+{
+	return method == PRESS_GPU_SHUFF_VBE21_ZD || method == PRESS_GPU_SHUFF_VBSSE21_ZD;
+}
+
 struct ExArgs {
 	int method;
 	const uint4 *samples;		// encode in
@@ -598,7 +604,13 @@ __global__ void __launch_bounds__(NT) ex_size_kernel(const __grid_constant__ ExA
 		const uint32_t nex = a.r_nex[r];
 		const ExList L = {a.pool2 + a.r_pool[r]};
 		hdr = ex_fixed_bytes(a.method) + ex_lists<false>(a.method, L, nex, nullptr, lane);
-		if (a.method == PRESS_GPU_SHUFF_VBE21_ZD) {
+		if (a.method == PRESS_GPU_SHUFF_VBSSE21_ZD && hdr - 2 > 0xffffu) {
+			// press.c:4753: the header length lives in a uint16_t there; longer ones wrap and
+			// the reference cannot read its own stream back.  Reported like the ex-zd cap.
+			if (lane == 0)
+				atomicOr(&a.hdr->error, ERR_EXZD_CAP);
+			hdr = X_FAIL;
+		} else if (ex_is_huff(a.method)) {
 			hdr += 4;	// [count u32 BE], huffman.c:1199-1203
 			size = hdr + (a.r_bits[r] + 7) / 8;
 		} else {
@@ -647,7 +659,7 @@ __global__ void __launch_bounds__(NT) ex_header_kernel(const __grid_constant__ E
 	const ExList L = {a.pool2 + a.r_pool[r]};
 	const uint32_t fx = ex_fixed_bytes(a.method);
 	const uint32_t ll = ex_lists<true>(a.method, L, nex, dst + fx, lane);
-	if (a.method == PRESS_GPU_SHUFF_VBE21_ZD && lane < 4) {
+	if (ex_is_huff(a.method) && lane < 4) {
 		const uint32_t cnt = (uint32_t) (n - 1 - nex);
 		dst[fx + ll + lane] = (uint8_t) (cnt >> (8 * (3 - lane)));	// htonl, huffman.c:1199
 	}

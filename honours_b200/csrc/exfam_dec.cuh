@@ -232,7 +232,7 @@ __global__ void __launch_bounds__(NT) ex_parse_kernel(const __grid_constant__ Ex
 		bad = bad || __any_sync(0xffffffffu, order_bad);
 	}
 	if (!bad) {
-		if (a.method == PRESS_GPU_SHUFF_VBE21_ZD) {
+		if (ex_is_huff(a.method)) {
 			// [count u32 BE] + bitstream; huffman.c:696-711 memread fails when no byte follows
 			bad = off + 4 >= s1;
 			if (!bad) {
@@ -512,7 +512,7 @@ __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant_
 	__shared__ uint32_t s_read, s_e;
 	__shared__ uint2 s_ex[NT];	// the next 256 exceptions of the read (position, value)
 	const int tid = threadIdx.x;
-	const bool shuff = a.method == PRESS_GPU_SHUFF_VBE21_ZD;
+	const bool shuff = ex_is_huff(a.method);
 	const uint8_t *lim_lo = shuff ? a.paybuf : a.in;
 	const uint8_t *lim_hi = shuff ? a.paybuf + ((a.offsets[a.nreads] + 15) & ~15ull) : a.in + a.in_bytes;
 	uint4 *out4 = reinterpret_cast<uint4 *>(a.samples_out);

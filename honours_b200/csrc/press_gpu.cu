@@ -127,7 +127,7 @@ ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples, dou
 		l.x_r8[0] = o;		o += align_up((nreads + 1) * 8, 256);
 		l.x_r8[1] = o;		o += align_up((nreads + 1) * 8, 256);
 		l.x_paybuf = o;
-		if (method == PRESS_GPU_SHUFF_VBE21_ZD)
+		if (ex_is_huff(method))
 			o += align_up(nsamples + 64, 256);
 		l.x_pool = o;
 		if (pool_frac < 0)
@@ -225,6 +225,8 @@ uint64_t press_gpu_batch_bound(int method, uint64_t nreads, uint64_t nsamples)
 	/* every sample an exception: 6 B (vbe21), <= 1.25 + 2.125 B (vbsse21) per sample */
 	case PRESS_GPU_VBE21_ZD: return 6 * nsamples + 16;
 	case PRESS_GPU_SHUFF_VBE21_ZD: return 6 * nsamples + 4 * nreads + 16;
+	/* lists as vbsse21, 3-byte codes at most for the rest */
+	case PRESS_GPU_SHUFF_VBSSE21_ZD: return 4 * nsamples + 20 * nreads + 16;
 	case PRESS_GPU_VBSSE21_ZD: return 4 * nsamples + 16 * nreads + 16;
 	case PRESS_GPU_EX_ZD: return 2 * nsamples + 1024 * nreads + 16;	/* ex_zd.c:411 cap */
 	default: break;

@@ -23,6 +23,7 @@ METHODS = {
     "vbsse21_zd": 5,
     "ex_zd": 6,
     "shuff_vbe21_zd": 7,
+    "shuff_vbsse21_zd": 8,
 }
 
 # per-read entry points of include/press_gpu.h, by method
@@ -37,6 +38,8 @@ PER_READ = {
               "hasgam_vbsse21_zdq_gpu_depress_16"),
     "shuff_vbe21_zd": ("shuffman_vbe21_zd_gpu_bound_16", "shuffman_vbe21_zd_gpu_press_16",
                        "shuffman_vbe21_zd_gpu_depress_16"),
+    "shuff_vbsse21_zd": ("shuffman_vbsse21_zd_gpu_bound_16", "shuffman_vbsse21_zd_gpu_press_16",
+                         "shuffman_vbsse21_zd_gpu_depress_16"),
 }
 
 
@@ -158,7 +161,7 @@ def press(method: str, sig: np.ndarray) -> tuple[int, bytes]:
         f.restype = None
         f.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]
         f(sig.ctypes.data, n, out.ctypes.data, C.byref(nout))
-    elif method == "shuff_vbe21_zd":
+    elif method in ("shuff_vbe21_zd", "shuff_vbsse21_zd"):
         f.restype = C.c_int
         f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]
         rc = f(None, sig.ctypes.data, n, out.ctypes.data, C.byref(nout))
@@ -190,7 +193,7 @@ def depress(method: str, stream: bytes, n: int) -> tuple[int, np.ndarray]:
         f.restype = None
         f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint32)]
         f(buf.ctypes.data, len(stream), out.ctypes.data, C.byref(nout))
-    elif method == "shuff_vbe21_zd":
+    elif method in ("shuff_vbe21_zd", "shuff_vbsse21_zd"):
         nout = C.c_uint32(n)
         f.restype = C.c_int
         f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint32)]

@@ -36,7 +36,8 @@ enum press_gpu_method {
 	PRESS_GPU_VBSSE21_ZD = 5,	/* vbsse21_zd_*_16         press.c:3543-3580 */
 	PRESS_GPU_EX_ZD = 6,		/* hasgam_vbsse21_zdq_*_16 press.h:958-964, ex_zd.c */
 	PRESS_GPU_SHUFF_VBE21_ZD = 7,	/* shuffman_vbe21_zd_*_16  press.h:632-638  */
-	PRESS_GPU_NMETHODS = 8
+	PRESS_GPU_SHUFF_VBSSE21_ZD = 8,	/* shuffman_vbsse21_zd_*_16 press.h:658-663, press.c:4742-4845 */
+	PRESS_GPU_NMETHODS = 9
 };
 
 /* ---- context ------------------------------------------------------------- */
@@ -106,6 +107,16 @@ int shuffman_vbe21_zd_gpu_press_16(const void *table, const int16_t *in, uint32_
 				   uint8_t *out, uint64_t *nout);
 int shuffman_vbe21_zd_gpu_depress_16(const void *table, uint8_t *in, uint64_t nin,
 				     int16_t *out, uint32_t *nout);
+
+/* static Huffman over the vbsse21 header: press.h:658-663 (press.c:4737-4845).  Same calling
+ * convention as above.  The reference keeps the header length in a uint16_t (press.c:4753)
+ * and cannot read back a stream whose coded exception lists pass 65535 bytes; press fails
+ * (1) for exactly those reads instead of writing such a stream. */
+uint64_t shuffman_vbsse21_zd_gpu_bound_16(uint32_t nin);
+int shuffman_vbsse21_zd_gpu_press_16(const void *table, const int16_t *in, uint32_t nin,
+				     uint8_t *out, uint64_t *nout);
+int shuffman_vbsse21_zd_gpu_depress_16(const void *table, uint8_t *in, uint64_t nin,
+				       int16_t *out, uint32_t *nout);
 
 /* ---- 2. batch API (device pointers) --------------------------------------
  * Layout: d_samples = all reads back to back (int16, base 16-byte aligned),

@@ -29,6 +29,7 @@ METHODS = {
     "vbsse21_zd": 5,      # press.h vbsse21_zd_*_16
     "ex_zd": 6,           # press.h hasgam_vbsse21_zdq_*_16
     "shuff_vbe21_zd": 7,  # press.h shuffman_vbe21_zd_*_16
+    "shuff_vbsse21_zd": 8,  # press.h shuffman_vbsse21_zd_*_16
 }
 
 _u8p = C.POINTER(C.c_uint8)

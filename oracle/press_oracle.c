@@ -703,6 +703,72 @@ static int shuff_vbe21_zd_depress(const uint8_t *in, uint64_t nbytes, uint64_t n
 	return ret;
 }
 
+/* ---------- a17: shuffman_vbsse21_zd (press.c:4737-4845) -------------------- */
+
+/* length of [nex][coded lists] at the head of a vbsse21 body (press.c:4766-4775, 4808-4817);
+ * the reference keeps it in a uint16_t: once the coded lists pass 65535 bytes its press copies
+ * a wrapped length and its depress looks for the second list length in the wrong place.  Those
+ * reads are reported as failures here (return 1) instead of restating the wrap. */
+static int vbsse21_exlen(const uint8_t *body, uint64_t nbody, uint64_t *exlen)
+{
+	if (nbody < 4)
+		return 1;
+	uint32_t nex = get_u32(body);
+	uint64_t e = 4;
+	if (nex > 1) {
+		if (e + 4 > nbody)
+			return 1;
+		e += 4 + (uint64_t) get_u32(body + e);
+		if (e + 4 > nbody)
+			return 1;
+		e += 4 + (uint64_t) get_u32(body + e);
+	} else if (nex == 1) {
+		e += 6;
+	}
+	if (e > nbody || e > 0xffff)
+		return 1;
+	*exlen = e;
+	return 0;
+}
+
+static int shuff_vbsse21_zd_press(const int16_t *in, uint32_t n, uint8_t *out, uint64_t *nout)
+{
+	if (!H.set || n == 0)
+		return 1;
+	uint64_t cap = 64 + 8 * (uint64_t) n;
+	uint8_t *vb = malloc(cap);
+	uint64_t nvb = 0, exlen = 0;
+	if (!vb || vbsse21_zd_press(in, n, vb, &nvb) || vbsse21_exlen(vb + 2, nvb - 2, &exlen)) {
+		free(vb);
+		return 1;
+	}
+	uint64_t hdr = 2 + exlen;	/* zd0, then the exception lists verbatim (press.c:4757, 4776) */
+	memcpy(out, vb, hdr);
+	*nout = hdr + huff_encode(vb + hdr, (uint32_t) (nvb - hdr), out + hdr);
+	free(vb);
+	return 0;
+}
+
+static int shuff_vbsse21_zd_depress(const uint8_t *in, uint64_t nbytes, uint64_t n,
+				    int16_t *out, uint64_t *nout)
+{
+	uint64_t exlen = 0;
+	if (!H.set || nbytes < 6 || vbsse21_exlen(in + 2, nbytes - 2, &exlen))
+		return 1;
+	uint64_t hdr = 2 + exlen;
+	uint32_t want = nbytes - hdr > 4 ? get_u32_be(in + hdr) : 0;
+	uint8_t *vb = malloc(hdr + (uint64_t) want + 16);
+	uint32_t m = 0;
+	if (!vb)
+		return 1;
+	memcpy(vb, in, hdr);
+	int ret = huff_decode(in + hdr, nbytes - hdr, vb + hdr, &m);	/* press.c:4826-4829 */
+	if (ret == 0)
+		ret = vbsse21_zd_depress(vb, hdr + m, n, out, nout) ? 1 : 0;
+	free(vb);
+	return ret;
+}
+
 /* ---------- uniform adapter ------------------------------------------------ */
 
 uint64_t oracle_bound(int method, uint64_t n)
@@ -715,6 +781,7 @@ uint64_t oracle_bound(int method, uint64_t n)
 	case ORC_VBE21_ZD:						/* press.c:3411-3414 */
 	case ORC_VBSSE21_ZD:						/* press.c:3543-3546 */
 	case ORC_SHUFF_VBE21_ZD:					/* press.c:4409-4412 -> 3965 */
+	case ORC_SHUFF_VBSSE21_ZD:					/* press.c:4737-4740 -> 4293 */
 		return 2 + vb1e2_bound((uint32_t) (n - 1));
 	case ORC_EX_ZD:							/* press.c:8461-8464 */
 		return svb32_bound(2 + vb1e2_bound((uint32_t) (n - 1)));
@@ -739,6 +806,7 @@ int oracle_press(int method, const int16_t *in, uint64_t n, uint8_t *out, uint64
 	case ORC_VBSSE21_ZD: return vbsse21_zd_press(in, (uint32_t) n, out, nout);
 	case ORC_EX_ZD: return ex_zd_press(in, (uint32_t) n, out, nout);
 	case ORC_SHUFF_VBE21_ZD: return shuff_vbe21_zd_press(in, (uint32_t) n, out, nout);
+	case ORC_SHUFF_VBSSE21_ZD: return shuff_vbsse21_zd_press(in, (uint32_t) n, out, nout);
 	}
 	return -1;
 }
@@ -757,6 +825,7 @@ int oracle_depress(int method, const uint8_t *in, uint64_t nbytes, uint64_t n,
 	case ORC_VBSSE21_ZD: return vbsse21_zd_depress(in, nbytes, n, out, nout);
 	case ORC_EX_ZD: return ex_zd_depress(in, nbytes, n, out, nout);
 	case ORC_SHUFF_VBE21_ZD: return shuff_vbe21_zd_depress(in, nbytes, n, out, nout);
+	case ORC_SHUFF_VBSSE21_ZD: return shuff_vbsse21_zd_depress(in, nbytes, n, out, nout);
 	}
 	return -1;
 }

@@ -32,6 +32,7 @@ enum {
 	ORC_VBSSE21_ZD = 5,	/* press.h vbsse21_zd_*_16        (a9)    */
 	ORC_EX_ZD = 6,		/* press.h hasgam_vbsse21_zdq_*_16 (a10-a12) */
 	ORC_SHUFF_VBE21_ZD = 7,	/* press.h shuffman_vbe21_zd_*_16 (a13-a16) */
+	ORC_SHUFF_VBSSE21_ZD = 8,	/* press.h shuffman_vbsse21_zd_*_16 (a17) */
 	ORC_NMETHODS = 8
 };
 

@@ -12,7 +12,8 @@ pytestmark = pytest.mark.gpu
 
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 IMPLEMENTED = ["svb16_zd", "svb_zd", "vbz_svb16_zd", "vbz_svb_zd",
-               "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd"]
+               "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd", "shuff_vbsse21_zd"]
+HUFF = ("shuff_vbe21_zd", "shuff_vbsse21_zd")
 EXFAM = IMPLEMENTED[4:]
 
 
@@ -94,8 +95,10 @@ def test_batch_host_matches_oracle(gpu, oracle, method):
     """tight container: stream r at out_offsets[r], all byte-identical to the oracle;
     reads are back to back so most start at a misaligned address."""
     rng = np.random.default_rng(7)
-    kinds = ("walk", "spiky", "q") if method in ("ex_zd", "shuff_vbe21_zd") else ("walk", "spiky", "q", "noise")
-    samples, offsets, reads = make_batch(rng, 300, 2 if method in EXFAM else 1, 30000, kinds=kinds)
+    kinds = ("walk", "spiky", "q") if method in ("ex_zd",) + HUFF else ("walk", "spiky", "q", "noise")
+    # (shuffman-vbsse21: coded exception lists must stay below 64 KB, press.c:4753)
+    hi = 12000 if method == "shuff_vbsse21_zd" else 30000
+    samples, offsets, reads = make_batch(rng, 300, 2 if method in EXFAM else 1, hi, kinds=kinds)
     rc, cont, oo = gpu.batch_press_host(method, samples, offsets)
     assert rc == 0
     expect = [oracle.press(method, s)[1] for s in reads]
@@ -109,7 +112,7 @@ def test_batch_host_matches_oracle(gpu, oracle, method):
 @pytest.mark.parametrize("method", IMPLEMENTED)
 def test_batch_with_empty_and_tiny_reads(gpu, oracle, method):
     rng = np.random.default_rng(9)
-    lens = [0, 2 if method == "shuff_vbe21_zd" else 1, 0, 5, 4096, 0, 4097, 8, 0]
+    lens = [0, 2 if method in HUFF else 1, 0, 5, 4096, 0, 4097, 8, 0]
     reads = [rand_read(rng, "spiky", n) for n in lens]
     samples = np.concatenate(reads) if reads else np.zeros(0, np.int16)
     offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
@@ -193,13 +196,32 @@ def test_ex_zd_scratch_cap_failure_mirrors_reference(gpu, oracle):
     assert rc == 1 and cont.tobytes() == e + e and int(oo[1]) == int(oo[2])
 
 
+def test_shuffman_vbsse21_header_limit_mirrors_reference(gpu, oracle):
+    """press.c:4753 keeps the header length in a uint16_t: once the coded exception lists pass
+    65535 bytes the reference writes a stream it cannot read back; both sides refuse the read"""
+    rng = np.random.default_rng(14)
+    s = rand_read(rng, "noise", 40000)          # ~40000 exceptions, > 130 KB of coded lists
+    assert oracle.press("shuff_vbsse21_zd", s)[0] != 0
+    assert gpu.press("shuff_vbsse21_zd", s)[0] != 0
+    small = rand_read(rng, "noise", 15000)      # ~50 KB of lists: still representable
+    ro, so = oracle.press("shuff_vbsse21_zd", small)
+    rc, st = gpu.press("shuff_vbsse21_zd", small)
+    assert ro == rc == 0 and st == so
+    ok = rand_read(rng, "walk", 5000)
+    samples = np.concatenate([ok, s, ok])
+    offsets = np.array([0, 5000, 45000, 50000], dtype=np.uint64)
+    rc, cont, oo = gpu.batch_press_host("shuff_vbsse21_zd", samples, offsets)
+    e = oracle.press("shuff_vbsse21_zd", ok)[1]
+    assert rc == 1 and cont.tobytes() == e + e and int(oo[1]) == int(oo[2])
+
+
 @pytest.mark.parametrize("method", EXFAM)
 @pytest.mark.parametrize("p_ex", [0.0, 1e-3, 0.1, 0.5])
 def test_exception_rate_sweep(gpu, oracle, method, p_ex):
     """config 3: exception-rate sweep on synthetic NA12878-like reads (host generator)"""
     from honours_b200 import workload
     lengths, x0, shift = workload.read_table(40, q_fraction=0.25)
-    lengths = np.minimum(lengths, 30000)
+    lengths = np.minimum(lengths, 12000 if method == "shuff_vbsse21_zd" else 30000)    # (press.c:4753)
     offsets = workload.offsets_of(lengths)
     samples = workload.synth_host(offsets, x0, shift, p_ex=p_ex)
     reads = [samples[int(offsets[r]):int(offsets[r + 1])] for r in range(len(lengths))]

@@ -74,11 +74,28 @@ def test_oracle_matches_reference_small_streams(oracle, method):
         if rc != 0:
             continue
         assert st == ref_st, (name, method)
-        if method == "shuff_vbe21_zd" and len(st) - (6 + 6 * int.from_bytes(st[2:6], "little")) <= 4:
+        if method in HUFF and len(st) - _huff_header_len(method, st) <= 4:
             assert oracle.depress(method, st, s.size)[0] != 0   # huffman.c:706 memread quirk
             continue
         rc, back = oracle.depress(method, st, s.size)
         assert rc == 0 and np.array_equal(back, s), (name, method)
+
+
+HUFF = ("shuff_vbe21_zd", "shuff_vbsse21_zd")
+
+
+def _huff_header_len(method, st):
+    """bytes before [count u32 BE]: zd0, nex and the exception lists (press.c:4437, 4766-4775)"""
+    nex = int.from_bytes(st[2:6], "little")
+    if method == "shuff_vbe21_zd":
+        return 6 + 6 * nex
+    if nex == 1:
+        return 12
+    if nex == 0:
+        return 6
+    lp = int.from_bytes(st[6:10], "little")
+    lv = int.from_bytes(st[10 + lp:14 + lp], "little")
+    return 14 + lp + lv
 
 
 def _random_read(rng, kind, n):
@@ -107,15 +124,14 @@ def test_oracle_matches_compiled_reference_random(oracle, ref, method):
         if rc_r != 0:
             continue
         assert st_o == st_r, (method, kind, n)
-        nsym = None
-        if method == "shuff_vbe21_zd":
-            nsym = len(st_o) - (6 + 6 * int.from_bytes(st_o[2:6], "little"))
-        if nsym is not None and nsym <= 4:
+        if method in HUFF and len(st_o) - _huff_header_len(method, st_o) <= 4:
             continue
         rc2, b = oracle.depress(method, st_r, n)
         assert rc2 == 0 and np.array_equal(b, s), (method, kind, n)
-        if method == "shuff_vbe21_zd" and 4 + 6 * int.from_bytes(st_o[2:6], "little") > 2 * n:
-            continue    # press.c:4472 sizes its scratch 2n bytes: the reference overflows it
+        if method in HUFF:  # press.c:4472 / 4821 size the scratch 2n bytes: the reference overflows it
+            nex = int.from_bytes(st_o[2:6], "little")
+            if _huff_header_len(method, st_o) - 2 + (n - 1 - nex) > 2 * n:
+                continue
         rc, a = ref.depress(method, st_o, n)
         assert rc == 0 and np.array_equal(a, s), (method, kind, n)
 

@@ -14,7 +14,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 G = os.path.join(ROOT, "gpurun_out")
 P = os.path.join(ROOT, "profiles")
 tag = sys.argv[1]
-METHODS = ["svb16_zd", "svb_zd", "vbz_svb16_zd", "vbz_svb_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd"]
+METHODS = ["svb16_zd", "svb_zd", "vbz_svb16_zd", "vbz_svb_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd",
+           "shuff_vbsse21_zd"]
 
 
 def last_json(path):
