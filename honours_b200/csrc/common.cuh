@@ -57,6 +57,15 @@ __device__ __forceinline__ void st_relaxed(uint64_t *p, uint64_t v)
 	asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// 16-byte asynchronous copy global -> shared (L2 only), and its group fences
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src)
+{
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t) __cvta_generic_to_shared(smem_dst)), "l"(gmem_src)
+		     : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 __device__ __forceinline__ uint64_t warp_sum64(uint64_t v)
 {
 #pragma unroll

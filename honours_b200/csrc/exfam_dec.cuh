@@ -507,7 +507,9 @@ __global__ void __launch_bounds__(NT, 6) huff_decode_kernel(const __grid_constan
 
 __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant__ ExDecArgs a)
 {
-	__shared__ __align__(16) uint8_t s_stage[XT + 64];
+	// the tile's payload bytes, double buffered: tile t + 1 arrives by cp.async (no registers
+	// held, no stage stores) while tile t is decoded
+	__shared__ __align__(16) uint8_t s_stage2[2][XT + 64];
 	__shared__ __align__(16) uint32_t s_warp[NW];
 	__shared__ uint32_t s_read, s_e;
 	__shared__ uint2 s_ex[NT];	// the next 256 exceptions of the read (position, value)
@@ -542,24 +544,25 @@ __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant_
 		auto vb = [&](uint32_t t) { return t == 0 ? 0u : t >= nt ? nm1 : t * (uint32_t) XT - m - 1u; };
 		// may every 16-byte word the walk can touch be loaded without a look at the limits?
 		const bool safe = pbase - 16 >= lim_lo && pbase + (uint64_t) nm1 + 48 <= lim_hi;
-		// payload bytes of a tile -> registers (word tid, and word 256 in thread 0)
-		uint4 dreg[2];
-		auto issue = [&](uint32_t j_lo, uint32_t j_hi, uint32_t e_lo) {
+		// payload bytes of a tile -> stage `buf` (16-byte word tid, and word 256 by thread 0)
+		auto issue = [&](uint32_t buf, uint32_t j_lo, uint32_t j_hi, uint32_t e_lo) {
 			const uint8_t *src = pbase + (j_lo - e_lo);
 			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
 			const uint32_t nw = (al + (j_hi - j_lo) + 15) >> 4;	// (a few bytes more than needed when
 			const uint8_t *b16 = src - al;				//  the tile holds exceptions)
+			uint4 *dst = reinterpret_cast<uint4 *>(s_stage2[buf]);
 			if (safe || (b16 >= lim_lo && b16 + 16ull * nw <= lim_hi)) {
 				if ((uint32_t) tid < nw)
-					dreg[0] = __ldg(reinterpret_cast<const uint4 *>(b16) + tid);
+					cp_async16(dst + tid, reinterpret_cast<const uint4 *>(b16) + tid);
 				if (tid == 0 && nw > NT)
-					dreg[1] = __ldg(reinterpret_cast<const uint4 *>(b16) + NT);
+					cp_async16(dst + NT, reinterpret_cast<const uint4 *>(b16) + NT);
 			} else {
 				if ((uint32_t) tid < nw)
-					dreg[0] = load_word_guarded(b16, tid, lim_lo, lim_hi);
+					dst[tid] = load_word_guarded(b16, tid, lim_lo, lim_hi);
 				if (tid == 0 && nw > NT)
-					dreg[1] = load_word_guarded(b16, NT, lim_lo, lim_hi);
+					dst[NT] = load_word_guarded(b16, NT, lim_lo, lim_hi);
 			}
+			cp_async_commit();
 		};
 		const uint32_t t_hi = (uint32_t) ((m + n) / XT);	// tiles [1, t_hi) lie inside the read
 		// the read's next 256 exceptions travel with the payload: requested one tile ahead,
@@ -570,19 +573,14 @@ __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant_
 		};
 		uint32_t e_lo = 0, carry = 0;
 		uint32_t j_lo = 0, j_hi = vb(1), j_nx = vb(2);	// v-indices before tiles t, t + 1, t + 2
-		issue(j_lo, j_hi, 0);
+		issue(0, j_lo, j_hi, 0);
 		if (nex)
 			issue_ex(0);
 		for (uint32_t t = 0; t < nt; t++, j_lo = j_hi, j_hi = j_nx, j_nx = vb(t + 2)) {
 			const uint32_t p_lo = j_lo - e_lo;
 			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(pbase + p_lo) & 15);
-			{
-				const uint32_t nw = (al + (j_hi - j_lo) + 15) >> 4;
-				if ((uint32_t) tid < nw)
-					reinterpret_cast<uint4 *>(s_stage)[tid] = dreg[0];
-				if (tid == 0 && nw > NT)
-					reinterpret_cast<uint4 *>(s_stage)[NT] = dreg[1];
-			}
+			const uint8_t *s_stage = s_stage2[t & 1];	// complete once the barrier below has passed
+			cp_async_wait_all();
 			uint32_t e_hi = 0;
 			const uint2 *xs = ex;	// where exceptions [e_lo, e_hi) are read from
 			if (!nex) {
@@ -611,7 +609,7 @@ __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant_
 				}
 			}
 			if (t + 1 < nt) {
-				issue(j_hi, j_nx, e_hi);
+				issue((t + 1) & 1, j_hi, j_nx, e_hi);
 				if (nex)
 					issue_ex(e_hi);
 			}

@@ -96,9 +96,11 @@ __device__ __forceinline__ uint32_t dec_keys_flags(const KeyRaw &k)
 }
 
 template <int KEYBITS, bool FRAME>
-__global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ SvbDec2Args a)
+__global__ void __launch_bounds__(NT, 5) svb_dec_kernel(const __grid_constant__ SvbDec2Args a)
 {
-	__shared__ __align__(16) uint8_t s_in[2 * DT + 64];
+	// the tile's data bytes, double buffered: tile t + 1 arrives by cp.async (no registers held,
+	// no stage stores) while tile t is decoded
+	__shared__ __align__(16) uint8_t s_in2[2][2 * DT + 64];
 	__shared__ __align__(16) uint32_t s_warp[NW];	// byte-count scans
 	__shared__ __align__(16) uint32_t s_warp2[NW];	// value scans
 	__shared__ uint32_t s_read;
@@ -151,28 +153,29 @@ __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ 
 			const int hi = left >= 16 ? 16 : (left > 0 ? (int) left : 0);
 			return hi > lo ? (0xffffu >> (16 - hi)) & (0xffffu << lo) & 0xffffu : 0u;
 		};
-		// data bytes of a tile -> registers: word u, u + 256, (u + 512)
-		uint4 dreg[3];
-		auto issue_data = [&](uint64_t D, uint32_t L) {
+		// data bytes of a tile -> stage `buf`: 16-byte words u, u + 256, (u + 512)
+		auto issue_data = [&](uint32_t buf, uint64_t D, uint32_t L) {
 			const uint8_t *src = data + D;
 			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
 			const uint8_t *b16 = src - al;
 			const uint32_t nw = (al + L + 15) >> 4;
+			uint4 *dst = reinterpret_cast<uint4 *>(s_in2[buf]);
 			if (b16 + 16ull * nw <= limit) {	// (b16 >= a.in: the container is 16-byte aligned)
 #pragma unroll
 				for (int j = 0; j < 3; j++) {
 					const uint32_t w = tid + j * NT;
 					if (w < nw)
-						dreg[j] = __ldg(reinterpret_cast<const uint4 *>(b16) + w);
+						cp_async16(dst + w, reinterpret_cast<const uint4 *>(b16) + w);
 				}
 			} else {
 #pragma unroll
 				for (int j = 0; j < 3; j++) {
 					const uint32_t w = tid + j * NT;
 					if (w < nw)
-						dreg[j] = load_word_guarded(b16, w, a.in, limit);
+						dst[w] = load_word_guarded(b16, w, a.in, limit);
 				}
 			}
+			cp_async_commit();
 		};
 
 		const bool keys_safe = keys + nkeys + 8 <= limit;
@@ -197,21 +200,15 @@ __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ 
 		uint32_t carry = 0;
 		bool overrun = L_cur > ndata;
 		if (!overrun)
-			issue_data(0, L_cur);
+			issue_data(0, 0, L_cur);
 		__syncthreads();	// s_warp is reused by the first scan-ahead
 
 		for (uint32_t t = 0; t < ntiles && !overrun; t++) {
-			// ---- data of tile t: registers -> stage (same 16-byte phase as in global memory)
+			// ---- data of tile t: in stage t & 1 once this thread's copies have landed and the
+			// barrier below has passed (same 16-byte phase as in global memory)
 			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(data + D) & 15);
-			{
-				const uint32_t nw = (al + L_cur + 15) >> 4;
-#pragma unroll
-				for (int j = 0; j < 3; j++) {
-					const uint32_t w = tid + j * NT;
-					if (w < nw)
-						reinterpret_cast<uint4 *>(s_in)[w] = dreg[j];
-				}
-			}
+			const uint8_t *s_in = s_in2[t & 1];
+			cp_async_wait_all();
 			// ---- scan ahead: tile t + 1's byte counts, then request its data and tile t + 2's keys
 			uint32_t fl_n = 0, va_n = 0, ex_n = 0, L_n = 0;
 			if (t + 1 < ntiles) {
@@ -229,7 +226,7 @@ __global__ void __launch_bounds__(NT, 4) svb_dec_kernel(const __grid_constant__ 
 				if (D + L_cur + L_n > ndata)
 					overrun = true;
 				else
-					issue_data(D + L_cur, L_n);
+					issue_data((t + 1) & 1, D + L_cur, L_n);
 				if (t + 2 < ntiles)
 					k_next = keys_of(t + 2);
 			} else {
