@@ -42,7 +42,13 @@ enum : uint32_t { ERR_SCRATCH = 8 };	// exception pool too small (press_gpu_set_
 // payload = static Huffman bitstream (else: the low bytes themselves)
 __host__ __device__ __forceinline__ bool ex_is_huff(int method)
 {
-	return method == PRESS_GPU_SHUFF_VBE21_ZD || method == PRESS_GPU_SHUFF_VBSSE21_ZD;
+	return method == PRESS_GPU_SHUFF_VBE21_ZD || method == PRESS_GPU_SHUFF_VBSSE21_ZD ||
+	       method == PRESS_GPU_SHUFF_VBBE21_ZD;
+}
+// exception lists bit-packed (vbbe21) instead of streamvbyte coded
+__host__ __device__ __forceinline__ bool ex_is_bitpacked(int method)
+{
+	return method == PRESS_GPU_VBBE21_ZD || method == PRESS_GPU_SHUFF_VBBE21_ZD;
 }
 
 struct ExArgs {
@@ -272,6 +278,40 @@ __device__ __forceinline__ uint32_t warp_svb_list(F value, uint32_t cnt, uint8_t
 	return nkeys + run;
 }
 
+// uint_press_16 / uint_press_32 of `cnt` values by one warp (press.c:489-507, 546-564 ->
+// uintx_press_core 285-397): [width u8] then the values as `width`-bit big-endian fields back to
+// back, most significant bit first, zero padded to a byte; width = uint_get_minbits(max)
+// (press.c:461-471).  Returns the byte length; writes when WRITE (a lane per output byte).
+template <bool WRITE, class F>
+__device__ __forceinline__ uint32_t warp_bitpack_list(F value, uint32_t cnt, uint8_t *dst, int lane)
+{
+	uint32_t mx = 0;
+	for (uint32_t k = lane; k < cnt; k += 32)
+		mx = max(mx, value(k));
+	mx = __reduce_max_sync(0xffffffffu, mx);
+	const uint32_t bits = mx ? 32u - __clz(mx) : 0u;
+	const uint64_t tot = (uint64_t) cnt * bits;
+	const uint32_t nbytes = (uint32_t) ((tot + 7) >> 3);
+	if (WRITE) {
+		if (lane == 0)
+			dst[0] = (uint8_t) bits;
+		for (uint32_t b = lane; b < nbytes; b += 32) {
+			// the fields overlapping bits [8b, 8b + 8) of the packed run
+			const uint64_t g0 = 8ull * b;
+			uint32_t k = (uint32_t) (g0 / bits);
+			uint32_t byte = 0;
+			for (uint64_t f0 = (uint64_t) k * bits; f0 < g0 + 8 && k < cnt; f0 += bits, k++) {
+				// field k covers bits [f0, f0 + bits); bit j of the byte (7 = first) is run bit g0 + 7 - j
+				const int64_t sh = (int64_t) (f0 + bits) - (int64_t) (g0 + 8);	// field's low bits past the byte
+				const uint64_t v = value(k);
+				byte |= (uint32_t) (sh >= 0 ? v >> sh : v << -sh) & 0xffu;
+			}
+			dst[1 + b] = (uint8_t) byte;
+		}
+	}
+	return 1 + nbytes;
+}
+
 __device__ __forceinline__ void put_le(uint8_t *p, uint64_t v, int nbytes)
 {
 	for (int b = 0; b < nbytes; b++)
@@ -307,11 +347,14 @@ __device__ __forceinline__ uint32_t ex_lists(int method, const ExList &L, uint32
 		}
 		return ex ? 8 : 6;
 	}
-	const uint32_t lp = warp_svb_list<2, WRITE>(gap, nex, dst + 4, lane);
+	const bool bp = ex_is_bitpacked(method);	// press.c:2822-2866
+	const uint32_t lp = bp ? warp_bitpack_list<WRITE>(gap, nex, dst + 4, lane) : warp_svb_list<2, WRITE>(gap, nex, dst + 4, lane);
 	if (WRITE && lane == 0)
 		put_le(dst, lp, 4);
 	uint8_t *d2 = dst + 4 + lp;
-	const uint32_t lv = ex ? warp_svb_list<2, WRITE>(val256, nex, d2 + 4, lane)
+	auto val16 = [&](uint32_t k) { return val256(k) & 0xffffu; };
+	const uint32_t lv = bp ? warp_bitpack_list<WRITE>(val16, nex, d2 + 4, lane)
+			  : ex ? warp_svb_list<2, WRITE>(val256, nex, d2 + 4, lane)
 			       : warp_svb_list<1, WRITE>(val256, nex, d2 + 4, lane);
 	if (WRITE && lane == 0)
 		put_le(d2, lv, 4);
@@ -604,8 +647,8 @@ __global__ void __launch_bounds__(NT) ex_size_kernel(const __grid_constant__ ExA
 		const uint32_t nex = a.r_nex[r];
 		const ExList L = {a.pool2 + a.r_pool[r]};
 		hdr = ex_fixed_bytes(a.method) + ex_lists<false>(a.method, L, nex, nullptr, lane);
-		if (a.method == PRESS_GPU_SHUFF_VBSSE21_ZD && hdr - 2 > 0xffffu) {
-			// press.c:4753: the header length lives in a uint16_t there; longer ones wrap and
+		if ((a.method == PRESS_GPU_SHUFF_VBSSE21_ZD || a.method == PRESS_GPU_SHUFF_VBBE21_ZD) && hdr - 2 > 0xffffu) {
+			// press.c:4753, 4521: the header length lives in a uint16_t there; longer ones wrap and
 			// the reference cannot read its own stream back.  Reported like the ex-zd cap.
 			if (lane == 0)
 				atomicOr(&a.hdr->error, ERR_EXZD_CAP);

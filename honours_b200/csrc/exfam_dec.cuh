@@ -112,6 +112,39 @@ __device__ __forceinline__ uint32_t warp_svb_decode(const uint8_t *src, uint64_t
 	return (uint32_t) run;
 }
 
+// uint_depress_16 / uint_depress_32 by one warp (press.c:509-528, 566-585): [width u8] + big-endian
+// bit fields (see warp_bitpack_list); sink as in warp_svb_decode.  Returns the bytes consumed.
+template <class F>
+__device__ __forceinline__ uint32_t warp_bitpack_decode(const uint8_t *src, uint64_t avail, uint32_t cnt,
+							F sink, int lane, bool &bad)
+{
+	if (avail < 1) {
+		bad = true;
+		return 0;
+	}
+	const uint32_t bits = src[0];
+	const uint64_t nbytes = ((uint64_t) cnt * bits + 7) >> 3;
+	if (bits > 32 || 1 + nbytes > avail) {
+		bad = true;
+		return 0;
+	}
+	for (uint32_t k0 = 0; k0 < cnt; k0 += 32) {
+		const uint32_t k = k0 + lane;
+		const bool act = k < cnt;
+		uint32_t val = 0;
+		if (act && bits) {
+			const uint64_t bo = (uint64_t) k * bits, b0 = bo >> 3;
+			uint64_t w = 0;		// bytes b0 .. b0 + 4 of the run, first byte on top
+			for (uint32_t i = 0; i < 5; i++)
+				if (b0 + i < nbytes)
+					w |= (uint64_t) src[1 + b0 + i] << (8 * (7 - i));
+			val = (uint32_t) ((w << (bo & 7)) >> (64 - bits));
+		}
+		sink(k, act, val);
+	}
+	return (uint32_t) (1 + nbytes);
+}
+
 __global__ void __launch_bounds__(NT) ex_parse_kernel(const __grid_constant__ ExDecArgs a)
 {
 	const uint64_t r = ((uint64_t) blockIdx.x * NT + threadIdx.x) >> 5;
@@ -218,7 +251,10 @@ __global__ void __launch_bounds__(NT) ex_parse_kernel(const __grid_constant__ Ex
 					break;
 				}
 				uint32_t used;
-				if (pass == 0)
+				if (ex_is_bitpacked(a.method))	// press.c:2912-2938
+					used = pass == 0 ? warp_bitpack_decode(a.in + off, len, nex, pos_sink, lane, bad)
+							 : warp_bitpack_decode(a.in + off, len, nex, val_sink, lane, bad);
+				else if (pass == 0)
 					used = warp_svb_decode<2>(a.in + off, len, nex, pos_sink, lane, bad);
 				else if (exz)
 					used = warp_svb_decode<2>(a.in + off, len, nex, val_sink, lane, bad);

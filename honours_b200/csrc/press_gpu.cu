@@ -227,6 +227,9 @@ uint64_t press_gpu_batch_bound(int method, uint64_t nreads, uint64_t nsamples)
 	case PRESS_GPU_SHUFF_VBE21_ZD: return 6 * nsamples + 4 * nreads + 16;
 	/* lists as vbsse21, 3-byte codes at most for the rest */
 	case PRESS_GPU_SHUFF_VBSSE21_ZD: return 4 * nsamples + 20 * nreads + 16;
+	/* bit-packed lists: <= 4 + 2 bytes per exception + two width bytes and two lengths */
+	case PRESS_GPU_VBBE21_ZD: return 6 * nsamples + 16 * nreads + 16;
+	case PRESS_GPU_SHUFF_VBBE21_ZD: return 6 * nsamples + 20 * nreads + 16;
 	case PRESS_GPU_VBSSE21_ZD: return 4 * nsamples + 16 * nreads + 16;
 	case PRESS_GPU_EX_ZD: return 2 * nsamples + 1024 * nreads + 16;	/* ex_zd.c:411 cap */
 	default: break;

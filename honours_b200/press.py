@@ -24,6 +24,8 @@ METHODS = {
     "ex_zd": 6,
     "shuff_vbe21_zd": 7,
     "shuff_vbsse21_zd": 8,
+    "vbbe21_zd": 9,
+    "shuff_vbbe21_zd": 10,
 }
 
 # per-read entry points of include/press_gpu.h, by method
@@ -40,6 +42,9 @@ PER_READ = {
                        "shuffman_vbe21_zd_gpu_depress_16"),
     "shuff_vbsse21_zd": ("shuffman_vbsse21_zd_gpu_bound_16", "shuffman_vbsse21_zd_gpu_press_16",
                          "shuffman_vbsse21_zd_gpu_depress_16"),
+    "vbbe21_zd": ("vbbe21_zd_gpu_bound_16", "vbbe21_zd_gpu_press_16", "vbbe21_zd_gpu_depress_16"),
+    "shuff_vbbe21_zd": ("shuffman_vbbe21_zd_gpu_bound_16", "shuffman_vbbe21_zd_gpu_press_16",
+                        "shuffman_vbbe21_zd_gpu_depress_16"),
 }
 
 
@@ -157,11 +162,11 @@ def press(method: str, sig: np.ndarray) -> tuple[int, bytes]:
         f.restype = None
         f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64)]
         f(sig.ctypes.data, n, out.ctypes.data, C.byref(nout))
-    elif method in ("vbe21_zd", "vbsse21_zd"):
+    elif method in ("vbe21_zd", "vbsse21_zd", "vbbe21_zd"):
         f.restype = None
         f.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]
         f(sig.ctypes.data, n, out.ctypes.data, C.byref(nout))
-    elif method in ("shuff_vbe21_zd", "shuff_vbsse21_zd"):
+    elif method in ("shuff_vbe21_zd", "shuff_vbsse21_zd", "shuff_vbbe21_zd"):
         f.restype = C.c_int
         f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]
         rc = f(None, sig.ctypes.data, n, out.ctypes.data, C.byref(nout))
@@ -188,12 +193,12 @@ def depress(method: str, stream: bytes, n: int) -> tuple[int, np.ndarray]:
         f.restype = None
         f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64)]
         f(buf.ctypes.data, n, out.ctypes.data, C.byref(nout))
-    elif method in ("vbe21_zd", "vbsse21_zd"):
+    elif method in ("vbe21_zd", "vbsse21_zd", "vbbe21_zd"):
         nout = C.c_uint32(n)
         f.restype = None
         f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint32)]
         f(buf.ctypes.data, len(stream), out.ctypes.data, C.byref(nout))
-    elif method in ("shuff_vbe21_zd", "shuff_vbsse21_zd"):
+    elif method in ("shuff_vbe21_zd", "shuff_vbsse21_zd", "shuff_vbbe21_zd"):
         nout = C.c_uint32(n)
         f.restype = C.c_int
         f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint32)]

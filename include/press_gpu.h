@@ -37,7 +37,9 @@ enum press_gpu_method {
 	PRESS_GPU_EX_ZD = 6,		/* hasgam_vbsse21_zdq_*_16 press.h:958-964, ex_zd.c */
 	PRESS_GPU_SHUFF_VBE21_ZD = 7,	/* shuffman_vbe21_zd_*_16  press.h:632-638  */
 	PRESS_GPU_SHUFF_VBSSE21_ZD = 8,	/* shuffman_vbsse21_zd_*_16 press.h:658-663, press.c:4742-4845 */
-	PRESS_GPU_NMETHODS = 9
+	PRESS_GPU_VBBE21_ZD = 9,	/* vbbe21_zd_*_16          press.h (press.c:3455-3500, 2775-2970): bit-packed lists */
+	PRESS_GPU_SHUFF_VBBE21_ZD = 10,	/* shuffman_vbbe21_zd_*_16 press.c:4505-4614 */
+	PRESS_GPU_NMETHODS = 11
 };
 
 /* ---- context ------------------------------------------------------------- */
@@ -117,6 +119,19 @@ int shuffman_vbsse21_zd_gpu_press_16(const void *table, const int16_t *in, uint3
 				     uint8_t *out, uint64_t *nout);
 int shuffman_vbsse21_zd_gpu_depress_16(const void *table, uint8_t *in, uint64_t nin,
 				       int16_t *out, uint32_t *nout);
+
+/* vbbe21-zd (exception lists bit-packed big-endian at their minimal width, press.c:2775-2970)
+ * and static Huffman over it (press.c:4505-4614; thesis' best non-range-coder ratio).  Same
+ * conventions as vbsse21_zd_gpu_* / shuffman_vbsse21_zd_gpu_* above, same 16-bit header limit
+ * for the Huffman variant (press.c:4521). */
+uint64_t vbbe21_zd_gpu_bound_16(uint32_t nin);
+void vbbe21_zd_gpu_press_16(const int16_t *in, uint32_t nin, uint8_t *out, uint64_t *nout);
+void vbbe21_zd_gpu_depress_16(uint8_t *in, uint64_t nin, int16_t *out, uint32_t *nout);
+uint64_t shuffman_vbbe21_zd_gpu_bound_16(uint32_t nin);
+int shuffman_vbbe21_zd_gpu_press_16(const void *table, const int16_t *in, uint32_t nin,
+				    uint8_t *out, uint64_t *nout);
+int shuffman_vbbe21_zd_gpu_depress_16(const void *table, uint8_t *in, uint64_t nin,
+				      int16_t *out, uint32_t *nout);
 
 /* ---- 2. batch API (device pointers) --------------------------------------
  * Layout: d_samples = all reads back to back (int16, base 16-byte aligned),

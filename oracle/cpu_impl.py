@@ -30,6 +30,8 @@ METHODS = {
     "ex_zd": 6,           # press.h hasgam_vbsse21_zdq_*_16
     "shuff_vbe21_zd": 7,  # press.h shuffman_vbe21_zd_*_16
     "shuff_vbsse21_zd": 8,  # press.h shuffman_vbsse21_zd_*_16
+    "vbbe21_zd": 9,  # press.h vbbe21_zd_*_16
+    "shuff_vbbe21_zd": 10,  # press.h shuffman_vbbe21_zd_*_16
 }
 
 _u8p = C.POINTER(C.c_uint8)

@@ -703,6 +703,119 @@ static int shuff_vbe21_zd_depress(const uint8_t *in, uint64_t nbytes, uint64_t n
 	return ret;
 }
 
+/* ---------- a18: vbbe21-zd (press.c:2775-2970, 3455-3500) ------------------- */
+
+/* uint_get_minbits (press.c:461-471): smallest i with max < 2^i */
+static uint8_t minbits_of(uint32_t max)
+{
+	uint8_t i = 0;
+	while (i < 32 && ((uint64_t) max >> i) != 0)
+		i++;
+	return i;
+}
+
+/* uint_press_16 / uint_press_32 (press.c:489-507, 546-564 -> uintx_press_core 285-397): one byte
+ * holding the width, then the values as `bits`-wide big-endian fields back to back, most
+ * significant bit first, the last byte padded with zero bits; width 0 writes nothing more. */
+static uint64_t bitpack_be(const uint32_t *v, uint32_t count, uint8_t bits, uint8_t *out)
+{
+	out[0] = bits;
+	uint64_t nbytes = ((uint64_t) count * bits + 7) / 8;
+	memset(out + 1, 0, nbytes);
+	uint64_t bp = 0;
+	for (uint32_t k = 0; k < count; k++)
+		for (int b = bits - 1; b >= 0; b--, bp++)
+			if ((v[k] >> b) & 1u)
+				out[1 + bp / 8] |= (uint8_t) (0x80u >> (bp % 8));
+	return 1 + nbytes;
+}
+
+static void bitunpack_be(const uint8_t *in, uint32_t count, uint32_t *v)
+{
+	uint8_t bits = in[0];
+	uint64_t bp = 0;
+	for (uint32_t k = 0; k < count; k++) {
+		uint32_t x = 0;
+		for (int b = 0; b < bits; b++, bp++)
+			x = (x << 1) | ((in[1 + bp / 8] >> (7 - bp % 8)) & 1u);
+		v[k] = x;
+	}
+}
+
+static uint32_t max_u32(const uint32_t *v, uint32_t n)
+{
+	uint32_t m = 0;
+	for (uint32_t k = 0; k < n; k++)
+		m = v[k] > m ? v[k] : m;
+	return m;
+}
+
+static int vbbe21_zd_press(const int16_t *in, uint32_t n, uint8_t *out, uint64_t *nout)
+{
+	if (n == 0)
+		return -1;
+	uint16_t *zd = malloc(n * sizeof *zd);
+	struct exlist e;
+	if (!zd)
+		return -1;
+	oracle_zigdelta(in, n, zd);
+	if (collect_exceptions(zd + 1, n - 1, &e))
+		return -1;
+	uint8_t *p = out;
+	put_u16(p, zd[0]); p += 2;
+	put_u32(p, e.nex); p += 4;
+	if (e.nex > 1) {	/* press.c:2822-2866 */
+		uint32_t *tmp = malloc(e.nex * sizeof *tmp);
+		pos_to_gaps(e.pos, e.nex, tmp);
+		uint32_t len = (uint32_t) bitpack_be(tmp, e.nex, minbits_of(max_u32(tmp, e.nex)), p + 4);
+		put_u32(p, len); p += 4 + len;
+		for (uint32_t k = 0; k < e.nex; k++)
+			tmp[k] = (uint16_t) (e.val[k] - 256);
+		len = (uint32_t) bitpack_be(tmp, e.nex, minbits_of(max_u32(tmp, e.nex)), p + 4);
+		put_u32(p, len); p += 4 + len;
+		free(tmp);
+	} else if (e.nex == 1) {	/* press.c:2867-2872 */
+		put_u32(p, e.pos[0]); p += 4;
+		put_u16(p, (uint16_t) (e.val[0] - 256)); p += 2;
+	}
+	p = emit_low_bytes(zd + 1, n - 1, p);
+	*nout = (uint64_t) (p - out);
+	free_exceptions(&e);
+	free(zd);
+	return 0;
+}
+
+static int vbbe21_zd_depress(const uint8_t *in, uint64_t nbytes, uint64_t ncap,
+			     int16_t *out, uint64_t *nout)
+{
+	uint64_t cap = (nbytes > ncap ? nbytes : ncap) + 1;
+	uint16_t *zd = malloc(cap * sizeof *zd);
+	if (!zd || nbytes < 6)
+		return -1;
+	zd[0] = get_u16(in);
+	uint32_t nex = get_u32(in + 2);
+	uint64_t off = 6;
+	uint32_t *pos = malloc((nex ? nex : 1) * sizeof *pos);
+	uint32_t *exv = malloc((nex ? nex : 1) * sizeof *exv);
+	if (nex > 1) {		/* press.c:2912-2938 */
+		uint32_t len = get_u32(in + off); off += 4;
+		bitunpack_be(in + off, nex, pos); off += len;
+		gaps_to_pos(pos, nex);
+		len = get_u32(in + off); off += 4;
+		bitunpack_be(in + off, nex, exv); off += len;
+	} else if (nex == 1) {
+		pos[0] = get_u32(in + off); off += 4;
+		exv[0] = get_u16(in + off); off += 2;
+	}
+	for (uint32_t k = 0; k < nex; k++)
+		zd[1 + pos[k]] = (uint16_t) (exv[k] + 256);
+	uint32_t m = merge_low_bytes(in + off, nbytes - off, pos, nex, zd + 1);
+	oracle_unzigdelta(zd, (uint64_t) m + 1, out);
+	*nout = (uint64_t) m + 1;
+	free(pos); free(exv); free(zd);
+	return 0;
+}
+
 /* ---------- a17: shuffman_vbsse21_zd (press.c:4737-4845) -------------------- */
 
 /* length of [nex][coded lists] at the head of a vbsse21 body (press.c:4766-4775, 4808-4817);
@@ -731,14 +844,16 @@ static int vbsse21_exlen(const uint8_t *body, uint64_t nbody, uint64_t *exlen)
 	return 0;
 }
 
-static int shuff_vbsse21_zd_press(const int16_t *in, uint32_t n, uint8_t *out, uint64_t *nout)
+/* a19: shuffman_vbbe21_zd (press.c:4505-4614) has the same frame over the vbbe21 body */
+static int shuff_lists_zd_press(int bitpacked, const int16_t *in, uint32_t n, uint8_t *out, uint64_t *nout)
 {
 	if (!H.set || n == 0)
 		return 1;
 	uint64_t cap = 64 + 8 * (uint64_t) n;
 	uint8_t *vb = malloc(cap);
 	uint64_t nvb = 0, exlen = 0;
-	if (!vb || vbsse21_zd_press(in, n, vb, &nvb) || vbsse21_exlen(vb + 2, nvb - 2, &exlen)) {
+	if (!vb || (bitpacked ? vbbe21_zd_press(in, n, vb, &nvb) : vbsse21_zd_press(in, n, vb, &nvb)) ||
+	    vbsse21_exlen(vb + 2, nvb - 2, &exlen)) {
 		free(vb);
 		return 1;
 	}
@@ -749,8 +864,8 @@ static int shuff_vbsse21_zd_press(const int16_t *in, uint32_t n, uint8_t *out, u
 	return 0;
 }
 
-static int shuff_vbsse21_zd_depress(const uint8_t *in, uint64_t nbytes, uint64_t n,
-				    int16_t *out, uint64_t *nout)
+static int shuff_lists_zd_depress(int bitpacked, const uint8_t *in, uint64_t nbytes, uint64_t n,
+				  int16_t *out, uint64_t *nout)
 {
 	uint64_t exlen = 0;
 	if (!H.set || nbytes < 6 || vbsse21_exlen(in + 2, nbytes - 2, &exlen))
@@ -764,7 +879,8 @@ static int shuff_vbsse21_zd_depress(const uint8_t *in, uint64_t nbytes, uint64_t
 	memcpy(vb, in, hdr);
 	int ret = huff_decode(in + hdr, nbytes - hdr, vb + hdr, &m);	/* press.c:4826-4829 */
 	if (ret == 0)
-		ret = vbsse21_zd_depress(vb, hdr + m, n, out, nout) ? 1 : 0;
+		ret = (bitpacked ? vbbe21_zd_depress(vb, hdr + m, n, out, nout)
+				 : vbsse21_zd_depress(vb, hdr + m, n, out, nout)) ? 1 : 0;
 	free(vb);
 	return ret;
 }
@@ -782,6 +898,8 @@ uint64_t oracle_bound(int method, uint64_t n)
 	case ORC_VBSSE21_ZD:						/* press.c:3543-3546 */
 	case ORC_SHUFF_VBE21_ZD:					/* press.c:4409-4412 -> 3965 */
 	case ORC_SHUFF_VBSSE21_ZD:					/* press.c:4737-4740 -> 4293 */
+	case ORC_VBBE21_ZD:						/* press.c:3455-3458 */
+	case ORC_SHUFF_VBBE21_ZD:					/* press.c:4505-4508 */
 		return 2 + vb1e2_bound((uint32_t) (n - 1));
 	case ORC_EX_ZD:							/* press.c:8461-8464 */
 		return svb32_bound(2 + vb1e2_bound((uint32_t) (n - 1)));
@@ -806,7 +924,9 @@ int oracle_press(int method, const int16_t *in, uint64_t n, uint8_t *out, uint64
 	case ORC_VBSSE21_ZD: return vbsse21_zd_press(in, (uint32_t) n, out, nout);
 	case ORC_EX_ZD: return ex_zd_press(in, (uint32_t) n, out, nout);
 	case ORC_SHUFF_VBE21_ZD: return shuff_vbe21_zd_press(in, (uint32_t) n, out, nout);
-	case ORC_SHUFF_VBSSE21_ZD: return shuff_vbsse21_zd_press(in, (uint32_t) n, out, nout);
+	case ORC_SHUFF_VBSSE21_ZD: return shuff_lists_zd_press(0, in, (uint32_t) n, out, nout);
+	case ORC_VBBE21_ZD: return vbbe21_zd_press(in, (uint32_t) n, out, nout);
+	case ORC_SHUFF_VBBE21_ZD: return shuff_lists_zd_press(1, in, (uint32_t) n, out, nout);
 	}
 	return -1;
 }
@@ -825,7 +945,9 @@ int oracle_depress(int method, const uint8_t *in, uint64_t nbytes, uint64_t n,
 	case ORC_VBSSE21_ZD: return vbsse21_zd_depress(in, nbytes, n, out, nout);
 	case ORC_EX_ZD: return ex_zd_depress(in, nbytes, n, out, nout);
 	case ORC_SHUFF_VBE21_ZD: return shuff_vbe21_zd_depress(in, nbytes, n, out, nout);
-	case ORC_SHUFF_VBSSE21_ZD: return shuff_vbsse21_zd_depress(in, nbytes, n, out, nout);
+	case ORC_SHUFF_VBSSE21_ZD: return shuff_lists_zd_depress(0, in, nbytes, n, out, nout);
+	case ORC_VBBE21_ZD: return vbbe21_zd_depress(in, nbytes, n, out, nout);
+	case ORC_SHUFF_VBBE21_ZD: return shuff_lists_zd_depress(1, in, nbytes, n, out, nout);
 	}
 	return -1;
 }

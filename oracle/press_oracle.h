@@ -33,6 +33,8 @@ enum {
 	ORC_EX_ZD = 6,		/* press.h hasgam_vbsse21_zdq_*_16 (a10-a12) */
 	ORC_SHUFF_VBE21_ZD = 7,	/* press.h shuffman_vbe21_zd_*_16 (a13-a16) */
 	ORC_SHUFF_VBSSE21_ZD = 8,	/* press.h shuffman_vbsse21_zd_*_16 (a17) */
+	ORC_VBBE21_ZD = 9,	/* press.h vbbe21_zd_*_16 (a18: bit-packed exception lists) */
+	ORC_SHUFF_VBBE21_ZD = 10,	/* press.h shuffman_vbbe21_zd_*_16 (a19) */
 	ORC_NMETHODS = 8
 };
 

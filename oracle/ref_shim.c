@@ -16,7 +16,7 @@
 #include "ex_zd.h"
 
 enum { M_SVB16_ZD, M_SVB_ZD, M_VBZ_SVB16_ZD, M_VBZ_SVB_ZD, M_VBE21_ZD,
-       M_VBSSE21_ZD, M_EX_ZD, M_SHUFF_VBE21_ZD, M_SHUFF_VBSSE21_ZD };
+       M_VBSSE21_ZD, M_EX_ZD, M_SHUFF_VBE21_ZD, M_SHUFF_VBSSE21_ZD, M_VBBE21_ZD, M_SHUFF_VBBE21_ZD };
 
 static huffman_node *g_root;
 static SymbolEncoder g_se;
@@ -52,6 +52,8 @@ uint64_t ref_bound(int method, uint64_t n)
 	case M_EX_ZD: return hasgam_vbsse21_zdq_bound_16((uint32_t) n);
 	case M_SHUFF_VBE21_ZD: return shuffman_vbe21_zd_bound_16((uint32_t) n);
 	case M_SHUFF_VBSSE21_ZD: return shuffman_vbsse21_zd_bound_16((uint32_t) n);
+	case M_VBBE21_ZD: return vbbe21_zd_bound_16((uint32_t) n);
+	case M_SHUFF_VBBE21_ZD: return shuffman_vbbe21_zd_bound_16((uint32_t) n);
 	}
 	return 0;
 }
@@ -97,6 +99,11 @@ int ref_press(int method, const int16_t *in, uint64_t n, uint8_t *out, uint64_t 
 		if (!g_have_table)
 			return 1;
 		return shuffman_vbsse21_zd_press_16(&g_se, in, (uint32_t) n, out, nout);	/* press.c:4742 */
+	case M_VBBE21_ZD: vbbe21_zd_press_16(in, (uint32_t) n, out, nout); return 0;	/* press.c:3460 */
+	case M_SHUFF_VBBE21_ZD:
+		if (!g_have_table)
+			return 1;
+		return shuffman_vbbe21_zd_press_16(&g_se, in, (uint32_t) n, out, nout);	/* press.c:4510 */
 	}
 	return -1;
 }
@@ -133,6 +140,12 @@ int ref_depress(int method, const uint8_t *in, uint64_t nbytes, uint64_t n,
 		if (!g_have_table)
 			return 1;
 		r = shuffman_vbsse21_zd_depress_16(g_root, (uint8_t *) in, nbytes, out, &n32);	/* press.c:4792 */
+		break;
+	case M_VBBE21_ZD: vbbe21_zd_depress_16((uint8_t *) in, nbytes, out, &n32); break;	/* press.c:3476 */
+	case M_SHUFF_VBBE21_ZD:
+		if (!g_have_table)
+			return 1;
+		r = shuffman_vbbe21_zd_depress_16(g_root, (uint8_t *) in, nbytes, out, &n32);	/* press.c:4560 */
 		break;
 	default: return -1;
 	}

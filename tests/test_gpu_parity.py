@@ -12,8 +12,9 @@ pytestmark = pytest.mark.gpu
 
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 IMPLEMENTED = ["svb16_zd", "svb_zd", "vbz_svb16_zd", "vbz_svb_zd",
-               "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd", "shuff_vbsse21_zd"]
-HUFF = ("shuff_vbe21_zd", "shuff_vbsse21_zd")
+               "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd", "shuff_vbsse21_zd", "vbbe21_zd", "shuff_vbbe21_zd"]
+HUFF = ("shuff_vbe21_zd", "shuff_vbsse21_zd", "shuff_vbbe21_zd")
+HDR16 = ("shuff_vbsse21_zd", "shuff_vbbe21_zd")    # header length kept in a uint16_t (press.c:4753, 4521)
 EXFAM = IMPLEMENTED[4:]
 
 
@@ -97,7 +98,7 @@ def test_batch_host_matches_oracle(gpu, oracle, method):
     rng = np.random.default_rng(7)
     kinds = ("walk", "spiky", "q") if method in ("ex_zd",) + HUFF else ("walk", "spiky", "q", "noise")
     # (shuffman-vbsse21: coded exception lists must stay below 64 KB, press.c:4753)
-    hi = 12000 if method == "shuff_vbsse21_zd" else 30000
+    hi = 12000 if method in HDR16 else 30000
     samples, offsets, reads = make_batch(rng, 300, 2 if method in EXFAM else 1, hi, kinds=kinds)
     rc, cont, oo = gpu.batch_press_host(method, samples, offsets)
     assert rc == 0
@@ -129,14 +130,14 @@ def test_long_read_many_tiles(gpu, oracle):
     """one 3.3 M-sample read: > 800 tiles chained by look-back inside one read"""
     rng = np.random.default_rng(11)
     s = rand_read(rng, "spiky", 3_300_001)
-    for method in ("svb16_zd", "vbz_svb_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd"):
+    for method in ("svb16_zd", "vbz_svb_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd", "vbbe21_zd"):
         rc, st = gpu.press(method, s)
         assert rc == 0 and st == oracle.press(method, s)[1]
         rc, back = gpu.depress(method, st, s.size)
         assert rc == 0 and np.array_equal(back, s)
 
 
-@pytest.mark.parametrize("method", ["svb16_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd"])
+@pytest.mark.parametrize("method", ["svb16_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd", "vbbe21_zd"])
 def test_device_batch_api_torch_pointers(gpu, oracle, method):
     """the measured path: device-resident in/out, raw pointers through the C ABI"""
     import torch
@@ -196,22 +197,23 @@ def test_ex_zd_scratch_cap_failure_mirrors_reference(gpu, oracle):
     assert rc == 1 and cont.tobytes() == e + e and int(oo[1]) == int(oo[2])
 
 
-def test_shuffman_vbsse21_header_limit_mirrors_reference(gpu, oracle):
-    """press.c:4753 keeps the header length in a uint16_t: once the coded exception lists pass
+@pytest.mark.parametrize("method", HDR16)
+def test_shuffman_header_limit_mirrors_reference(gpu, oracle, method):
+    """press.c:4753 / 4521 keep the header length in a uint16_t: once the coded exception lists pass
     65535 bytes the reference writes a stream it cannot read back; both sides refuse the read"""
     rng = np.random.default_rng(14)
     s = rand_read(rng, "noise", 40000)          # ~40000 exceptions, > 130 KB of coded lists
-    assert oracle.press("shuff_vbsse21_zd", s)[0] != 0
-    assert gpu.press("shuff_vbsse21_zd", s)[0] != 0
+    assert oracle.press(method, s)[0] != 0
+    assert gpu.press(method, s)[0] != 0
     small = rand_read(rng, "noise", 15000)      # ~50 KB of lists: still representable
-    ro, so = oracle.press("shuff_vbsse21_zd", small)
-    rc, st = gpu.press("shuff_vbsse21_zd", small)
+    ro, so = oracle.press(method, small)
+    rc, st = gpu.press(method, small)
     assert ro == rc == 0 and st == so
     ok = rand_read(rng, "walk", 5000)
     samples = np.concatenate([ok, s, ok])
     offsets = np.array([0, 5000, 45000, 50000], dtype=np.uint64)
-    rc, cont, oo = gpu.batch_press_host("shuff_vbsse21_zd", samples, offsets)
-    e = oracle.press("shuff_vbsse21_zd", ok)[1]
+    rc, cont, oo = gpu.batch_press_host(method, samples, offsets)
+    e = oracle.press(method, ok)[1]
     assert rc == 1 and cont.tobytes() == e + e and int(oo[1]) == int(oo[2])
 
 
@@ -221,7 +223,7 @@ def test_exception_rate_sweep(gpu, oracle, method, p_ex):
     """config 3: exception-rate sweep on synthetic NA12878-like reads (host generator)"""
     from honours_b200 import workload
     lengths, x0, shift = workload.read_table(40, q_fraction=0.25)
-    lengths = np.minimum(lengths, 12000 if method == "shuff_vbsse21_zd" else 30000)    # (press.c:4753)
+    lengths = np.minimum(lengths, 12000 if method in HDR16 else 30000)    # (press.c:4753)
     offsets = workload.offsets_of(lengths)
     samples = workload.synth_host(offsets, x0, shift, p_ex=p_ex)
     reads = [samples[int(offsets[r]):int(offsets[r + 1])] for r in range(len(lengths))]

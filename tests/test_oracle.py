@@ -81,7 +81,7 @@ def test_oracle_matches_reference_small_streams(oracle, method):
         assert rc == 0 and np.array_equal(back, s), (name, method)
 
 
-HUFF = ("shuff_vbe21_zd", "shuff_vbsse21_zd")
+HUFF = ("shuff_vbe21_zd", "shuff_vbsse21_zd", "shuff_vbbe21_zd")
 
 
 def _huff_header_len(method, st):
