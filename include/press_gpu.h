@@ -76,7 +76,10 @@ void svb_zd_gpu_depress_16(const uint8_t *in, uint64_t nin, int16_t *out, uint64
 /* VBZ, the part before / after zstd (zstd itself stays on the host, outside
  * this library): press.h:378-384, 402-408 (press.c:1860-1910, 2020-2070).
  * press writes tmp = [nin u32 LE] ++ stream, exactly what the reference hands
- * to zstd_press (press.c:1881, 2041); depress takes that tmp. */
+ * to zstd_press (press.c:1881, 2041); depress takes that tmp.
+ * Every depress whose sample count comes from the stream itself (these two, the exception
+ * methods) reads *nout on entry as the room in `out`, in samples, the way press/test.c sets
+ * it (test.c:2195, 5933), and fails instead of writing past it; 0 = unknown, no check. */
 uint64_t vbz_svb_zd_gpu_bound_16(uint32_t nin);
 int vbz_svb_zd_gpu_press_16(const int16_t *in, uint32_t nin, uint8_t *out, uint64_t *nout);
 int vbz_svb_zd_gpu_depress_16(const uint8_t *in, uint64_t nin, int16_t *out, uint32_t *nout);

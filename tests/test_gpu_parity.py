@@ -361,3 +361,15 @@ def test_bench_scale_chunk_properties(gpu, oracle, method):
     assert bool((d_back[ns:] == -1).all())      # nothing written past the last sample
     del d_s, d_out, d_back, d_scr
     torch.cuda.empty_cache()
+
+
+def test_corrupted_streams_do_not_fault():
+    """truncated, bit-flipped and length-forged streams through every per-read depress: an error
+    or wrong samples, never a crash or a CUDA fault (own process: a fault would poison the context
+    of this session).  tools/fuzz_decode.py checks after every call that the context still works."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "fuzz_decode.py"), "40", "7"],
+                       capture_output=True, text=True, timeout=600, cwd=root)
+    assert r.returncode == 0 and "fuzz ok" in r.stdout, (r.returncode, r.stdout[-800:], r.stderr[-800:])
