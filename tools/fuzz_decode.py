@@ -69,4 +69,28 @@ for method in press.implemented_methods():
             print(f"CONTEXT DEAD after {method} case {case} mode {mode} n {n} len {len(b)}: {press.last_error()}")
             sys.exit(1)
     print(f"{method}: {errs} rejected, {oks} decoded (to whatever the bytes say), context alive")
+# ---- the batch path: a container of 40 reads with corrupted bytes / truncated tail
+for method in press.implemented_methods():
+    lens = rng.integers(2, 9000, 40)
+    reads = [make(i % 3, int(n)) for i, n in enumerate(lens)]
+    samples = np.concatenate(reads)
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    rc, cont, oo = press.batch_press_host(method, samples, offsets)
+    assert rc == 0
+    rej = 0
+    for case in range(max(4, N // 10)):
+        c = cont.copy()
+        for _ in range(int(rng.integers(1, 40))):
+            c[int(rng.integers(0, c.size))] ^= int(rng.integers(1, 256))
+        o2 = oo.copy()
+        if case % 3 == 2:       # the last stream cut short
+            o2[-1] = max(int(o2[-2]), int(o2[-1]) - int(rng.integers(1, 200)))
+        try:
+            press.batch_depress_host(method, c, o2, offsets)
+        except press.PressGpuError:
+            rej += 1
+        if not alive(method):
+            print(f"CONTEXT DEAD after batch {method} case {case}: {press.last_error()}")
+            sys.exit(1)
+    print(f"{method}: batch, {rej} containers rejected, context alive")
 print("fuzz ok")
