@@ -12,7 +12,7 @@ python -m pytest tests -m gpu -x -q > $O/pytest_gpu_$TAG.log 2>&1; echo "pytest 
 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke_$TAG.log 2>&1; echo "smoke exit $?"; tail -2 $O/smoke_$TAG.log
 python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_ref_$TAG.json 2> $O/bench_ref_$TAG.err; echo "ref exit $?"
 python bench.py > $O/bench_svb16_zd_$TAG.json 2> $O/bench_svb16_zd_$TAG.err; echo "bench exit $?"; tail -2 $O/bench_svb16_zd_$TAG.err
-for m in svb_zd vbz_svb16_zd vbz_svb_zd vbe21_zd vbsse21_zd ex_zd shuff_vbe21_zd shuff_vbsse21_zd; do
+for m in svb_zd vbz_svb16_zd vbz_svb_zd vbe21_zd vbsse21_zd ex_zd shuff_vbe21_zd shuff_vbsse21_zd vbbe21_zd shuff_vbbe21_zd; do
   python bench.py --method $m --reads 125000 --steps 3 --warmup 3 --e2e-gb 1.0 --cpu-reads 1500 --cpu-seconds 4 \
       > $O/bench_${m}_$TAG.json 2> $O/bench_${m}_$TAG.err; echo "$m exit $?"
 done

@@ -15,7 +15,7 @@ G = os.path.join(ROOT, "gpurun_out")
 P = os.path.join(ROOT, "profiles")
 tag = sys.argv[1]
 METHODS = ["svb16_zd", "svb_zd", "vbz_svb16_zd", "vbz_svb_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd",
-           "shuff_vbsse21_zd"]
+           "shuff_vbsse21_zd", "vbbe21_zd", "shuff_vbbe21_zd"]
 
 
 def last_json(path):
