@@ -99,9 +99,12 @@ for m, enc, dec, bps in (("vbe21_zd", ["ex_count", "ex_emit_bytes"], ["ex_decode
                                               + " + ".join(ks) + ")"}
     except Exception as e:
         print(m, "traffic:", e)
-for twin in ("vbsse21_zd", "ex_zd"):    # same kernels as vbe21_zd; only the header coding differs
-    for nm in ("encode", "decode"):
-        if f"vbe21_zd_{nm}" in traffic:
-            traffic[f"{twin}_{nm}"] = dict(traffic[f"vbe21_zd_{nm}"], source=traffic[f"vbe21_zd_{nm}"]["source"] + " [vbe21_zd capture: same kernels]")
+# same kernels as the captured method; only the header coding differs
+for base, twins in (("vbe21_zd", ("vbsse21_zd", "vbbe21_zd", "ex_zd")), ("shuff_vbe21_zd", ("shuff_vbsse21_zd", "shuff_vbbe21_zd"))):
+    for twin in twins:
+        for nm in ("encode", "decode"):
+            if f"{base}_{nm}" in traffic:
+                traffic[f"{twin}_{nm}"] = dict(traffic[f"{base}_{nm}"],
+                                               source=traffic[f"{base}_{nm}"]["source"] + f" [{base} capture: same kernels]")
 json.dump(traffic, open(os.path.join(P, "traffic.json"), "w"), indent=1)
 print("profiles/ updated for", tag, "; traffic keys:", sorted(traffic))
