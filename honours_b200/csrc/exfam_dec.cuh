@@ -396,7 +396,7 @@ __device__ __forceinline__ uint32_t hd_run(uint32_t swt_sa, uint32_t lut_sa, con
 	return pos;
 }
 
-__global__ void __launch_bounds__(NT, 6) huff_decode_kernel(const __grid_constant__ ExDecArgs a)
+__global__ void __launch_bounds__(NT, 5) huff_decode_kernel(const __grid_constant__ ExDecArgs a)
 {
 	__shared__ uint32_t s_lut[1 << HD_L1];
 	__shared__ uint32_t s_exit[2][NT];
@@ -441,31 +441,41 @@ __global__ void __launch_bounds__(NT, 6) huff_decode_kernel(const __grid_constan
 		uint32_t entry = 0;	// bit offset of the first code inside the step
 		int64_t done = 0;	// symbols out so far
 		uint64_t steps = 0, rounds = 0;
-		for (uint64_t cb = 0; cb < nbytes && done < count; cb += HD_CHUNK) {
-			// stage HD_CHUNK + 4 bytes of the bitstream from byte cb, zero filled past its end
-			const uint64_t left = nbytes - cb;
-			{
-				const uint8_t *s = src + cb;
-				const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(s) & 3);
-				const uint32_t *gw = reinterpret_cast<const uint32_t *>(s - al);
-				for (uint32_t w = tid; w <= HD_CHUNK / 4; w += NT) {
+		// Every thread fetches the 20 bytes of its own sub-block (+ the next one's first word)
+		// straight from global memory, one step ahead, as six aligned words; its column of the
+		// transposed stage is private, so staging needs no barrier.  Bytes past the end of the
+		// bitstream (the next read's stream, or zeros outside the container) only ever decode
+		// into symbols beyond `count`, which are dropped.
+		uint32_t g[6];
+		const uint32_t gal = (uint32_t) (reinterpret_cast<uintptr_t>(src + 16 * tid) & 3);
+		auto fetch = [&](uint64_t cb) {
+			const uint8_t *s = src + cb + 16 * tid - gal;	// 4-byte aligned
+			if (s >= a.in && s + 24 <= limit) {
+				const uint32_t *gw = reinterpret_cast<const uint32_t *>(s);
+#pragma unroll
+				for (int j = 0; j < 6; j++)
+					g[j] = __ldg(gw + j);
+			} else {
+#pragma unroll
+				for (int j = 0; j < 6; j++) {
 					uint32_t v = 0;
-					if (4ull * w < left) {
-						const uint8_t *p0 = reinterpret_cast<const uint8_t *>(gw + w);
-						if (4ull * w + 8 <= left && p0 >= a.in && p0 + 8 <= limit) {
-							v = __funnelshift_r(__ldg(gw + w), __ldg(gw + w + 1), 8 * al);
-						} else {
-							for (uint32_t b = 0; b < 4 && 4ull * w + b < left; b++)
-								v |= (uint32_t) s[4ull * w + b] << (8 * b);
-						}
+					for (int b = 0; b < 4; b++) {
+						const uint8_t *q = s + 4 * j + b;
+						if (q >= a.in && q < limit)
+							v |= (uint32_t) *q << (8 * b);
 					}
-					if (w < HD_CHUNK / 4)
-						s_w[(w & 3u) * HD_ROW + (w >> 2)] = v;
-					if ((w & 3u) == 0 && w)
-						s_w[4 * HD_ROW + (w >> 2) - 1] = v;
+					g[j] = v;
 				}
 			}
-			__syncthreads();
+		};
+		fetch(0);
+		for (uint64_t cb = 0; cb < nbytes && done < count; cb += HD_CHUNK) {
+			const uint64_t left = nbytes - cb;
+#pragma unroll
+			for (int j = 0; j < 5; j++)
+				s_w[j * HD_ROW + tid] = __funnelshift_r(g[j], g[j + 1], 8 * gal);
+			if (cb + HD_CHUNK < nbytes)
+				fetch(cb + HD_CHUNK);
 			const uint32_t cbits = left < HD_CHUNK ? (uint32_t) left * 8 : HD_CHUNK * 8;
 			const uint32_t nsub = (cbits + HD_SUB - 1) / HD_SUB;
 			const bool act = (uint32_t) tid < nsub;
