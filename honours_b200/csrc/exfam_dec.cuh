@@ -489,22 +489,33 @@ __global__ void __launch_bounds__(NT, 5) huff_decode_kernel(const __grid_constan
 			s_exit[0][tid] = ex;
 			__syncthreads();
 			uint32_t rd = 0;
-			for (;;) {	// until no exit moved (exits double buffered: one barrier per round)
+			// Rounds until nothing moves (exits double buffered: one barrier per round).  Inside a
+			// round every warp settles its own 32 sub-blocks by shuffles -- a lane whose left
+			// neighbour's exit moved decodes again at once -- so only the exit of a warp's last
+			// lane, the one the next warp reads from shared memory, can ask for another round:
+			// that exit is right after the first pass in all but ~0.5 % of the sub-blocks.
+			const int lane = tid & 31;
+			for (;;) {
 				rd++;
-				const uint32_t e = tid ? s_exit[(rd - 1) & 1][tid - 1] : entry;
-				bool moved = false;
-				if (act && e != cur) {
-					cur = e;
-					uint32_t x;
-					if (slots)
-						x = hd_run_pairs(swt_sa, lut_sa, sub, sub_bits, cur, cnt, two, mypairs) - HD_SUB;
-					else
-						x = hd_run<0>(swt_sa, lut_sa, sub, sub_bits, cur, cnt, nullptr, 0) - HD_SUB;
-					moved = x != ex;
-					ex = x;
+				uint32_t e = tid ? s_exit[(rd - 1) & 1][tid - 1] : entry;
+				const uint32_t ex0 = ex;
+				for (;;) {
+					const bool need = act && e != cur;
+					if (!__any_sync(0xffffffffu, need))
+						break;
+					if (need) {
+						cur = e;
+						if (slots)
+							ex = hd_run_pairs(swt_sa, lut_sa, sub, sub_bits, cur, cnt, two, mypairs) - HD_SUB;
+						else
+							ex = hd_run<0>(swt_sa, lut_sa, sub, sub_bits, cur, cnt, nullptr, 0) - HD_SUB;
+					}
+					const uint32_t left_ex = __shfl_up_sync(0xffffffffu, ex, 1);
+					if (lane)
+						e = left_ex;
 				}
 				s_exit[rd & 1][tid] = ex;
-				if (!__syncthreads_or(moved))
+				if (!__syncthreads_or(lane == 31 && ex != ex0))
 					break;
 			}
 			const uint32_t nsym = slots ? cnt + __popc(two) : cnt;
