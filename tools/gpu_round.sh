@@ -29,6 +29,6 @@ ls $O | grep $TAG
 # the exception / Huffman methods: launch lists and one full capture per kernel (20 k reads)
 bash tools/ncu_list.sh $TAG 20000 vbe21_zd shuff_vbe21_zd > $O/ncu_list_ex_$TAG.log 2>&1
 bash tools/ncu_full.sh $TAG 20000 vbe21_zd ex_count ex_emit_bytes ex_decode > $O/ncu_full_vbe21_$TAG.log 2>&1
-bash tools/ncu_full.sh $TAG 20000 shuff_vbe21_zd ex_count ex_emit_kernel huff_decode ex_decode > $O/ncu_full_shuff_$TAG.log 2>&1
+bash tools/ncu_full.sh $TAG 20000 shuff_vbe21_zd ex_count ex_emit_kernel huff_decode > $O/ncu_full_shuff_$TAG.log 2>&1
 bash tools/sweep.sh $TAG 20000 > $O/sweep_$TAG.log 2>&1
 ls $O | grep -c $TAG

@@ -36,7 +36,7 @@ for a, b in [(f"pytest_gpu_{tag}.log", f"{tag}_pytest_gpu.log"), (f"smoke_{tag}.
 pd.launches(os.path.join(G, f"launches_svb16_zd_{tag}.csv"), os.path.join(P, f"{tag}_svb16_zd_launches.txt"))
 pd.kernels(os.path.join(G, f"prof_svb16_zd_{tag}.ncu-rep"), os.path.join(P, f"{tag}_svb16_zd_kernels.txt"))
 caps = {"vbe21_zd": ["ex_count", "ex_emit_bytes", "ex_decode"],
-        "shuff_vbe21_zd": ["ex_count", "ex_emit_kernel", "huff_decode", "ex_decode"]}
+        "shuff_vbe21_zd": ["ex_count", "ex_emit_kernel", "huff_decode"]}
 for m, ks in caps.items():
     lc = os.path.join(G, f"launches_{m}_{tag}.csv")
     if os.path.exists(lc):
@@ -93,7 +93,8 @@ for m, enc, dec, bps in (("vbe21_zd", ["ex_count", "ex_emit_bytes"], ["ex_decode
     try:
         alg = (2.0 + bps) * NS20K
         for nm, ks in (("encode", enc), ("decode", dec)):
-            tot = sum(dram(os.path.join(P, f"{tag}_{m}_{k}_kernels.txt")) for k in ks)
+            # (the Huffman methods' ex_decode is the kernel captured under vbe21_zd)
+            tot = sum(dram(os.path.join(P, f"{tag}_{'vbe21_zd' if k == 'ex_decode' else m}_{k}_kernels.txt")) for k in ks)
             traffic[f"{m}_{nm}"] = {"dram_bytes": tot, "alg_bytes": alg,
                                     "source": f"profiles/{tag}_{m}_*_kernels.txt (ncu --set full, bench.py --method {m} --reads 20000; "
                                               + " + ".join(ks) + ")"}
