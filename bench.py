@@ -69,7 +69,7 @@ def cpu_leg(method: str, nreads: int, p_ex: float, seconds: float, steps: int | 
     """Time the reference's own CPU code (oracle/_ref when it was compiled, else
     the oracle port) on the first `nreads` reads of the same synthetic batch,
     all host threads, per-read bound/press/depress/compare like press/test.c."""
-    from honours_b200 import workload
+    from benchdata import workload
     from oracle import cpu_impl
     kind = "ref" if cpu_impl.available("ref") else "oracle"
     if kind == "oracle" and not cpu_impl.available("oracle"):
@@ -122,7 +122,7 @@ def run_reference(args):
     if rank != 0:
         return
     p_ex = args.p_ex
-    from honours_b200 import workload
+    from benchdata import workload
     if p_ex is None:
         p_ex = workload.P_EX
     r = cpu_leg(args.method, args.cpu_reads, p_ex, args.cpu_seconds, args.steps, args.warmup)
@@ -212,7 +212,8 @@ class ClockSampler:
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from honours_b200 import press, workload
+    from honours_b200 import press
+    from benchdata import workload
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -1,6 +1,9 @@
-// synth.cuh -- synthetic NA12878-like reads (the bench / test workload of
+// synth_core.h -- synthetic NA12878-like reads (the bench / test workload of
 // SURVEY.md 8(d)); integer-only, so the host and device generators agree bit
-// for bit and any shard of a batch can be regenerated anywhere.
+// for bit and any shard of a batch can be regenerated anywhere.  NOT part of the
+// product library: compiled into benchdata/libsynth_gpu.so (nvcc, the device
+// generator) and benchdata/libsynth_host.so (g++ only, the host twin; the CPU
+// reference arm of bench.py loads nothing else besides oracle/).
 //
 //   sample 0 of read r          = x0[r]
 //   sample i >= 1               : h  = mix(key(seed, r) + i * GOLD)
@@ -18,10 +21,16 @@
 // iteration with one warp scan; reads are handed out by an atomic ticket.
 #pragma once
 
-#include "common.cuh"
+#include <stdint.h>
 
 #include <thread>
 #include <vector>
+
+#ifndef __CUDACC__
+#define __host__
+#define __device__
+#define __forceinline__ inline
+#endif
 
 namespace pg {
 
@@ -83,6 +92,7 @@ __host__ __device__ __forceinline__ uint32_t syn_fold(uint32_t m)
 	return m <= 2047u ? m : SYN_PERIOD - m;
 }
 
+#ifdef __CUDACC__
 struct SynthArgs {
 	int16_t *samples;
 	const uint64_t *offsets;
@@ -153,6 +163,8 @@ __global__ void __launch_bounds__(256) synth_kernel(const __grid_constant__ Synt
 		}
 	}
 }
+
+#endif  // __CUDACC__
 
 // Host twin of the kernel: same arithmetic, sample by sample.  The inverse-CDF
 // search is short-cut by a 64 Ki-entry table on the top 16 bits of the draw

@@ -4,10 +4,11 @@ matching the NA12878 median / mean (thesis/plots/n-tab.tex), first samples
 press/gen_huffman.c:11 with exception rate ``p_ex``.
 
 Lengths / first samples / shifts are small per-read tables made here with
-numpy; the samples themselves are generated by libpress_gpu's integer-only
-generator (csrc/synth.cuh), on the device for the bench and on the host for the
-CPU baseline and the tests -- both give identical bits for the same
-(seed, read index).
+numpy; the samples themselves come from the integer-only generator of
+benchdata/synth_core.h, on the device (libsynth_gpu.so) for the bench and on the
+host (libsynth_host.so, no CUDA) for the CPU baseline and the tests -- both give
+identical bits for the same (seed, read index).  Nothing here touches the
+product library.
 """
 from __future__ import annotations
 
@@ -17,8 +18,6 @@ import math
 import os
 
 import numpy as np
-
-from . import press
 
 PKG = os.path.dirname(os.path.abspath(__file__))
 
@@ -34,7 +33,7 @@ SIGMA = math.sqrt(2.0 * (math.log(MEAN_LEN) - MU))
 
 
 def histogram() -> np.ndarray:
-    with open(os.path.join(PKG, "data", "NA12878_zd_hist.json")) as f:
+    with open(os.path.join(PKG, "NA12878_zd_hist.json")) as f:
         return np.asarray(json.load(f)["counts"], dtype=np.uint64)
 
 
@@ -75,14 +74,25 @@ def p_ex_u32(p_ex: float) -> int:
     return min(0xFFFFFFFF, int(round(p_ex * 2.0 ** 32)))
 
 
-def _synth_fns():
-    L = press.lib()
-    vp, u64, u32 = C.c_void_p, C.c_uint64, C.c_uint32
-    L.press_gpu_synth_device.restype = C.c_int
-    L.press_gpu_synth_device.argtypes = [vp, vp, u64, vp, vp, vp, u32, u64, u64, vp]
-    L.press_gpu_synth_host.restype = C.c_int
-    L.press_gpu_synth_host.argtypes = [vp, vp, u64, vp, vp, vp, u32, u64, u64]
-    return L
+_libs: dict[str, C.CDLL] = {}
+
+
+def _lib(which: str) -> C.CDLL:
+    if which not in _libs:
+        p = os.path.join(PKG, f"libsynth_{which}.so")
+        if not os.path.exists(p):
+            from . import build
+            build.build()
+        L = C.CDLL(p)
+        vp, u64, u32 = C.c_void_p, C.c_uint64, C.c_uint32
+        if which == "gpu":
+            L.synth_gpu_device.restype = C.c_int
+            L.synth_gpu_device.argtypes = [vp, vp, u64, vp, vp, vp, u32, u64, u64, vp]
+        else:
+            L.synth_host_fill.restype = C.c_int
+            L.synth_host_fill.argtypes = [vp, vp, u64, vp, vp, vp, u32, u64, u64]
+        _libs[which] = L
+    return _libs[which]
 
 
 def synth_host(offsets: np.ndarray, x0: np.ndarray, shift: np.ndarray | None = None,
@@ -90,26 +100,26 @@ def synth_host(offsets: np.ndarray, x0: np.ndarray, shift: np.ndarray | None = N
     """Samples of the reads described by ``offsets`` (uint64[nreads+1]) on the host.
     ``first_read`` is the batch index of offsets' read 0: read r's samples depend
     only on (seed, first_read + r)."""
-    L = _synth_fns()
+    L = _lib("host")
     offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
     x0 = np.ascontiguousarray(x0, dtype=np.int16)
     sh = None if shift is None else np.ascontiguousarray(shift, dtype=np.uint8)
     hist = histogram()
     out = np.empty(int(offsets[-1]), dtype=np.int16)
-    rc = L.press_gpu_synth_host(out.ctypes.data, offsets.ctypes.data, offsets.size - 1,
+    rc = L.synth_host_fill(out.ctypes.data, offsets.ctypes.data, offsets.size - 1,
                                 x0.ctypes.data, None if sh is None else sh.ctypes.data,
                                 hist.ctypes.data, p_ex_u32(p_ex), seed, first_read)
     if rc != 0:
-        raise press.PressGpuError(press.last_error())
+        raise RuntimeError("synth_host_fill failed")
     return out
 
 
 def synth_device(d_samples: int, d_offsets: int, nreads: int, d_x0: int, d_shift: int | None,
                  p_ex: float = P_EX, seed: int = SEED, first_read: int = 0, stream: int = 0) -> None:
     """Fill device memory (raw pointers) with the same samples synth_host returns."""
-    L = _synth_fns()
+    L = _lib("gpu")
     hist = histogram()
-    rc = L.press_gpu_synth_device(d_samples, d_offsets, nreads, d_x0, d_shift, hist.ctypes.data,
+    rc = L.synth_gpu_device(d_samples, d_offsets, nreads, d_x0, d_shift, hist.ctypes.data,
                                   p_ex_u32(p_ex), seed, first_read, stream)
     if rc != 0:
-        raise press.PressGpuError(press.last_error())
+        raise RuntimeError("synth_gpu_device failed (no CUDA device?)")

@@ -35,7 +35,8 @@ namespace pg {
 constexpr int XT = 4096;		// samples per tile
 constexpr int XG = XT / 8;		// 16-byte groups per tile
 constexpr uint32_t X_FAIL = 0xffffffffu;	// r_hdr of a read that has no stream (empty, ex-zd cap)
-constexpr int X_STAGE = 22 * XT / 8 + 64;	// payload stage: 4096 x 22-bit codes, + phase + slack
+constexpr int X_STAGE = 24 * XT / 8 + 64;	// payload stage: 4096 codes of the longest length accepted
+						// (24 bits, press_gpu_set_huffman_table), + phase + slack
 
 enum : uint32_t { ERR_SCRATCH = 8 };	// exception pool too small (press_gpu_set_exception_capacity)
 

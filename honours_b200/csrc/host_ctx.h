@@ -8,7 +8,7 @@
 namespace pg {
 
 struct ScratchLayout {
-	size_t hdr, status, status2, status_blk, status2_blk, zero_bytes, tile_start, kx, tile_read, extra, total;
+	size_t hdr, status, zero_bytes, tile_start, kx, tile_read, total;
 	// exception-coded methods (exfam.cuh): per-tile / per-read tables, Huffman payload, exception pool
 	size_t x_t[6], x_r[4], x_r8[2], x_paybuf, x_pool, x_pool2;
 	uint64_t x_pool_cap;	// entries

@@ -12,8 +12,7 @@
 namespace pg {
 
 enum PlanTiling : int {
-	TILING_ALIGNED = 0,	// encode: tiles start on 16-byte (8-sample) boundaries of d_samples
-	TILING_READ = 1		// tiles start at multiples of the tile size inside the read
+	TILING_ALIGNED = 0	// tiles start on 16-byte (8-sample) boundaries of d_samples
 };
 
 struct PlanArgs {
@@ -31,7 +30,8 @@ struct PlanArgs {
 
 __device__ __forceinline__ uint32_t plan_tiles(uint64_t off, uint64_t n, int tiling, uint32_t tile)
 {
-	uint64_t span = tiling == TILING_ALIGNED ? (off & 7) + n : n;
+	uint64_t span = (off & 7) + n;
+	(void) tiling;
 	uint64_t t = (span + tile - 1) / tile;
 	return t ? (uint32_t) t : 1u;	// an empty read still owns one (empty) tile
 }

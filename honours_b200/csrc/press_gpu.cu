@@ -21,7 +21,6 @@
 #include "exfam.cuh"
 #include "exfam_dec.cuh"
 #include "svb_dec.cuh"
-#include "synth.cuh"
 #include "host_ctx.h"
 
 using namespace pg;
@@ -96,9 +95,11 @@ int ensure_init()
 // scratch layout -------------------------------------------------------------
 namespace pg {
 
+// upper bound on the tiles of a batch: the svb encoder's 8192-sample tiles (the
+// exception-coded methods size their own 4096-sample tile tables below)
 uint64_t max_tiles(uint64_t nreads, uint64_t nsamples)
 {
-	return nsamples / WT + 2 * nreads + 2;
+	return nsamples / EN_TS + 2 * nreads + 2;
 }
 
 static double default_pool_frac();
@@ -132,9 +133,12 @@ ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples, dou
 		l.x_pool = o;
 		if (pool_frac < 0)
 			pool_frac = default_pool_frac();
+		// (ex-zd reads with q > 0 are captured twice, once per pass of ex_count_kernel, and the
+		//  first capture's space is not given back: its pool may need 2 entries per sample)
+		const uint64_t cap_max = (method == PRESS_GPU_EX_ZD ? 2 : 1) * (nsamples + 1);
 		uint64_t cap = (uint64_t) ((double) nsamples * pool_frac) + 4096;
-		if (cap > nsamples + 1)
-			cap = nsamples + 1;
+		if (cap > cap_max)
+			cap = cap_max;
 		l.x_pool_cap = cap;
 		l.x_pool2 = o + align_up(cap * 8, 256);	// two pools: as captured, and gathered per read
 		o += 2 * align_up(cap * 8, 256);
@@ -142,9 +146,6 @@ ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples, dou
 		return l;
 	}
 	l.status = o;		o += align_up(mt * 8, 256);
-	l.status2 = o;		o += align_up(mt * 8, 256);
-	l.status_blk = o;	o += align_up((mt / 32 + 2) * 8, 256);
-	l.status2_blk = o;	o += align_up((mt / 32 + 2) * 8, 256);
 	l.zero_bytes = o;	// [0, zero_bytes) is cleared before every batch call
 	l.tile_start = o;	o += align_up((nreads + 1) * 4, 256);
 	l.kx = o;		o += align_up((nreads + 1) * 8, 256);
@@ -158,8 +159,9 @@ ScratchLayout scratch_layout_for(int method, uint64_t nreads, uint64_t nsamples,
 	ScratchLayout l = scratch_layout(method, nreads, nsamples, 0.0);
 	if (method >= PRESS_GPU_VBE21_ZD && bytes > l.total) {
 		uint64_t cap = l.x_pool_cap + (bytes - l.total) / 16 / 256 * 256;	// the two pools share what is left
-		if (cap > nsamples + 1)
-			cap = nsamples + 1;
+		const uint64_t cap_max = (method == PRESS_GPU_EX_ZD ? 2 : 1) * (nsamples + 1);
+		if (cap > cap_max)
+			cap = cap_max;
 		l.x_pool_cap = cap;
 		l.x_pool2 = l.x_pool + align_up(cap * 8, 256);
 		l.total = l.x_pool + 2 * align_up(cap * 8, 256);
@@ -355,7 +357,11 @@ int press_gpu_batch_press(int method, const int16_t *d_samples, const uint64_t *
 		set_err("d_samples must be 16-byte and d_scratch 256-byte aligned");
 		return -1;
 	}
-	if (max_tiles(nreads, nsamples) >= (1ull << 32)) {
+	if (l.x_pool_cap >= (1ull << 32)) {
+		set_err("batch too large for the exception pool (positions are 32-bit): split it");
+		return -1;
+	}
+	if (nsamples / 4096 + 2 * nreads + 2 >= (1ull << 32)) {
 		set_err("batch too large: split it (tile ids are 32-bit)");
 		return -1;
 	}
@@ -380,7 +386,6 @@ int press_gpu_batch_press(int method, const int16_t *d_samples, const uint64_t *
 		a.tile_read = reinterpret_cast<const uint32_t *>(scr + l.tile_read);
 		a.kx = reinterpret_cast<const uint64_t *>(scr + l.kx);
 		a.status = reinterpret_cast<uint64_t *>(scr + l.status);
-		a.status_blk = reinterpret_cast<uint64_t *>(scr + l.status_blk);
 		if (!k2 && !frame) return launch_svb_encode<1, false>(a, st);
 		if (!k2 && frame) return launch_svb_encode<1, true>(a, st);
 		if (k2 && !frame) return launch_svb_encode<2, false>(a, st);
@@ -406,11 +411,16 @@ int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_i
 		set_err("scratch too small: %zu < %zu", scratch_bytes, l.total);
 		return -1;
 	}
-	if ((reinterpret_cast<uintptr_t>(d_samples_out) & 15) || (reinterpret_cast<uintptr_t>(d_scratch) & 255)) {
-		set_err("d_samples_out must be 16-byte and d_scratch 256-byte aligned");
+	if ((reinterpret_cast<uintptr_t>(d_samples_out) & 15) || (reinterpret_cast<uintptr_t>(d_in) & 15) ||
+	    (reinterpret_cast<uintptr_t>(d_scratch) & 255)) {
+		set_err("d_samples_out and d_in must be 16-byte and d_scratch 256-byte aligned");
 		return -1;
 	}
-	if (max_tiles(nreads, nsamples) >= (1ull << 32)) {
+	if (l.x_pool_cap >= (1ull << 32)) {
+		set_err("batch too large for the exception pool (positions are 32-bit): split it");
+		return -1;
+	}
+	if (nsamples / 4096 + 2 * nreads + 2 >= (1ull << 32)) {
 		set_err("batch too large: split it (tile ids are 32-bit)");
 		return -1;
 	}
@@ -454,7 +464,8 @@ int press_gpu_batch_status(void *d_scratch, void *stream)
 	return (int) h.error;
 }
 
-/* debug: copy the scratch header's aux words (role timing of -DPG_ROLE_TIMING builds) */
+#if defined(PG_ROLE_TIMING) || defined(PG_DEBUG_AUX)
+/* debug builds only (tools/role_timing.py, tools/debug_huff.py): the scratch header's aux words */
 int press_gpu_debug_aux(void *d_scratch, void *stream, uint64_t out[29])
 {
 	Hdr h;
@@ -465,6 +476,7 @@ int press_gpu_debug_aux(void *d_scratch, void *stream, uint64_t out[29])
 	memcpy(out, h.aux, sizeof h.aux);
 	return 0;
 }
+#endif
 
 void press_gpu_profile_enable(int on) { g_prof = on != 0; }
 
@@ -534,4 +546,3 @@ void press_gpu_host_free(void *p)
 }  // extern "C"
 
 #include "host_paths.inc"
-#include "synth_host.inc"

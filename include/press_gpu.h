@@ -68,6 +68,11 @@ uint64_t svb12_zd_gpu_bound(uint64_t nin);
 void svb12_zd_gpu_press(const int16_t *in, uint64_t nin, uint8_t *out, uint64_t *nout);
 void svb12_zd_gpu_depress(const uint8_t *in, uint64_t nin, int16_t *out, uint64_t *nout);
 
+/* scalar twin of the above: press.h:340-344 (press.c:1647-1674).  Same bytes, same kernels. */
+uint64_t svb12_zd_nosimd_gpu_bound(uint64_t nin);
+void svb12_zd_nosimd_gpu_press(const int16_t *in, uint64_t nin, uint8_t *out, uint64_t *nout);
+void svb12_zd_nosimd_gpu_depress(const uint8_t *in, uint64_t nin, int16_t *out, uint64_t *nout);
+
 /* classical svb-zd: press.h:322-328 (press.c:1585-1612).  depress nin = SAMPLES. */
 uint64_t svb_zd_gpu_bound_16(uint64_t nin);
 void svb_zd_gpu_press_16(const int16_t *in, uint64_t nin, uint8_t *out, uint64_t *nout);
@@ -103,10 +108,28 @@ uint64_t hasgam_vbsse21_zdq_gpu_bound_16(uint32_t nin);
 int hasgam_vbsse21_zdq_gpu_press_16(const int16_t *in, uint32_t nin, uint8_t *out, uint64_t *nout);
 int hasgam_vbsse21_zdq_gpu_depress_16(uint8_t *in, uint64_t nin, int16_t *out, uint32_t *nout);
 
-/* static-Huffman-zd: press.h:632-638 (press.c:4409-4498).  The reference
- * passes SymbolEncoder* / huffman_node*; here the first argument is an opaque
- * table handle: NULL selects the table installed by press_gpu_set_huffman_table.
+/* static-Huffman-zd: press.h:632-638 (press.c:4409-4498).  The first argument is what the
+ * reference passes: press takes the caller's `SymbolEncoder *` (huffman.h:50, built by
+ * build_symbol_encoder, test.c:3786-3791), depress the caller's `huffman_node *` tree root
+ * (read_code_table, huffman.c:549).  The device tables are derived from those structures
+ * once per distinct pointer (layout mirrors below); NULL selects the table installed by
+ * press_gpu_set_huffman_table.  The code must cover all 256 symbols with codes of <= 24 bits.
  * depress: *nout = expected sample count on entry (press.c:4472).  0 ok / 1 error. */
+typedef struct press_gpu_huffman_node {		/* == huffman_node, huffman/huffman.h:22-37 */
+	unsigned char isLeaf;
+	unsigned long count;
+	struct press_gpu_huffman_node *parent;
+	union {
+		struct {
+			struct press_gpu_huffman_node *zero, *one;
+		};
+		unsigned char symbol;
+	};
+} press_gpu_huffman_node;
+typedef struct press_gpu_huffman_code {		/* == huffman_code, huffman/huffman.h:38-48 */
+	unsigned long numbits;
+	unsigned char *bits;	/* bit k of the code at bit k % 8 of bits[k / 8] */
+} press_gpu_huffman_code;
 uint64_t shuffman_vbe21_zd_gpu_bound_16(uint32_t nin);
 int shuffman_vbe21_zd_gpu_press_16(const void *table, const int16_t *in, uint32_t nin,
 				   uint8_t *out, uint64_t *nout);
@@ -206,19 +229,6 @@ int press_gpu_profile_collect(double ms[2], uint64_t launches[2]);
 /* pinned host memory for the host-buffer path (cudaHostAlloc / cudaFreeHost) */
 void *press_gpu_host_alloc(size_t bytes);
 void press_gpu_host_free(void *p);
-
-/* ---- synthetic NA12878-like reads (bench / test workload generator) -------
- * Deterministic, integer-only, identical on host and device: the samples of
- * read r depend only on (seed, first_read + r), so shards of one batch agree.  d_/h_ variants fill samples for reads
- * whose lengths are given by offsets; x0[r] is the first sample, shift[r] the
- * left shift applied to every sample (0 normally; 2 gives q = 2 reads).
- * p_ex_u32 = exception probability * 2^32.  hist = 256 one-byte-zd counts. */
-int press_gpu_synth_device(int16_t *d_samples, const uint64_t *d_offsets, uint64_t nreads,
-			   const int16_t *d_x0, const uint8_t *d_shift, const uint64_t *hist256,
-			   uint32_t p_ex_u32, uint64_t seed, uint64_t first_read, void *stream);
-int press_gpu_synth_host(int16_t *h_samples, const uint64_t *h_offsets, uint64_t nreads,
-			 const int16_t *h_x0, const uint8_t *h_shift, const uint64_t *hist256,
-			 uint32_t p_ex_u32, uint64_t seed, uint64_t first_read);
 
 #ifdef __cplusplus
 }

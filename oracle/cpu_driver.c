@@ -139,3 +139,94 @@ int FN(run_batch)(int method, const int16_t *samples, const uint64_t *offsets,
 	free(jobs);
 	return res[3] == 0 && res[4] == 0 ? 0 : -1;
 }
+
+/* ---- per-read fingerprints (FNV-1a-64, the fingerprint of SURVEY.md 8(c)) ----------------
+ * hash_batch: every read of the batch pressed by this implementation, hashes[r] = FNV-1a-64
+ * of its stream, sizes[r] = its length (0 and hash of nothing when press fails).
+ * hash_slices: the same fingerprint of slices [oo[r], oo[r + 1]) of a container somebody
+ * else wrote (the GPU).  Both split the reads over T threads by sample / byte count, so a
+ * whole bench-scale chunk is compared byte for byte in seconds. */
+static uint64_t fnv1a64(const uint8_t *p, uint64_t n)
+{
+	uint64_t h = 0xCBF29CE484222325ull;
+	for (uint64_t i = 0; i < n; i++)
+		h = (h ^ p[i]) * 0x100000001B3ull;
+	return h;
+}
+
+struct hjob {
+	int method;
+	const int16_t *samples;
+	const uint8_t *buf;
+	const uint64_t *offsets;
+	uint64_t r0, r1;
+	uint64_t *hashes, *sizes;
+};
+
+static void *hash_press_worker(void *arg)
+{
+	struct hjob *j = arg;
+	for (uint64_t r = j->r0; r < j->r1; r++) {
+		uint64_t n = j->offsets[r + 1] - j->offsets[r];
+		uint64_t cap = FN(bound)(j->method, n) + 8 * n + 64;
+		uint8_t *out = malloc(cap);
+		uint64_t nout = cap;
+		if (!out || n == 0 || FN(press)(j->method, j->samples + j->offsets[r], n, out, &nout))
+			nout = 0;
+		j->hashes[r] = fnv1a64(out, nout);
+		j->sizes[r] = nout;
+		free(out);
+	}
+	return NULL;
+}
+
+static void *hash_slice_worker(void *arg)
+{
+	struct hjob *j = arg;
+	for (uint64_t r = j->r0; r < j->r1; r++)
+		j->hashes[r] = fnv1a64(j->buf + j->offsets[r], j->offsets[r + 1] - j->offsets[r]);
+	return NULL;
+}
+
+static int hash_run(struct hjob proto, uint64_t nreads, int nthreads, void *(*fn)(void *))
+{
+	if (nthreads < 1)
+		nthreads = 1;
+	if ((uint64_t) nthreads > nreads && nreads)
+		nthreads = (int) nreads;
+	pthread_t *tid = calloc(nthreads, sizeof *tid);
+	struct hjob *jobs = calloc(nthreads, sizeof *jobs);
+	const uint64_t *o = proto.offsets;
+	uint64_t total = o[nreads] - o[0], r = 0;
+	for (int t = 0; t < nthreads; t++) {
+		uint64_t goal = o[0] + total / nthreads * (t + 1);
+		jobs[t] = proto;
+		jobs[t].r0 = r;
+		if (t == nthreads - 1)
+			r = nreads;
+		else
+			while (r < nreads && o[r + 1] <= goal)
+				r++;
+		jobs[t].r1 = r;
+		pthread_create(&tid[t], NULL, fn, &jobs[t]);
+	}
+	for (int t = 0; t < nthreads; t++)
+		pthread_join(tid[t], NULL);
+	free(tid);
+	free(jobs);
+	return 0;
+}
+
+int FN(hash_batch)(int method, const int16_t *samples, const uint64_t *offsets, uint64_t nreads,
+		   int nthreads, uint64_t *hashes, uint64_t *sizes)
+{
+	struct hjob p = {method, samples, NULL, offsets, 0, 0, hashes, sizes};
+	return hash_run(p, nreads, nthreads, hash_press_worker);
+}
+
+int FN(hash_slices)(const uint8_t *buf, const uint64_t *oo, uint64_t nreads, int nthreads,
+		    uint64_t *hashes)
+{
+	struct hjob p = {0, NULL, buf, oo, 0, 0, hashes, NULL};
+	return hash_run(p, nreads, nthreads, hash_slice_worker);
+}

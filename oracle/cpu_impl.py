@@ -112,6 +112,28 @@ class CpuImpl:
                            out.ctypes.data_as(_i16p), C.byref(nout))
         return rc, out[: nout.value].copy()
 
+    def nosimd_press(self, sig: np.ndarray) -> bytes:
+        """svb12_zd_nosimd_press (press.c:1655-1662), reference build only."""
+        sig = np.ascontiguousarray(sig, dtype=np.int16)
+        self.lib.ref_nosimd_bound.restype = C.c_uint64
+        self.lib.ref_nosimd_bound.argtypes = [C.c_uint64]
+        cap = int(self.lib.ref_nosimd_bound(sig.size)) + 64
+        out = np.zeros(cap, dtype=np.uint8)
+        nout = C.c_uint64(cap)
+        self.lib.ref_nosimd_press.argtypes = [_i16p, C.c_uint64, _u8p, _u64p]
+        self.lib.ref_nosimd_press(sig.ctypes.data_as(_i16p), sig.size, out.ctypes.data_as(_u8p), C.byref(nout))
+        return out[: nout.value].tobytes()
+
+    def nosimd_depress(self, stream: bytes, n: int) -> np.ndarray:
+        """svb12_zd_nosimd_depress (press.c:1664-1674), reference build only."""
+        buf = np.zeros(len(stream) + 64, dtype=np.uint8)
+        buf[: len(stream)] = np.frombuffer(stream, dtype=np.uint8)
+        out = np.zeros(n + 64, dtype=np.int16)
+        nout = C.c_uint64(n)
+        self.lib.ref_nosimd_depress.argtypes = [_u8p, C.c_uint64, _i16p, _u64p]
+        self.lib.ref_nosimd_depress(buf.ctypes.data_as(_u8p), n, out.ctypes.data_as(_i16p), C.byref(nout))
+        return out[: nout.value].copy()
+
     def run_batch(self, method: str, samples: np.ndarray, offsets: np.ndarray,
                   threads: int = 1) -> dict:
         """press/test.c-style loop over the reads; wall-clock seconds per phase."""
@@ -123,6 +145,39 @@ class CpuImpl:
         return {"rc": rc, "press_s": res[0], "depress_s": res[1],
                 "bytes": int(res[2]), "mismatches": int(res[3]), "errors": int(res[4])}
 
+
+def _hash_batch(self, method: str, samples: np.ndarray, offsets: np.ndarray, threads: int = 0):
+    """-> (hashes uint64[nreads], sizes uint64[nreads]): FNV-1a-64 and length of every read's
+    stream as this implementation writes it (size 0: press failed or empty read)."""
+    samples = np.ascontiguousarray(samples, dtype=np.int16)
+    offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+    nreads = offsets.size - 1
+    hashes = np.zeros(nreads, dtype=np.uint64)
+    sizes = np.zeros(nreads, dtype=np.uint64)
+    f = getattr(self.lib, f"{self.kind}_hash_batch")
+    f.restype = C.c_int
+    f.argtypes = [C.c_int, _i16p, _u64p, C.c_uint64, C.c_int, _u64p, _u64p]
+    f(METHODS[method], samples.ctypes.data_as(_i16p), offsets.ctypes.data_as(_u64p), nreads,
+      threads or (os.cpu_count() or 1), hashes.ctypes.data_as(_u64p), sizes.ctypes.data_as(_u64p))
+    return hashes, sizes
+
+
+def _hash_slices(self, container: np.ndarray, oo: np.ndarray, threads: int = 0) -> np.ndarray:
+    """FNV-1a-64 of container[oo[r]:oo[r + 1]] for every r."""
+    container = np.ascontiguousarray(container, dtype=np.uint8)
+    oo = np.ascontiguousarray(oo, dtype=np.uint64)
+    nreads = oo.size - 1
+    hashes = np.zeros(nreads, dtype=np.uint64)
+    f = getattr(self.lib, f"{self.kind}_hash_slices")
+    f.restype = C.c_int
+    f.argtypes = [_u8p, _u64p, C.c_uint64, C.c_int, _u64p]
+    f(container.ctypes.data_as(_u8p), oo.ctypes.data_as(_u64p), nreads, threads or (os.cpu_count() or 1),
+      hashes.ctypes.data_as(_u64p))
+    return hashes
+
+
+CpuImpl.hash_batch = _hash_batch
+CpuImpl.hash_slices = _hash_slices
 
 _cache: dict[str, CpuImpl] = {}
 

@@ -152,3 +152,18 @@ int ref_depress(int method, const uint8_t *in, uint64_t nbytes, uint64_t n,
 	*nout = n32;
 	return r;
 }
+
+/* a5 pin: the scalar twin svb12_zd_nosimd_* (press.c:1647-1674 ->
+ * streamvbyte_12_encode.c:90-110) called directly, so a committed test can assert that it
+ * writes the same bytes as the SIMD svb12_zd_* path and as the GPU. */
+uint64_t ref_nosimd_bound(uint64_t n) { return svb12_zd_nosimd_bound(n); }
+int ref_nosimd_press(const int16_t *in, uint64_t n, uint8_t *out, uint64_t *nout)
+{
+	svb12_zd_nosimd_press(in, n, out, nout);
+	return 0;
+}
+int ref_nosimd_depress(const uint8_t *in, uint64_t n, int16_t *out, uint64_t *nout)
+{
+	svb12_zd_nosimd_depress(in, n, out, nout);
+	return 0;
+}

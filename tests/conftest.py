@@ -32,3 +32,16 @@ def ref():
     r = cpu_impl.load("ref")
     r.set_huffman_table(open(os.path.join(ROOT, "honours_b200", "data", "NA12878_zd.huffman"), "rb").read())
     return r
+
+
+@pytest.fixture(scope="session")
+def checker(oracle):
+    """The strongest CPU checker present: the reference's own code compiled in place
+    (oracle/_ref/libpress_ref.so -- it travels to the GPU box) when it exists, else the
+    restatement (which tests/test_oracle.py pins to it byte for byte)."""
+    from oracle import cpu_impl
+    if cpu_impl.available("ref"):
+        r = cpu_impl.load("ref")
+        r.set_huffman_table(open(os.path.join(ROOT, "honours_b200", "data", "NA12878_zd.huffman"), "rb").read())
+        return r
+    return oracle

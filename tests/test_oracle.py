@@ -136,6 +136,37 @@ def test_oracle_matches_compiled_reference_random(oracle, ref, method):
         assert rc == 0 and np.array_equal(a, s), (method, kind, n)
 
 
+def test_scalar_twin_nosimd_equals_simd(oracle, ref):
+    """svb12_zd_nosimd_* (press.c:1647-1674, scalar streamvbyte_encode_12)
+    writes the bytes svb12_zd_* (SSE svb16) writes, and both equal the restatement; each decodes
+    the other's stream."""
+    rng = np.random.default_rng(4321)
+    for trial in range(80):
+        kind = ["walk", "spiky", "q", "noise"][trial % 4]
+        n = int(rng.integers(1, 9000)) if trial % 5 else int(rng.integers(1, 40))
+        s = _random_read(rng, kind, n)
+        scalar = ref.nosimd_press(s)
+        rc, simd = ref.press("svb16_zd", s)
+        assert rc == 0 and scalar == simd == oracle.press("svb16_zd", s)[1], (kind, n)
+        assert np.array_equal(ref.nosimd_depress(simd, n), s)
+        rc, back = ref.depress("svb16_zd", scalar, n)
+        assert rc == 0 and np.array_equal(back, s)
+
+
+def test_hash_batch_matches_per_read_hashes(oracle, ref, three_reads):
+    """the multi-threaded fingerprint used by the bench-scale GPU parity test"""
+    samples, offsets, _ = three_reads
+    for impl in (oracle, ref):
+        for m in ("svb16_zd", "ex_zd", "shuff_vbe21_zd"):
+            h, sz = impl.hash_batch(m, samples, offsets, threads=3)
+            streams = [impl.press(m, samples[int(offsets[r]):int(offsets[r + 1])])[1] for r in range(3)]
+            assert sz.tolist() == [len(x) for x in streams]
+            assert h.tolist() == [cpu_impl.fnv1a64(x) for x in streams]
+            oo = np.concatenate([[0], np.cumsum([len(x) for x in streams])]).astype(np.uint64)
+            cont = np.frombuffer(b"".join(streams), dtype=np.uint8)
+            assert impl.hash_slices(cont, oo, threads=2).tolist() == h.tolist()
+
+
 def test_building_blocks(oracle):
     import ctypes as C
     lib = oracle.lib

@@ -2,7 +2,8 @@
 import ctypes as C, sys, time
 import numpy as np, torch
 sys.path.insert(0, ".")
-from honours_b200 import press, workload
+from honours_b200 import press
+from benchdata import workload
 press.init(0); press.set_huffman_table()
 nreads = int(sys.argv[1]) if len(sys.argv) > 1 else 5000
 dev = torch.device("cuda:0")

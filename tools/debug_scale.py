@@ -2,7 +2,8 @@
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
-from honours_b200 import press, workload
+from honours_b200 import press
+from benchdata import workload
 
 def run(nreads, method="svb16_zd"):
     dev = torch.device("cuda:0")

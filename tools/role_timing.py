@@ -8,7 +8,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 import torch
 
-from honours_b200 import press, workload
+from honours_b200 import press
+from benchdata import workload
 
 method = sys.argv[1] if len(sys.argv) > 1 else "svb16_zd"
 nreads = int(sys.argv[2]) if len(sys.argv) > 2 else 20000
