@@ -88,6 +88,8 @@ def _lib(which: str) -> C.CDLL:
         if which == "gpu":
             L.synth_gpu_device.restype = C.c_int
             L.synth_gpu_device.argtypes = [vp, vp, u64, vp, vp, vp, u32, u64, u64, vp]
+            L.bench_link_probe.restype = C.c_int
+            L.bench_link_probe.argtypes = [C.c_size_t, C.c_size_t, C.c_int, C.POINTER(C.c_double)]
         else:
             L.synth_host_fill.restype = C.c_int
             L.synth_host_fill.argtypes = [vp, vp, u64, vp, vp, vp, u32, u64, u64]
@@ -123,3 +125,13 @@ def synth_device(d_samples: int, d_offsets: int, nreads: int, d_x0: int, d_shift
                                   p_ex_u32(p_ex), seed, first_read, stream)
     if rc != 0:
         raise RuntimeError("synth_gpu_device failed (no CUDA device?)")
+
+
+def link_probe(total_bytes: int = 1 << 30, chunk_bytes: int = 64 << 20, reps: int = 3) -> dict:
+    """Plain pinned cudaMemcpyAsync bandwidth of this process's GPU (GB/s): each direction alone
+    and both at once -- the ceiling the host-buffer (e2e) path is measured against."""
+    out = (C.c_double * 4)()
+    if _lib("gpu").bench_link_probe(total_bytes, chunk_bytes, reps, out) != 0:
+        raise RuntimeError("bench_link_probe failed")
+    return {"h2d_gbs": out[0], "d2h_gbs": out[1], "h2d_duplex_gbs": out[2], "d2h_duplex_gbs": out[3],
+            "bytes": total_bytes, "chunk_bytes": chunk_bytes, "reps": reps}

@@ -94,11 +94,14 @@ struct HostCtx {
 	int sms = 0;
 	cudaStream_t stream = nullptr;
 	GrowBuf samples, offsets, out, out_offsets, scratch, misc;
-	PipeSlot slot[PIPE_SLOTS];
+	PipeSlot slot[2][PIPE_SLOTS];	// [0]: press_host pipeline, [1]: depress_host pipeline -- one thread may
+					// compress a batch while another decompresses an earlier one (full duplex link)
 	void release()
 	{
-		for (int i = 0; i < PIPE_SLOTS; i++)
-			slot[i].release();
+		for (int i = 0; i < PIPE_SLOTS; i++) {
+			slot[0][i].release();
+			slot[1][i].release();
+		}
 		samples.release();
 		offsets.release();
 		out.release();

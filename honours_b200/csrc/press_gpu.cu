@@ -11,6 +11,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
 #include <mutex>
 #include <vector>
 
@@ -31,7 +32,7 @@ using namespace pg;
 namespace {
 
 char g_err[512] = "";
-uint64_t g_launches = 0;
+std::atomic<uint64_t> g_launches{0};
 std::once_flag g_once;
 HostCtx g_ctx;
 
@@ -211,7 +212,7 @@ void press_gpu_shutdown(void)
 
 const char *press_gpu_last_error(void) { return g_err; }
 const char *press_gpu_version(void) { return "press_gpu 0.1 sm_100a"; }
-uint64_t press_gpu_launch_count(void) { return g_launches; }
+uint64_t press_gpu_launch_count(void) { return g_launches.load(); }
 int press_gpu_method_implemented(int method)
 {
 	return method >= PRESS_GPU_SVB16_ZD && method < PRESS_GPU_NMETHODS;
@@ -333,6 +334,10 @@ bool is_svb(int m) { return m >= PRESS_GPU_SVB16_ZD && m <= PRESS_GPU_VBZ_SVB_ZD
 
 }  // namespace
 
+// side-car of the call in progress (press_gpu_batch_*_sidecar; null: none).  thread_local: the
+// host-buffer pipelines of two threads never see each other's.
+thread_local uint8_t *g_sidecar = nullptr;
+
 #include "ex_host.inc"
 
 namespace pg {
@@ -450,6 +455,46 @@ int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_i
 	return -1;
 }
 
+size_t press_gpu_sidecar_bytes(int method, uint64_t nreads, uint64_t nsamples)
+{
+	return ex_sidecar_bytes(method, nreads, nsamples);
+}
+
+int press_gpu_batch_press_sidecar(int method, const int16_t *d_samples, const uint64_t *d_offsets,
+				  uint64_t nreads, uint64_t nsamples, uint8_t *d_out, uint64_t out_capacity,
+				  uint64_t *d_out_offsets, void *d_scratch, size_t scratch_bytes,
+				  uint8_t *d_sidecar, size_t sidecar_bytes, void *stream)
+{
+	if (d_sidecar && (sidecar_bytes < ex_sidecar_bytes(method, nreads, nsamples) ||
+			  (reinterpret_cast<uintptr_t>(d_sidecar) & 15))) {
+		set_err("side-car buffer too small or not 16-byte aligned (press_gpu_sidecar_bytes)");
+		return -1;
+	}
+	g_sidecar = ex_sidecar_bytes(method, nreads, nsamples) ? d_sidecar : nullptr;
+	const int rc = press_gpu_batch_press(method, d_samples, d_offsets, nreads, nsamples, d_out, out_capacity,
+					     d_out_offsets, d_scratch, scratch_bytes, stream);
+	g_sidecar = nullptr;
+	return rc;
+}
+
+int press_gpu_batch_depress_sidecar(int method, const uint8_t *d_in, const uint64_t *d_in_offsets,
+				    uint64_t in_bytes, const uint64_t *d_offsets, uint64_t nreads,
+				    uint64_t nsamples, int16_t *d_samples_out, void *d_scratch,
+				    size_t scratch_bytes, const uint8_t *d_sidecar, size_t sidecar_bytes,
+				    void *stream)
+{
+	if (d_sidecar && (sidecar_bytes < ex_sidecar_bytes(method, nreads, nsamples) ||
+			  (reinterpret_cast<uintptr_t>(d_sidecar) & 15))) {
+		set_err("side-car buffer too small or not 16-byte aligned (press_gpu_sidecar_bytes)");
+		return -1;
+	}
+	g_sidecar = ex_sidecar_bytes(method, nreads, nsamples) ? const_cast<uint8_t *>(d_sidecar) : nullptr;
+	const int rc = press_gpu_batch_depress(method, d_in, d_in_offsets, in_bytes, d_offsets, nreads, nsamples,
+					       d_samples_out, d_scratch, scratch_bytes, stream);
+	g_sidecar = nullptr;
+	return rc;
+}
+
 int press_gpu_batch_status(void *d_scratch, void *stream)
 {
 	if (ensure_init())
@@ -546,3 +591,4 @@ void press_gpu_host_free(void *p)
 }  // extern "C"
 
 #include "host_paths.inc"
+#include "comm.inc"

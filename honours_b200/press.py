@@ -89,6 +89,12 @@ def lib() -> C.CDLL:
         L.press_gpu_batch_press.argtypes = [i32, vp, vp, u64, u64, vp, u64, vp, vp, sz, vp]
         L.press_gpu_batch_depress.restype = i32
         L.press_gpu_batch_depress.argtypes = [i32, vp, vp, u64, vp, u64, u64, vp, vp, sz, vp]
+        L.press_gpu_sidecar_bytes.restype = sz
+        L.press_gpu_sidecar_bytes.argtypes = [i32, u64, u64]
+        L.press_gpu_batch_press_sidecar.restype = i32
+        L.press_gpu_batch_press_sidecar.argtypes = [i32, vp, vp, u64, u64, vp, u64, vp, vp, sz, vp, sz, vp]
+        L.press_gpu_batch_depress_sidecar.restype = i32
+        L.press_gpu_batch_depress_sidecar.argtypes = [i32, vp, vp, u64, vp, u64, u64, vp, vp, sz, vp, sz, vp]
         L.press_gpu_batch_status.restype = i32
         L.press_gpu_batch_status.argtypes = [vp, vp]
         L.press_gpu_batch_press_host.restype = i32
@@ -97,6 +103,13 @@ def lib() -> C.CDLL:
         L.press_gpu_batch_depress_host.argtypes = [i32, vp, vp, vp, u64, vp]
         L.press_gpu_global_offsets.restype = i32
         L.press_gpu_global_offsets.argtypes = [vp, i32, u64, vp, vp]
+        L.press_gpu_comm_unique_id.restype = i32
+        L.press_gpu_comm_unique_id.argtypes = [vp]
+        L.press_gpu_comm_init.restype = i32
+        L.press_gpu_comm_init.argtypes = [vp, i32, i32]
+        L.press_gpu_comm_destroy.restype = None
+        L.press_gpu_allgather_offsets.restype = i32
+        L.press_gpu_allgather_offsets.argtypes = [vp, u64, vp, vp, vp]
         L.press_gpu_profile_enable.restype = None
         L.press_gpu_profile_enable.argtypes = [i32]
         L.press_gpu_profile_collect.restype = i32
@@ -222,9 +235,21 @@ def batch_scratch_bytes(method: str, nreads: int, nsamples: int) -> int:
     return int(lib().press_gpu_batch_scratch_bytes(METHODS[method], nreads, nsamples))
 
 
+def sidecar_bytes(method: str, nreads: int, nsamples: int) -> int:
+    """Bytes of the optional decode side-car of `method` for a batch (0: the method has none)."""
+    return int(lib().press_gpu_sidecar_bytes(METHODS[method], nreads, nsamples))
+
+
 def batch_press(method: str, d_samples: int, d_offsets: int, nreads: int, nsamples: int,
                 d_out: int, out_capacity: int, d_out_offsets: int, d_scratch: int,
-                scratch_bytes: int, stream: int = 0) -> None:
+                scratch_bytes: int, stream: int = 0, sidecar: int = 0, sidecar_bytes: int = 0) -> None:
+    if sidecar:
+        rc = lib().press_gpu_batch_press_sidecar(METHODS[method], d_samples, d_offsets, nreads, nsamples,
+                                                 d_out, out_capacity, d_out_offsets, d_scratch,
+                                                 scratch_bytes, sidecar, sidecar_bytes, stream)
+        if rc != 0:
+            raise PressGpuError(last_error())
+        return
     rc = lib().press_gpu_batch_press(METHODS[method], d_samples, d_offsets, nreads, nsamples,
                                      d_out, out_capacity, d_out_offsets, d_scratch,
                                      scratch_bytes, stream)
@@ -234,7 +259,14 @@ def batch_press(method: str, d_samples: int, d_offsets: int, nreads: int, nsampl
 
 def batch_depress(method: str, d_in: int, d_in_offsets: int, in_bytes: int, d_offsets: int,
                   nreads: int, nsamples: int, d_samples_out: int, d_scratch: int,
-                  scratch_bytes: int, stream: int = 0) -> None:
+                  scratch_bytes: int, stream: int = 0, sidecar: int = 0, sidecar_bytes: int = 0) -> None:
+    if sidecar:
+        rc = lib().press_gpu_batch_depress_sidecar(METHODS[method], d_in, d_in_offsets, in_bytes, d_offsets,
+                                                   nreads, nsamples, d_samples_out, d_scratch,
+                                                   scratch_bytes, sidecar, sidecar_bytes, stream)
+        if rc != 0:
+            raise PressGpuError(last_error())
+        return
     rc = lib().press_gpu_batch_depress(METHODS[method], d_in, d_in_offsets, in_bytes, d_offsets,
                                        nreads, nsamples, d_samples_out, d_scratch,
                                        scratch_bytes, stream)
@@ -279,6 +311,30 @@ def batch_depress_host(method: str, container: np.ndarray, in_offsets: np.ndarra
 
 def global_offsets(d_gathered: int, nranks: int, nreads: int, d_global: int, stream: int = 0) -> None:
     if lib().press_gpu_global_offsets(d_gathered, nranks, nreads, d_global, stream) != 0:
+        raise PressGpuError(last_error())
+
+
+def comm_unique_id() -> bytes:
+    buf = (C.c_uint8 * 128)()
+    if lib().press_gpu_comm_unique_id(buf) != 0:
+        raise PressGpuError(last_error())
+    return bytes(buf)
+
+
+def comm_init(uid: bytes, rank: int, nranks: int) -> None:
+    buf = (C.c_uint8 * 128).from_buffer_copy(uid)
+    if lib().press_gpu_comm_init(buf, rank, nranks) != 0:
+        raise PressGpuError(last_error())
+
+
+def comm_destroy() -> None:
+    lib().press_gpu_comm_destroy()
+
+
+def allgather_offsets(d_out_offsets: int, nreads: int, d_gathered: int, d_global: int, stream: int = 0) -> None:
+    """The path's one exchange through the C ABI: ncclAllGather of the per-read byte positions +
+    the container index (press_gpu_global_offsets) on the same stream."""
+    if lib().press_gpu_allgather_offsets(d_out_offsets, nreads, d_gathered, d_global, stream) != 0:
         raise PressGpuError(last_error())
 
 

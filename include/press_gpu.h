@@ -187,6 +187,28 @@ int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_i
 			    uint64_t nsamples, int16_t *d_samples_out, void *d_scratch,
 			    size_t scratch_bytes, void *stream);
 
+/* Decode side-car of the static-Huffman methods (7, 8, 10).  The reference's Huffman stream
+ * (huffman.c:1199-1209: a symbol count, then codes back to back) has no entry points for a
+ * parallel decoder, so press_gpu_batch_depress decodes it self-synchronising, speculatively.
+ * When the stream was written HERE, press can also leave, OUTSIDE the container (its bytes stay
+ * exactly the reference's), one uint16 per 32 payload symbols: the low 16 bits of that symbol's
+ * bit offset in the read's bitstream; entries of read r start at index (offsets[r] >> 5) + r.
+ * depress with the side-car decodes every 32-symbol group independently and in one fused kernel
+ * (bits -> samples), and reports status bit 1 if the side-car does not match the stream.
+ * press_gpu_sidecar_bytes() = bytes to provide (0: the method has no side-car, the pointer is
+ * ignored); d_sidecar = NULL selects the plain calls' behaviour. */
+size_t press_gpu_sidecar_bytes(int method, uint64_t nreads, uint64_t nsamples);
+int press_gpu_batch_press_sidecar(int method, const int16_t *d_samples, const uint64_t *d_offsets,
+				  uint64_t nreads, uint64_t nsamples, uint8_t *d_out,
+				  uint64_t out_capacity, uint64_t *d_out_offsets, void *d_scratch,
+				  size_t scratch_bytes, uint8_t *d_sidecar, size_t sidecar_bytes,
+				  void *stream);
+int press_gpu_batch_depress_sidecar(int method, const uint8_t *d_in, const uint64_t *d_in_offsets,
+				    uint64_t in_bytes, const uint64_t *d_offsets, uint64_t nreads,
+				    uint64_t nsamples, int16_t *d_samples_out, void *d_scratch,
+				    size_t scratch_bytes, const uint8_t *d_sidecar, size_t sidecar_bytes,
+				    void *stream);
+
 /* The exception-coded methods (4-7) collect the values > 255 in a pool inside
  * d_scratch.  Its size is `entries_per_sample` x nsamples + 4096 entries of 8
  * bytes (default 1/64; NA12878 signal has 4.3e-5 exceptions per sample;
@@ -218,6 +240,23 @@ int press_gpu_batch_depress_host(int method, const uint8_t *h_in, const uint64_t
  * d_global[k * nreads + r], total bytes in d_global[nranks * nreads]. */
 int press_gpu_global_offsets(const uint64_t *d_gathered, int nranks, uint64_t nreads,
 			     uint64_t *d_global, void *stream);
+
+/* Multi-GPU driver, one process per GPU.  Rank 0 makes an id
+ * (press_gpu_comm_unique_id) and hands the 128 bytes to the other ranks by any means (MPI, a
+ * file, torch.distributed ...); every rank then calls press_gpu_comm_init(id, rank, nranks)
+ * after press_gpu_init.  press_gpu_allgather_offsets enqueues, on `stream`, the path's one
+ * exchange -- ncclAllGather of this rank's d_out_offsets[nreads + 1] (every rank passes the same
+ * nreads: shards with fewer reads pad d_out_offsets with their total) into
+ * d_gathered[nranks][nreads + 1] -- and press_gpu_global_offsets on the result (d_global as
+ * above).  NCCL is bound at run time (libnccl.so.2); no call here is needed on one GPU. */
+#define PRESS_GPU_COMM_ID_BYTES 128
+int press_gpu_comm_unique_id(uint8_t id[PRESS_GPU_COMM_ID_BYTES]);
+int press_gpu_comm_init(const uint8_t id[PRESS_GPU_COMM_ID_BYTES], int rank, int nranks);
+void press_gpu_comm_destroy(void);
+int press_gpu_comm_size(void);
+int press_gpu_comm_rank(void);
+int press_gpu_allgather_offsets(const uint64_t *d_out_offsets, uint64_t nreads, uint64_t *d_gathered,
+				uint64_t *d_global, void *stream);
 
 /* Kernel timing for bench.py's roofline: when enabled every main codec kernel
  * launch is bracketed by CUDA events on its stream.  collect() waits for them

@@ -317,6 +317,52 @@ def test_huffman_custom_tables(gpu, oracle, shape):
         gpu.set_huffman_table(na12878)
 
 
+def test_huffman_tile_of_longest_24bit_codes(gpu, oracle):
+    """a table whose longest code has 24 bits (the longest accepted) and reads made of
+    that symbol alone: 4096-sample tiles of 24-bit codes must fit the encoder's stage."""
+    freq = [2.0 ** -min(k, 23) + 1e-9 * (256 - k) for k in range(256)]
+    blob, lens = _huffman_table_blob(freq)
+    assert max(lens) == 24
+    sym = max(range(256), key=lambda s: (lens[s], s))       # a one-byte zd value with a 24-bit code
+    delta = (sym >> 1) ^ -(sym & 1)                         # unzigzag
+    na12878 = open(os.path.join(os.path.dirname(GOLD), "..", "honours_b200", "data", "NA12878_zd.huffman"), "rb").read()
+    try:
+        oracle.set_huffman_table(blob)
+        gpu.set_huffman_table(blob)
+        for n in (4097, 20000):
+            s = (np.arange(n, dtype=np.int64) * delta).astype(np.int16)
+            ro, so = oracle.press("shuff_vbe21_zd", s)
+            rc, st = gpu.press("shuff_vbe21_zd", s)
+            assert ro == rc == 0 and st == so and len(st) > 3 * (n - 1) - 8
+            rc, back = gpu.depress("shuff_vbe21_zd", so, n)
+            assert rc == 0 and np.array_equal(back, s)
+    finally:
+        oracle.set_huffman_table(na12878)
+        gpu.set_huffman_table(na12878)
+
+
+def test_ex_zd_q_read_with_mostly_exceptions(gpu, oracle):
+    """an ex-zd read with q > 0 whose shifted signal is mostly exceptions: both passes of
+    the count sweep capture into the pool; the reference makes one pass (ex_zd.c:436-447) and succeeds."""
+    rng = np.random.default_rng(21)
+    for n in (1000, 30000):
+        s = (np.cumsum(rng.choice([-200, 200], n)) << 2).astype(np.int16)
+        ro, so = oracle.press("ex_zd", s)
+        rc, st = gpu.press("ex_zd", s)
+        assert (rc == 0) == (ro == 0)
+        if ro == 0:
+            assert st == so
+            rc, back = gpu.depress("ex_zd", so, n)
+            assert rc == 0 and np.array_equal(back, s)
+    # inside a batch, next to ordinary reads
+    reads = [rand_read(rng, "walk", 9000), (np.cumsum(rng.choice([-150, 150], 20000)) << 3).astype(np.int16),
+             rand_read(rng, "q", 7000)]
+    offsets = np.concatenate([[0], np.cumsum([r.size for r in reads])]).astype(np.uint64)
+    rc, cont, oo = gpu.batch_press_host("ex_zd", np.concatenate(reads), offsets)
+    assert rc == 0 and cont.tobytes() == b"".join(oracle.press("ex_zd", r)[1] for r in reads)
+    assert np.array_equal(gpu.batch_depress_host("ex_zd", cont, oo, offsets), np.concatenate(reads))
+
+
 @pytest.mark.parametrize("method", IMPLEMENTED)
 def test_bench_scale_chunk_properties(gpu, checker, method):
     """the bench's workload at chunk scale (9000 NA12878-like reads, ~1 G samples, generated on the
