@@ -70,6 +70,7 @@ struct ExArgs {
 	uint2 *pool2;			// the same, one contiguous run per read (Hdr aux[3] = entries used)
 	uint64_t pool_cap;
 	const uint32_t *huff_enc;	// 256 x (code | length << 24)
+	uint16_t *sidecar;		// HUFF, optional: see huff_fused.cuh (null: none)
 };
 
 // per-halfword arithmetic shift right (ex_zd.c:383-394 on int16)
@@ -747,6 +748,8 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_kernel(const __grid_constant__ 
 		uint8_t *pay = dst + hdr;	// first payload byte of the read
 		uint64_t pos = 0;		// payload bytes (bits when HUFF) written so far
 		uint32_t carryb = 0;		// HUFF: the bits of the last, still partial byte
+		uint32_t psym = 0;		// HUFF: payload symbols written so far (side-car index)
+		uint16_t *sc = HUFF && a.sidecar ? a.sidecar + (T.off0 >> 5) + r : nullptr;
 		for (uint32_t t = 0; t < nt; t++) {
 			T.t = t;
 			T.k0 = A + (uint64_t) t * XG;
@@ -787,9 +790,14 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_kernel(const __grid_constant__ 
 			} else {
 				// code lengths -> bit position of every symbol (huffman.c:848-887: codes back
 				// to back, first bit of the stream in bit 0 of byte 0)
+				// (one scan for both running values: bits of a tile < 2^17, symbols <= 4096)
 				const uint32_t bits = ex_code_bits(v, ne, s_lut);
-				uint32_t c1[1] = {bits}, ex1[1], tot;
+				uint32_t c1[1] = {bits | ((uint32_t) __popc(ne) << 17)}, ex1[1], tot;
 				block_scan<1>(c1, ex1, tot, s_warp);
+				uint32_t si = psym + (ex1[0] >> 17);	// payload index of the thread's first symbol
+				psym += tot >> 17;
+				ex1[0] &= 0x1ffffu;
+				tot &= 0x1ffffu;
 				// the stage mirrors global memory from the 16-byte word holding the tile's first bit
 				const uint64_t G = 8 * (uint64_t) (pay - a.out) + pos;
 				const uint32_t s0 = (uint32_t) (G & 127), e0 = s0 + tot;
@@ -807,6 +815,10 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_kernel(const __grid_constant__ 
 				for (int e = 0; e < 16; e++) {
 					if ((ne >> e) & 1) {
 						const uint32_t c = s_lut[ex_elem(v, e)];
+						// side-car: the bit offset (in the read's bitstream) of every 32nd symbol
+						if (sc && (si & 31u) == 0)
+							sc[si >> 5] = (uint16_t) (pos + (32u * word + nacc - s0));
+						si++;
 						acc |= (uint64_t) (c & 0xffffffu) << nacc;
 						nacc += c >> 24;
 						if (nacc >= 32) {

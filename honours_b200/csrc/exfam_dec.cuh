@@ -33,6 +33,7 @@ struct ExDecArgs {
 	const uint32_t *huff_dec;	// 4096 two-symbol entries: see hd_run
 	const uint16_t *huff_sub;	// second level: [k][1 << huff_sub_bits]
 	uint32_t huff_sub_bits, huff_minlen;
+	const uint16_t *sidecar;	// SHUFF, optional: see huff_fused.cuh (null: self-synchronising decode)
 };
 
 // 16-byte word `w` of the 16-byte aligned region starting at `base16`, bytes outside [lo, hi) read as 0

@@ -86,7 +86,8 @@ struct PipeSlot {
 	}
 };
 
-constexpr int PIPE_SLOTS = 3;
+constexpr int PIPE_SLOTS = 6;	// chunks in flight per direction: deep enough that a copy queued behind the OTHER
+				// pipeline's traffic (duplex use) does not stall this one's uploads
 
 struct HostCtx {
 	bool ready = false;

@@ -58,7 +58,7 @@ def test_dropin_round_trips_fixture_reads(oracle, tmp_path):
     # plus two short synthetic reads (a q > 0 read among them)
     rng = np.random.default_rng(5)
     extra = [((100 + np.cumsum(rng.integers(-6, 7, 5000))) << 2).astype(np.int16),
-             (475 + np.cumsum(rng.integers(-25, 26, 1))).astype(np.int16)]
+             (475 + np.cumsum(rng.integers(-25, 26, 40))).astype(np.int16)]
     reads = [samples[int(offsets[r]):int(offsets[r + 1])] for r in range(3)] + extra
     off = np.concatenate([[0], np.cumsum([r.size for r in reads])]).astype(np.uint64)
     p = tmp_path / "reads.bin"
