@@ -749,7 +749,7 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_kernel(const __grid_constant__ 
 		uint64_t pos = 0;		// payload bytes (bits when HUFF) written so far
 		uint32_t carryb = 0;		// HUFF: the bits of the last, still partial byte
 		uint32_t psym = 0;		// HUFF: payload symbols written so far (side-car index)
-		uint16_t *sc = HUFF && a.sidecar ? a.sidecar + (T.off0 >> 5) + r : nullptr;
+		uint16_t *sc = HUFF && a.sidecar ? a.sidecar + (T.off0 >> 4) + r : nullptr;
 		for (uint32_t t = 0; t < nt; t++) {
 			T.t = t;
 			T.k0 = A + (uint64_t) t * XG;
@@ -815,9 +815,9 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_kernel(const __grid_constant__ 
 				for (int e = 0; e < 16; e++) {
 					if ((ne >> e) & 1) {
 						const uint32_t c = s_lut[ex_elem(v, e)];
-						// side-car: the bit offset (in the read's bitstream) of every 32nd symbol
-						if (sc && (si & 31u) == 0)
-							sc[si >> 5] = (uint16_t) (pos + (32u * word + nacc - s0));
+						// side-car: the bit offset (in the read's bitstream) of every 16th symbol
+						if (sc && (si & 15u) == 0)
+							sc[si >> 4] = (uint16_t) (pos + (32u * word + nacc - s0));
 						si++;
 						acc |= (uint64_t) (c & 0xffffffu) << nacc;
 						nacc += c >> 24;

@@ -32,7 +32,7 @@ struct ExDecArgs {
 	uint8_t *paybuf;		// SHUFF: symbols of read r at paybuf + offsets[r]
 	const uint32_t *huff_dec;	// 4096 two-symbol entries: see hd_run
 	const uint16_t *huff_sub;	// second level: [k][1 << huff_sub_bits]
-	uint32_t huff_sub_bits, huff_minlen;
+	uint32_t huff_sub_bits, huff_minlen, huff_nsub;
 	const uint16_t *sidecar;	// SHUFF, optional: see huff_fused.cuh (null: self-synchronising decode)
 };
 

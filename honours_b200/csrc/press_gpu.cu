@@ -21,6 +21,7 @@
 #include "svb_enc.cuh"
 #include "exfam.cuh"
 #include "exfam_dec.cuh"
+#include "huff_fused.cuh"
 #include "svb_dec.cuh"
 #include "host_ctx.h"
 

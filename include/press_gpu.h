@@ -191,9 +191,9 @@ int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_i
  * (huffman.c:1199-1209: a symbol count, then codes back to back) has no entry points for a
  * parallel decoder, so press_gpu_batch_depress decodes it self-synchronising, speculatively.
  * When the stream was written HERE, press can also leave, OUTSIDE the container (its bytes stay
- * exactly the reference's), one uint16 per 32 payload symbols: the low 16 bits of that symbol's
- * bit offset in the read's bitstream; entries of read r start at index (offsets[r] >> 5) + r.
- * depress with the side-car decodes every 32-symbol group independently and in one fused kernel
+ * exactly the reference's), one uint16 per 16 payload symbols: the low 16 bits of that symbol's
+ * bit offset in the read's bitstream; entries of read r start at index (offsets[r] >> 4) + r.
+ * depress with the side-car decodes every 16-symbol run independently and in one fused kernel
  * (bits -> samples), and reports status bit 1 if the side-car does not match the stream.
  * press_gpu_sidecar_bytes() = bytes to provide (0: the method has no side-car, the pointer is
  * ignored); d_sidecar = NULL selects the plain calls' behaviour. */

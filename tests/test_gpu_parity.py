@@ -248,6 +248,98 @@ def test_huffman_decodes_oracle_streams_without_sidecar(gpu, oracle):
         assert rc == 0 and np.array_equal(back, s), n
 
 
+def _device_roundtrip(gpu, method, samples, offsets, sidecar=True, corrupt=None):
+    """device batch press (+ side-car) and depress -> (container bytes, out_offsets, decoded, status)"""
+    import torch
+    dev = torch.device("cuda:0")
+    nreads, ns = offsets.size - 1, int(offsets[-1])
+    d_s = torch.from_numpy(samples).to(dev)
+    d_off = torch.from_numpy(offsets.astype(np.int64)).to(dev)
+    cap = gpu.batch_bound(method, nreads, ns)
+    gpu.set_exception_capacity(1.0)
+    sb = gpu.batch_scratch_bytes(method, nreads, ns)
+    gpu.set_exception_capacity(1.0 / 64)
+    nsc = gpu.sidecar_bytes(method, nreads, ns) if sidecar else 0
+    d_out = torch.empty(cap + 64, dtype=torch.uint8, device=dev)
+    d_oo = torch.empty(nreads + 1, dtype=torch.int64, device=dev)
+    d_scr = torch.empty(sb, dtype=torch.uint8, device=dev)
+    d_sc = torch.zeros(nsc + 64, dtype=torch.uint8, device=dev) if nsc else None
+    st = torch.cuda.current_stream().cuda_stream
+    gpu.batch_press(method, d_s.data_ptr(), d_off.data_ptr(), nreads, ns, d_out.data_ptr(), cap, d_oo.data_ptr(),
+                    d_scr.data_ptr(), sb, st, sidecar=d_sc.data_ptr() if nsc else 0, sidecar_bytes=nsc)
+    assert gpu.batch_status(d_scr.data_ptr(), st) == 0
+    oo = d_oo.cpu().numpy().astype(np.uint64)
+    total = int(oo[-1])
+    if corrupt is not None and nsc:
+        corrupt(d_sc)
+    d_back = torch.full((ns + 64,), -1, dtype=torch.int16, device=dev)
+    gpu.batch_depress(method, d_out.data_ptr(), d_oo.data_ptr(), total, d_off.data_ptr(), nreads, ns,
+                      d_back.data_ptr(), d_scr.data_ptr(), sb, st, sidecar=d_sc.data_ptr() if nsc else 0,
+                      sidecar_bytes=nsc)
+    status = gpu.batch_status(d_scr.data_ptr(), st)
+    assert bool((d_back[ns:] == -1).all())
+    return d_out[:total].cpu().numpy().tobytes(), oo, d_back[:ns].cpu().numpy(), status
+
+
+@pytest.mark.parametrize("method", HUFF)
+def test_huffman_sidecar_decode(gpu, checker, method):
+    """config 4, our own streams: press leaves the side-car (bit offset of every 32nd payload symbol)
+    OUTSIDE the container, whose bytes stay the reference's; depress with it (fused bits -> samples
+    kernel) returns the input; the same container decodes without it as well (self-synchronising)."""
+    rng = np.random.default_rng(31)
+    lens = [2, 3, 33, 34, 35, 65, 4096, 4097, 8191, 8192, 8193, 8225, 8226, 12289, 40000, 70001, 200000, 1, 0, 9]
+    kinds = ("walk", "spiky", "q", "walk")
+    hi = 12000 if method in HDR16 else 10 ** 9
+    reads = [rand_read(rng, kinds[i % 4], min(n, hi) if kinds[i % 4] != "walk" else n) for i, n in enumerate(lens)]
+    reads = [r if r.size != 1 else rand_read(rng, "walk", 2) for r in reads]       # (no 1-sample Huffman streams)
+    samples = np.concatenate(reads)
+    offsets = np.concatenate([[0], np.cumsum([r.size for r in reads])]).astype(np.uint64)
+    cont, oo, back, status = _device_roundtrip(gpu, method, samples, offsets, sidecar=True)
+    assert status == 0
+    assert cont == b"".join(checker.press(method, r)[1] if r.size else b"" for r in reads)
+    assert np.array_equal(back, samples)
+    cont2, _, back2, status2 = _device_roundtrip(gpu, method, samples, offsets, sidecar=False)
+    assert status2 == 0 and cont2 == cont and np.array_equal(back2, samples)
+
+
+def test_huffman_sidecar_mismatch_is_reported(gpu):
+    """a side-car that does not belong to the stream: status bit 1, no fault"""
+    rng = np.random.default_rng(32)
+    reads = [rand_read(rng, "walk", 50000), rand_read(rng, "spiky", 30000)]
+    samples = np.concatenate(reads)
+    offsets = np.array([0, 50000, 80000], dtype=np.uint64)
+
+    def corrupt(d_sc):
+        d_sc[64:4096] = 0x5a
+
+    _, _, _, status = _device_roundtrip(gpu, "shuff_vbe21_zd", samples, offsets, corrupt=corrupt)
+    assert status & 2
+    _, _, back, status = _device_roundtrip(gpu, "shuff_vbe21_zd", samples, offsets)
+    assert status == 0 and np.array_equal(back, samples)
+
+
+def test_huffman_sidecar_long_codes_take_the_global_path(gpu, oracle):
+    """a step whose codes average more than 12 bits does not fit the bit stage: decoded from global memory"""
+    freq = [2.0 ** -min(k, 23) + 1e-9 * (256 - k) for k in range(256)]
+    blob, lens = _huffman_table_blob(freq)
+    sym = max(range(256), key=lambda s: (lens[s], s))
+    delta = (sym >> 1) ^ -(sym & 1)
+    na12878 = open(os.path.join(os.path.dirname(GOLD), "..", "honours_b200", "data", "NA12878_zd.huffman"), "rb").read()
+    rng = np.random.default_rng(33)
+    try:
+        oracle.set_huffman_table(blob)
+        gpu.set_huffman_table(blob)
+        reads = [(np.arange(30000, dtype=np.int64) * delta).astype(np.int16), rand_read(rng, "walk", 20000)]
+        samples = np.concatenate(reads)
+        offsets = np.array([0, 30000, 50000], dtype=np.uint64)
+        cont, oo, back, status = _device_roundtrip(gpu, "shuff_vbe21_zd", samples, offsets)
+        assert status == 0 and np.array_equal(back, samples)
+        assert cont == b"".join(oracle.press("shuff_vbe21_zd", r)[1] for r in reads)
+    finally:
+        oracle.set_huffman_table(na12878)
+        gpu.set_huffman_table(na12878)
+
+
 def _huffman_table_blob(freq):
     """A code-table file image (huffman.c:440-480 layout) of the Huffman code of `freq`:
     [count u32 BE][data bytes u32 BE] then per symbol [sym][nbits][code bytes, bit k of the
@@ -388,8 +480,10 @@ def test_bench_scale_chunk_properties(gpu, checker, method):
     d_out = torch.empty(cap, dtype=torch.uint8, device=dev)
     d_oo = torch.empty(nreads + 1, dtype=torch.int64, device=dev)
     d_scr = torch.empty(sb, dtype=torch.uint8, device=dev)
+    nsc = gpu.sidecar_bytes(method, nreads, ns)     # (Huffman methods: decode through the fused side-car kernel)
+    d_sc = torch.empty(nsc + 64, dtype=torch.uint8, device=dev) if nsc else None
     gpu.batch_press(method, d_s.data_ptr(), d_off.data_ptr(), nreads, ns, d_out.data_ptr(), cap,
-                    d_oo.data_ptr(), d_scr.data_ptr(), sb, st)
+                    d_oo.data_ptr(), d_scr.data_ptr(), sb, st, sidecar=d_sc.data_ptr() if nsc else 0, sidecar_bytes=nsc)
     assert gpu.batch_status(d_scr.data_ptr(), st) == 0
     oo = d_oo.cpu().numpy().astype(np.uint64)
     assert oo[0] == 0 and np.all(np.diff(oo.astype(np.int64)) > 0) and int(oo[-1]) <= cap
@@ -403,11 +497,17 @@ def test_bench_scale_chunk_properties(gpu, checker, method):
     del samples, cont
     d_back = torch.full((ns + 64,), -1, dtype=torch.int16, device=dev)
     gpu.batch_depress(method, d_out.data_ptr(), d_oo.data_ptr(), int(oo[-1]), d_off.data_ptr(), nreads, ns,
-                      d_back.data_ptr(), d_scr.data_ptr(), sb, st)
+                      d_back.data_ptr(), d_scr.data_ptr(), sb, st, sidecar=d_sc.data_ptr() if nsc else 0, sidecar_bytes=nsc)
     assert gpu.batch_status(d_scr.data_ptr(), st) == 0
     assert torch.equal(d_back[:ns], d_s[:ns])
     assert bool((d_back[ns:] == -1).all())      # nothing written past the last sample
-    del d_s, d_out, d_back, d_scr
+    if nsc:     # and once more without the side-car: the self-synchronising decoder on the same container
+        d_back.fill_(-1)
+        gpu.batch_depress(method, d_out.data_ptr(), d_oo.data_ptr(), int(oo[-1]), d_off.data_ptr(), nreads, ns,
+                          d_back.data_ptr(), d_scr.data_ptr(), sb, st)
+        assert gpu.batch_status(d_scr.data_ptr(), st) == 0
+        assert torch.equal(d_back[:ns], d_s[:ns])
+    del d_s, d_out, d_back, d_scr, d_sc
     torch.cuda.empty_cache()
 
 
