@@ -6,7 +6,7 @@ import subprocess
 
 PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
-LIB = os.path.join(PKG, "libpress_gpu.so")
+LIB = os.environ.get("PRESS_GPU_LIB") or os.path.join(PKG, "libpress_gpu.so")   # (variant builds: tools/)
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

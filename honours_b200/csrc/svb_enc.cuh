@@ -54,7 +54,11 @@ constexpr int EN_W_B = EN_NA;			// first B warp
 constexpr int EN_W_SCAN = EN_NA + EN_NBW;	// prefix warp; + 1: publish warp
 constexpr int EN_W_PROD = EN_W_SCAN + 3;	// (+ 2: window warp)
 constexpr int EN_THREADS = (EN_W_PROD + 1) * 32;
-constexpr int EN_STAGES = 12;
+#ifndef PG_EN_STAGES
+#define PG_EN_STAGES 12
+#endif
+constexpr int EN_STAGES = PG_EN_STAGES;	// ring depth: tiles in flight per CTA.  Throughput follows it (6 / 9 / 12 stages:
+					// 38 / 51 / 59 % of HBM peak, r02): the kernel is bound by tile lifetime x ring size
 constexpr int EN_STAGE_BYTES = (EN_TG + 2) * 16 + 96;	// slots 0 .. TG+1, padded to 128
 constexpr int EN_LINE_BYTES = 2 * 8 * EN_EG + 16;	// per worker staging line (general path)
 constexpr int EN_WS = 4;				// window sums in flight between the window and the prefix warp
@@ -62,6 +66,14 @@ constexpr int EN_WW = 5;				// window words per lane: grid <= 32 * EN_WW + 1
 constexpr int EN_MAX_GRID = 32 * EN_WW + 1;
 constexpr int EN_WIN_WORDS = 32 * EN_WW + 4;	// window + alignment slack
 constexpr int EN_PACK_OFF = 512;			// packed bytes of a fast block: middle of its 2 KB of samples
+// A block that is not fast (a two-byte value, a read boundary) is packed by phase A as well when
+// its bytes fit between the block's first and last group, which the neighbouring blocks read and
+// which therefore stay intact: data bytes from EN_SLOW_DATA on, the block's key bytes at
+// EN_SLOW_KEYS.  (Phase B then only copies; before r02 it redid the block sample by sample while
+// holding the tile's ring stage: 6800 cycles per such block, 0.69 of them per tile.)
+constexpr int EN_SLOW_DATA = 16;
+constexpr int EN_SLOW_KEYS = 16 * EN_EG - 16 - 256;
+constexpr int EN_SLOW_MAX = EN_SLOW_KEYS - EN_SLOW_DATA;	// data bytes a packed slow block can hold (1760)
 
 struct EnTileInfo {
 	uint64_t off0, rend;	// sample range of the tile's read
@@ -83,7 +95,8 @@ struct EnSmem {
 	uint32_t tileL[EN_STAGES];		// data bytes of the tile (publish warp)
 	uint64_t kbase[EN_STAGES];		// container position of the read's key section
 	uint32_t blkL[EN_STAGES][EN_NB];	// data bytes of each 1024-sample block (phase A)
-	uint32_t blkF[EN_STAGES][EN_NB];	// 1: the block's data bytes are packed in its stage (phase A)
+	uint32_t blkF[EN_STAGES][EN_NB];	// phase A left the block 1: packed at EN_PACK_OFF (fast), 2: packed at
+						// EN_SLOW_DATA with its keys at EN_SLOW_KEYS, 0: as loaded (phase B codes it)
 	uint32_t ajob, bjob;			// next (tile, block) job of the A / B warps
 	uint64_t wsum_done[EN_WS], wsum_free[EN_WS];
 	uint2 wsum[EN_WS];				// window sum, sum of its last t words
@@ -125,25 +138,76 @@ __device__ __forceinline__ void en_group_zd(const EnTileInfo &ti, const uint8_t 
 	zd_group(x, prev, first ? (int) (ti.off0 & 7) : -1, z);
 }
 
-// exact data-byte count of block bw (valid samples + two-byte values).  One warp.
-__device__ __noinline__ uint32_t en_count_slow(const EnTileInfo &ti, const uint8_t *st, int bw, int lane)
+// Phase A of a block that is not fast: count, and when the bytes fit (EN_SLOW_MAX) pack data and
+// key bytes into the block's own stage area.  All four columns are loaded before the first byte
+// is stored.  Returns the data-byte count; packed = false leaves the block as loaded.
+template <int KEYBITS>
+__device__ __noinline__ uint32_t en_pack_slow(const EnTileInfo &ti, uint8_t *st, int bw, int lane, bool &packed)
 {
 	const uint64_t kw = ti.k0 + bw * EN_EG;
-	uint32_t cnt = 0;
-#pragma unroll 1
+	packed = true;
+	if (8 * kw >= ti.rend)
+		return 0;	// block past the end of the read
+	const uint32_t m = (uint32_t) (ti.off0 & 7);
+	uint32_t z[EN_EC][4], valid[EN_EC], fl[EN_EC];
+#pragma unroll
 	for (int c = 0; c < EN_EC; c++) {
-		uint32_t z[4];
-		en_group_zd(ti, st, bw * EN_EG + 32 * c + lane, z);
-		const uint32_t valid = group_valid(kw + 32 * c + lane, ti.off0, ti.rend);
-		cnt += __popc(valid) + __popc(flags_group(z) & valid);
+		en_group_zd(ti, st, bw * EN_EG + 32 * c + lane, z[c]);
+		valid[c] = group_valid(kw + 32 * c + lane, ti.off0, ti.rend);
+		fl[c] = flags_group(z[c]) & valid[c];
 	}
-	return __reduce_add_sync(0xffffffffu, cnt);
+	uint32_t fafter;	// flags of the group after the block (its first key bits belong to our last key byte)
+	{
+		uint32_t zn[4];
+		en_group_zd(ti, st, bw * EN_EG + EN_EG, zn);
+		fafter = flags_group(zn) & group_valid(kw + EN_EG, ti.off0, ti.rend);
+	}
+	__syncwarp();	// every lane holds its samples: the stage may be overwritten
+	const uint32_t sa = (__popc(valid[0]) + __popc(fl[0])) | ((__popc(valid[1]) + __popc(fl[1])) << 16);
+	const uint32_t sb = (__popc(valid[2]) + __popc(fl[2])) | ((__popc(valid[3]) + __popc(fl[3])) << 16);
+	const uint32_t ia = warp_inc_scan(sa, lane), ib = warp_inc_scan(sb, lane);
+	const uint32_t ta = __shfl_sync(0xffffffffu, ia, 31), tb = __shfl_sync(0xffffffffu, ib, 31);
+	const uint32_t t0 = ta & 0xffffu, t1 = ta >> 16, t2 = tb & 0xffffu, t3 = tb >> 16;
+	const uint32_t L = t0 + t1 + t2 + t3;
+	if (L > (uint32_t) EN_SLOW_MAX) {
+		packed = false;
+		return L;
+	}
+	const uint32_t off[EN_EC] = {(ia & 0xffffu) - (sa & 0xffffu), t0 + (ia >> 16) - (sa >> 16),
+				     t0 + t1 + (ib & 0xffffu) - (sb & 0xffffu), t0 + t1 + t2 + (ib >> 16) - (sb >> 16)};
+	uint8_t *blk = st + 16 * (bw * EN_EG + 1);
+#pragma unroll
+	for (int c = 0; c < EN_EC; c++) {
+		uint8_t *p = blk + EN_SLOW_DATA + off[c];
+#pragma unroll
+		for (int e = 0; e < 8; e++) {
+			const uint32_t v = (z[c][e >> 1] >> (16 * (e & 1))) & 0xffffu;
+			if ((valid[c] >> e) & 1) {
+				*p++ = (uint8_t) v;
+				if ((fl[c] >> e) & 1)
+					*p++ = (uint8_t) (v >> 8);
+			}
+		}
+		// keys: read-relative key block j of group k is k - A: bits m..7 of group j's flags +
+		// bits 0..m-1 of group j + 1's (the next lane's, the next column's first, the group after)
+		uint32_t fnext = __shfl_down_sync(0xffffffffu, fl[c], 1);
+		const uint32_t wrap = __shfl_sync(0xffffffffu, fl[c < EN_EC - 1 ? c + 1 : c], 0);
+		if (lane == 31)
+			fnext = c < EN_EC - 1 ? wrap : fafter;
+		const uint32_t f = ((fl[c] >> m) | (fnext << (8 - m))) & 0xffu;
+		if (KEYBITS == 1)
+			blk[EN_SLOW_KEYS + 32 * c + lane] = (uint8_t) f;
+		else
+			reinterpret_cast<uint16_t *>(blk + EN_SLOW_KEYS)[32 * c + lane] = (uint16_t) spread8(f);
+	}
+	return L;
 }
 
 // Phase A: byte count of the block -> blkL[bw].  A fast block (inside the read, no
 // two-byte value) also leaves its 1024 data bytes packed in the middle of its own
 // 2 KB of staged samples: the first and last group of the block, which the
 // neighbouring blocks read, stay intact.
+template <int KEYBITS>
 __device__ __forceinline__ void en_phase_a(const EnTileInfo &ti, uint8_t *st, uint32_t *blkL, uint32_t *blkF,
 					   int bw, int lane)
 {
@@ -183,10 +247,63 @@ __device__ __forceinline__ void en_phase_a(const EnTileInfo &ti, uint8_t *st, ui
 							       __byte_perm(z[c][2], z[c][3], 0x6420));
 		}
 	}
-	const uint32_t cnt = fast ? 8 * EN_EG : en_count_slow(ti, st, bw, lane);
+	uint32_t cnt = 8 * EN_EG, mode = 1;
+	if (!fast) {
+		bool packed;
+		cnt = en_pack_slow<KEYBITS>(ti, st, bw, lane, packed);
+		mode = packed ? 2u : 0u;
+	}
 	if (lane == 0) {
-		blkF[bw] = fast;
+		blkF[bw] = mode;
 		blkL[bw] = cnt;
+	}
+}
+
+// Phase B of a block packed by en_pack_slow: L data bytes from the stage to S (any alignment) as
+// aligned 64-bit stores (bytes at the edges), then the block's key bytes.
+template <int KEYBITS>
+__device__ __noinline__ void en_emit_packed(const SvbEncArgs &a, const EnTileInfo &ti, const uint8_t *st, uint64_t P,
+					    uint64_t kbase, uint32_t L, int bw, int lane)
+{
+	const uint64_t kw = ti.k0 + bw * EN_EG;
+	if (8 * kw >= ti.rend)
+		return;			// block past the end of the read
+	const uint8_t *blk = st + 16 * (bw * EN_EG + 1);
+	uint8_t *S = a.out + P;
+	const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(S) & 7), sh = 8 * s;
+	const uint64_t *pk = reinterpret_cast<const uint64_t *>(blk + EN_SLOW_DATA);
+	uint8_t *Wb = S - s;
+	const uint32_t end = s + L, nwords = (end + 7) >> 3;
+	for (uint32_t q = lane; q < nwords; q += 32) {
+		// aligned word q = packed bytes [8 q - s, 8 q - s + 8)  (pk[-1] is the block's first group: masked below)
+		const uint64_t hi = pk[q], lo = s ? pk[(int) q - 1] : 0ull;
+		const uint64_t v = s ? (lo >> (64 - sh)) | (hi << sh) : hi;
+		const uint32_t b0 = q << 3, b1 = b0 + 8;
+		if (b0 >= s && b1 <= end) {
+			*reinterpret_cast<uint64_t *>(Wb + b0) = v;
+		} else {
+			const uint32_t f = b0 < s ? s : b0, l = b1 > end ? end : b1;
+			for (uint32_t b = f; b < l; b++)
+				Wb[b] = (uint8_t) (v >> (8 * (b - b0)));
+		}
+	}
+	// keys: group 32 c + lane of the block is key block j of the read (svb16: one byte, svb32: two)
+	const uint64_t n = ti.rend - ti.off0;
+	const uint64_t jw = (uint64_t) ti.t * EN_TG + bw * EN_EG;
+	uint8_t *kout = a.out + kbase;
+#pragma unroll
+	for (int c = 0; c < EN_EC; c++) {
+		const uint64_t j = jw + 32 * c + lane;
+		if (KEYBITS == 1) {
+			if (8 * j < n)
+				kout[j] = blk[EN_SLOW_KEYS + 32 * c + lane];
+		} else {
+			const uint32_t kk = reinterpret_cast<const uint16_t *>(blk + EN_SLOW_KEYS)[32 * c + lane];
+			if (8 * j < n)
+				kout[2 * j] = (uint8_t) kk;
+			if (8 * j + 4 < n)
+				kout[2 * j + 1] = (uint8_t) (kk >> 8);
+		}
 	}
 }
 
@@ -610,7 +727,7 @@ __global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_con
 			mbar_wait(&sm.full[s], (i / EN_STAGES) & 1);
 			RT_END(0);
 			RT_BEGIN();
-			en_phase_a(sm.info[s], sm.in[s], sm.blkL[s], sm.blkF[s], bw, lane);
+			en_phase_a<KEYBITS>(sm.info[s], sm.in[s], sm.blkL[s], sm.blkF[s], bw, lane);
 			__syncwarp();
 			if (lane == 0)
 				mbar_arrive(&sm.cnt_done[s]);
@@ -635,10 +752,14 @@ __global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_con
 		RT_END(0);
 		RT_BEGIN();
 		const uint64_t P = sm.tileP[s];
-		const bool fast = sm.blkF[s][bw] != 0;
+		const uint32_t mode = sm.blkF[s][bw];
+		const bool fast = mode == 1;
 		if (P != SENTINEL) {
 			if (fast)
 				en_emit_fast<KEYBITS>(a, sm.info[s], sm.in[s], P + sm.blkOff[s][bw], sm.kbase[s], bw, lane);
+			else if (mode == 2)
+				en_emit_packed<KEYBITS>(a, sm.info[s], sm.in[s], P + sm.blkOff[s][bw], sm.kbase[s],
+							sm.blkL[s][bw], bw, lane);
 			else
 				en_emit_slow<KEYBITS>(a, sm.info[s], sm.in[s], P + sm.blkOff[s][bw], sm.kbase[s],
 						      sm.blkL[s][bw], sm.line[warp - EN_W_B], bw, lane);

@@ -53,7 +53,8 @@ class PressGpuError(RuntimeError):
 
 
 def lib_path() -> str:
-    return os.path.join(PKG, "libpress_gpu.so")
+    # PRESS_GPU_LIB: a variant build of the same library (tuning experiments, tools/)
+    return os.environ.get("PRESS_GPU_LIB") or os.path.join(PKG, "libpress_gpu.so")
 
 
 _lib = None

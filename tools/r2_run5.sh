@@ -1,0 +1,8 @@
+#!/bin/bash
+O=gpurun_out; T=${1:-r02i}
+( time timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "vbe21_zd or vbsse21_zd or vbbe21_zd or ex_zd" ) > $O/pytest_gpu_$T.log 2>&1; echo "pytest exit $?"; tail -25 $O/pytest_gpu_$T.log
+for m in vbe21_zd ex_zd; do
+timeout 300 python bench.py --method $m --reads 125000 --steps 3 --warmup 2 --methods "" --no-cpu-baseline --no-e2e > $O/bench_${m}_$T.json 2> $O/bench_${m}_$T.err; echo "bench exit $?"; tail -3 $O/bench_${m}_$T.err
+python -c "
+import json; b=json.load(open('$O/bench_${m}_$T.json')); print('$m', b['value'], b['compress_gbs'], b['decompress_gbs'], {k:(v['frac'],v['ms_per_launch']) for k,v in b['kernels'].items()})"
+done
