@@ -55,12 +55,11 @@ constexpr int EN_W_SCAN = EN_NA + EN_NBW;	// prefix warp; + 1: publish warp
 constexpr int EN_W_PROD = EN_W_SCAN + 3;	// (+ 2: window warp)
 constexpr int EN_THREADS = (EN_W_PROD + 1) * 32;
 #ifndef PG_EN_STAGES
-#define PG_EN_STAGES 12
+#define PG_EN_STAGES 13
 #endif
 constexpr int EN_STAGES = PG_EN_STAGES;	// ring depth: tiles in flight per CTA.  Throughput follows it (6 / 9 / 12 stages:
-					// 38 / 51 / 59 % of HBM peak, r02): the kernel is bound by tile lifetime x ring size
+					// 38 / 51 / 59 % of HBM peak before phase A packed every block, r02): the kernel is bound by tile lifetime x ring size
 constexpr int EN_STAGE_BYTES = (EN_TG + 2) * 16 + 96;	// slots 0 .. TG+1, padded to 128
-constexpr int EN_LINE_BYTES = 2 * 8 * EN_EG + 16;	// per worker staging line (general path)
 constexpr int EN_WS = 4;				// window sums in flight between the window and the prefix warp
 constexpr int EN_WW = 5;				// window words per lane: grid <= 32 * EN_WW + 1
 constexpr int EN_MAX_GRID = 32 * EN_WW + 1;
@@ -86,7 +85,6 @@ struct EnTileInfo {
 
 struct EnSmem {
 	alignas(128) uint8_t in[EN_STAGES][EN_STAGE_BYTES];
-	alignas(16) uint8_t line[EN_NBW][EN_LINE_BYTES];
 	EnTileInfo info[EN_STAGES];
 	uint64_t full[EN_STAGES], cnt_done[EN_STAGES], pub_done[EN_STAGES], scan_done[EN_STAGES], empty[EN_STAGES];
 	uint64_t tileP[EN_STAGES];		// container position of the tile's data (prefix warp);
@@ -307,11 +305,12 @@ __device__ __noinline__ void en_emit_packed(const SvbEncArgs &a, const EnTileInf
 	}
 }
 
-// general path of phase B: per-sample placement through the warp's staging line,
-// key bytes from the two-byte flags.  Group by group, nothing unrolled.
+// Last resort of phase B, for blocks en_pack_slow could not pack (more than EN_SLOW_MAX data
+// bytes: most values take two bytes, i.e. not a nanopore signal): per-sample placement straight
+// into the container, key bytes from the two-byte flags.  Group by group, nothing unrolled.
 template <int KEYBITS>
 __device__ __noinline__ void en_emit_slow(const SvbEncArgs &a, const EnTileInfo &ti, const uint8_t *st,
-					  uint64_t P, uint64_t kbase, uint32_t L, uint8_t *line, int bw, int lane)
+					  uint64_t P, uint64_t kbase, int bw, int lane)
 {
 	const uint64_t kw = ti.k0 + bw * EN_EG;
 	if (8 * kw >= ti.rend)
@@ -320,7 +319,6 @@ __device__ __noinline__ void en_emit_slow(const SvbEncArgs &a, const EnTileInfo 
 	const uint32_t m = (uint32_t) (ti.off0 & 7);
 	const uint64_t jw = (uint64_t) ti.t * EN_TG + bw * EN_EG;	// read-relative group of the block
 	uint8_t *S = a.out + P, *kout = a.out + kbase;
-	const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(S) & 7);
 	uint32_t run = 0;
 #pragma unroll 1
 	for (int c = 0; c < EN_EC; c++) {
@@ -331,7 +329,7 @@ __device__ __noinline__ void en_emit_slow(const SvbEncArgs &a, const EnTileInfo 
 		const uint32_t fl = flags_group(z) & valid;
 		const uint32_t cnt = __popc(valid) + __popc(fl);
 		const uint32_t inc = warp_inc_scan(cnt, lane);
-		uint8_t *p = line + s + run + inc - cnt;
+		uint8_t *p = S + run + inc - cnt;
 		run += __shfl_sync(0xffffffffu, inc, 31);
 #pragma unroll
 		for (int e = 0; e < 8; e++) {
@@ -361,9 +359,6 @@ __device__ __noinline__ void en_emit_slow(const SvbEncArgs &a, const EnTileInfo 
 				kout[2 * j + 1] = (uint8_t) (kk >> 8);
 		}
 	}
-	__syncwarp();
-	warp_copy_out(line, S, L, lane);
-	__syncwarp();
 }
 
 // Phase B of a fast block: its packed bytes to the container, key bytes zero.
@@ -762,7 +757,7 @@ __global__ void __launch_bounds__(EN_THREADS, 1) svb_enc_kernel(const __grid_con
 							sm.blkL[s][bw], bw, lane);
 			else
 				en_emit_slow<KEYBITS>(a, sm.info[s], sm.in[s], P + sm.blkOff[s][bw], sm.kbase[s],
-						      sm.blkL[s][bw], sm.line[warp - EN_W_B], bw, lane);
+						      bw, lane);
 		}
 		__syncwarp();
 		if (lane == 0)
