@@ -333,7 +333,7 @@ class Runner:
         max_ns = max(c["ns"] for c in chunks)
         max_nr = max(pad_reads)
         cap = max(press.batch_bound(method, c["nreads"], c["ns"]) for c in chunks)
-        if press.METHODS[method] >= 4:
+        if 4 <= press.METHODS[method] <= 10:
             # batch_bound is "every sample an exception" (6 B/sample); the container and the
             # exception pool are sized for this workload's exception rate instead (with slack) --
             # an overflow of either is reported by batch_status, never silent
@@ -492,7 +492,7 @@ class Runner:
         off = workload.offsets_of(lengths[:nreads])
         ns = int(off[-1])
         cap = press.batch_bound(method, nreads, ns)
-        if press.METHODS[method] >= 4:
+        if 4 <= press.METHODS[method] <= 10:
             cap = min(cap, int((1.05 + 8.0 * self.p_ex) * ns) + 1100 * nreads + 4096)
         h_s = press.pinned_array(2 * ns + 64)
         h_back = press.pinned_array(2 * ns + 64)

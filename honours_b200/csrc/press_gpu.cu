@@ -22,6 +22,7 @@
 #include "exfam.cuh"
 #include "exfam_dec.cuh"
 #include "huff_fused.cuh"
+#include "misc_codecs.cuh"
 #include "svb_dec.cuh"
 #include "host_ctx.h"
 
@@ -112,6 +113,13 @@ ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples, dou
 	const uint64_t mt = max_tiles(nreads, nsamples);
 	size_t o = 0;
 	l.hdr = o;		o += sizeof(Hdr);
+	if (method == PRESS_GPU_SVB0124_ZD || method == PRESS_GPU_UINT_ZD) {	// misc_codecs.cuh: per-read size and width
+		l.zero_bytes = o;
+		l.x_r8[0] = o;		o += align_up((nreads + 1) * 8, 256);
+		l.x_r[0] = o;		o += align_up((nreads + 1) * 4, 256);
+		l.total = o;
+		return l;
+	}
 	if (method >= PRESS_GPU_VBE21_ZD) {
 		const uint64_t xt = nsamples / 4096 + 2 * nreads + 2;	// tiles of 4096 samples
 		l.zero_bytes = o;	// only the header is cleared
@@ -159,7 +167,7 @@ ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples, dou
 ScratchLayout scratch_layout_for(int method, uint64_t nreads, uint64_t nsamples, size_t bytes)
 {
 	ScratchLayout l = scratch_layout(method, nreads, nsamples, 0.0);
-	if (method >= PRESS_GPU_VBE21_ZD && bytes > l.total) {
+	if (method >= PRESS_GPU_VBE21_ZD && method <= PRESS_GPU_SHUFF_VBBE21_ZD && bytes > l.total) {
 		uint64_t cap = l.x_pool_cap + (bytes - l.total) / 16 / 256 * 256;	// the two pools share what is left
 		const uint64_t cap_max = (method == PRESS_GPU_EX_ZD ? 2 : 1) * (nsamples + 1);
 		if (cap > cap_max)
@@ -236,6 +244,8 @@ uint64_t press_gpu_batch_bound(int method, uint64_t nreads, uint64_t nsamples)
 	case PRESS_GPU_SHUFF_VBBE21_ZD: return 6 * nsamples + 20 * nreads + 16;
 	case PRESS_GPU_VBSSE21_ZD: return 4 * nsamples + 16 * nreads + 16;
 	case PRESS_GPU_EX_ZD: return 2 * nsamples + 1024 * nreads + 16;	/* ex_zd.c:411 cap */
+	case PRESS_GPU_SVB0124_ZD: return 2 * nsamples + nsamples / 4 + nreads + 16;
+	case PRESS_GPU_UINT_ZD: return 2 * nsamples + 3 * nreads + 16;
 	default: break;
 	}
 	return 0;
@@ -397,6 +407,8 @@ int press_gpu_batch_press(int method, const int16_t *d_samples, const uint64_t *
 		if (k2 && !frame) return launch_svb_encode<2, false>(a, st);
 		return launch_svb_encode<2, true>(a, st);
 	}
+	if (method == PRESS_GPU_SVB0124_ZD || method == PRESS_GPU_UINT_ZD)
+		return mc_batch_press(method, d_samples, d_offsets, nreads, d_out, out_capacity, d_out_offsets, l, scr, st);
 	if (method >= PRESS_GPU_VBE21_ZD && method < PRESS_GPU_NMETHODS)
 		return ex_batch_press(method, d_samples, d_offsets, nreads, nsamples, d_out, out_capacity,
 				      d_out_offsets, l, scr, st);
@@ -449,6 +461,8 @@ int press_gpu_batch_depress(int method, const uint8_t *d_in, const uint64_t *d_i
 		if (k2 && !frame) return launch_svb_decode<2, false>(a, st);
 		return launch_svb_decode<2, true>(a, st);
 	}
+	if (method == PRESS_GPU_SVB0124_ZD || method == PRESS_GPU_UINT_ZD)
+		return mc_batch_depress(method, d_in, d_in_offsets, in_bytes, d_offsets, nreads, d_samples_out, l, scr, st);
 	if (method >= PRESS_GPU_VBE21_ZD && method < PRESS_GPU_NMETHODS)
 		return ex_batch_depress(method, d_in, d_in_offsets, in_bytes, d_offsets, nreads, nsamples,
 					d_samples_out, l, scr, st);

@@ -95,8 +95,11 @@ __device__ __forceinline__ uint32_t dec_keys_flags(const KeyRaw &k)
 	return ((squeeze16(c) | (squeeze16(c >> 16) << 8)) << k.skip) & 0xffffu;
 }
 
+#ifndef PG_DEC_CTAS
+#define PG_DEC_CTAS 5
+#endif
 template <int KEYBITS, bool FRAME>
-__global__ void __launch_bounds__(NT, 5) svb_dec_kernel(const __grid_constant__ SvbDec2Args a)
+__global__ void __launch_bounds__(NT, PG_DEC_CTAS) svb_dec_kernel(const __grid_constant__ SvbDec2Args a)
 {
 	// the tile's data bytes, double buffered: tile t + 1 arrives by cp.async (no registers held,
 	// no stage stores) while tile t is decoded

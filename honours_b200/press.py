@@ -26,6 +26,8 @@ METHODS = {
     "shuff_vbsse21_zd": 8,
     "vbbe21_zd": 9,
     "shuff_vbbe21_zd": 10,
+    "svb0124_zd": 11,
+    "uint_zd": 12,
 }
 
 # per-read entry points of include/press_gpu.h, by method
@@ -45,6 +47,8 @@ PER_READ = {
     "vbbe21_zd": ("vbbe21_zd_gpu_bound_16", "vbbe21_zd_gpu_press_16", "vbbe21_zd_gpu_depress_16"),
     "shuff_vbbe21_zd": ("shuffman_vbbe21_zd_gpu_bound_16", "shuffman_vbbe21_zd_gpu_press_16",
                         "shuffman_vbbe21_zd_gpu_depress_16"),
+    "svb0124_zd": ("svb0124_zd_gpu_bound_16", "svb0124_zd_gpu_press_16", "svb0124_zd_gpu_depress_16"),
+    "uint_zd": ("uint_zd_gpu_bound_16", "uint_zd_gpu_press_16", "uint_zd_gpu_depress_16"),
 }
 
 
@@ -158,7 +162,7 @@ def set_exception_capacity(entries_per_sample: float) -> None:
 def bound(method: str, nin: int) -> int:
     f = getattr(lib(), PER_READ[method][0])
     f.restype = C.c_uint64
-    f.argtypes = [C.c_uint64 if method in ("svb16_zd", "svb_zd") else C.c_uint32]
+    f.argtypes = [C.c_uint64 if method in ("svb16_zd", "svb_zd", "svb0124_zd", "uint_zd") else C.c_uint32]
     return int(f(nin))
 
 
@@ -172,10 +176,14 @@ def press(method: str, sig: np.ndarray) -> tuple[int, bytes]:
     nout = C.c_uint64(cap)
     f = getattr(L, PER_READ[method][1])
     rc = 0
-    if method in ("svb16_zd", "svb_zd"):
+    if method in ("svb16_zd", "svb_zd", "svb0124_zd"):
         f.restype = None
         f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64)]
         f(sig.ctypes.data, n, out.ctypes.data, C.byref(nout))
+    elif method == "uint_zd":
+        f.restype = C.c_int
+        f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64)]
+        rc = f(sig.ctypes.data, n, out.ctypes.data, C.byref(nout))
     elif method in ("vbe21_zd", "vbsse21_zd", "vbbe21_zd"):
         f.restype = None
         f.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]
@@ -202,11 +210,16 @@ def depress(method: str, stream: bytes, n: int) -> tuple[int, np.ndarray]:
     out = np.zeros(n + 64, dtype=np.int16)
     f = getattr(L, PER_READ[method][2])
     rc = 0
-    if method in ("svb16_zd", "svb_zd"):
+    if method in ("svb16_zd", "svb_zd", "svb0124_zd"):
         nout = C.c_uint64(n)
         f.restype = None
         f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64)]
         f(buf.ctypes.data, n, out.ctypes.data, C.byref(nout))
+    elif method == "uint_zd":
+        nout = C.c_uint64(n)
+        f.restype = C.c_int
+        f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64)]
+        rc = f(buf.ctypes.data, n, out.ctypes.data, C.byref(nout))
     elif method in ("vbe21_zd", "vbsse21_zd", "vbbe21_zd"):
         nout = C.c_uint32(n)
         f.restype = None

@@ -39,7 +39,9 @@ enum press_gpu_method {
 	PRESS_GPU_SHUFF_VBSSE21_ZD = 8,	/* shuffman_vbsse21_zd_*_16 press.h:658-663, press.c:4742-4845 */
 	PRESS_GPU_VBBE21_ZD = 9,	/* vbbe21_zd_*_16          press.h (press.c:3455-3500, 2775-2970): bit-packed lists */
 	PRESS_GPU_SHUFF_VBBE21_ZD = 10,	/* shuffman_vbbe21_zd_*_16 press.c:4505-4614 */
-	PRESS_GPU_NMETHODS = 11
+	PRESS_GPU_SVB0124_ZD = 11,	/* svb0124_zd_*_16         press.h:332-336, press.c:1616-1643 */
+	PRESS_GPU_UINT_ZD = 12,		/* uint_zd_*_16            press.h:106-112, press.c:639-687 */
+	PRESS_GPU_NMETHODS = 13
 };
 
 /* ---- context ------------------------------------------------------------- */
@@ -158,6 +160,21 @@ int shuffman_vbbe21_zd_gpu_press_16(const void *table, const int16_t *in, uint32
 				    uint8_t *out, uint64_t *nout);
 int shuffman_vbbe21_zd_gpu_depress_16(const void *table, uint8_t *in, uint64_t nin,
 				      int16_t *out, uint32_t *nout);
+
+/* svb0124-zd: press.h:332-336 (press.c:1616-1643): streamvbyte with 0 / 1 / 2 / 4-byte codes over
+ * zd.  depress nin = SAMPLES. */
+uint64_t svb0124_zd_gpu_bound_16(uint64_t nin);
+void svb0124_zd_gpu_press_16(const int16_t *in, uint64_t nin, uint8_t *out, uint64_t *nout);
+void svb0124_zd_gpu_depress_16(const uint8_t *in, uint64_t nin, int16_t *out, uint64_t *nout);
+
+/* uint-zd: press.h:106-112 (press.c:639-687): first sample, width byte, zd[1..] bit-packed at its
+ * minimal width.  The reference splits press in two calls -- uint_zd_get_minbits_16 (which also
+ * returns the zd array) and uint_zd_press_16(out_bits, in0, nin, in_zd, ...) -- because its zd
+ * lives on the host; here both are one call on the samples (test.c:363-378 collapses to it).
+ * depress: press.h:111, nin = SAMPLES.  0 ok / -1 failure. */
+uint64_t uint_zd_gpu_bound_16(uint64_t nin);	/* worst case: width 16 */
+int uint_zd_gpu_press_16(const int16_t *in, uint64_t nin, uint8_t *out, uint64_t *nout);
+int uint_zd_gpu_depress_16(const uint8_t *in, uint64_t nin, int16_t *out, uint64_t *nout);
 
 /* ---- 2. batch API (device pointers) --------------------------------------
  * Layout: d_samples = all reads back to back (int16, base 16-byte aligned),

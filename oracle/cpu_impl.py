@@ -32,6 +32,8 @@ METHODS = {
     "shuff_vbsse21_zd": 8,  # press.h shuffman_vbsse21_zd_*_16
     "vbbe21_zd": 9,  # press.h vbbe21_zd_*_16
     "shuff_vbbe21_zd": 10,  # press.h shuffman_vbbe21_zd_*_16
+    "svb0124_zd": 11,     # press.h svb0124_zd_*_16
+    "uint_zd": 12,        # press.h uint_zd_*_16
 }
 
 _u8p = C.POINTER(C.c_uint8)

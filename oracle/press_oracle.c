@@ -885,6 +885,96 @@ static int shuff_lists_zd_depress(int bitpacked, const uint8_t *in, uint64_t nby
 	return ret;
 }
 
+/* ---------- svb0124-zd (press.c:1616-1643; streamvbyte_0124_encode.c:8-59) ------------------ */
+
+/* keys[(n + 3) / 4] then data: value i has a 2-bit code at bit 2 (i & 3) of key byte i >> 2:
+ * 0 = no byte (value 0), 1 = one byte, 2 = two bytes LE, 3 = four bytes LE; the values are zd of
+ * all n samples widened to u32 (zigdelta_16_u32, trans.c:233-249: the first against 0). */
+static int svb0124_zd_press(const int16_t *in, uint64_t n, uint8_t *out, uint64_t *nout)
+{
+	uint64_t nk = (n + 3) / 4;
+	uint8_t *data = out + nk;
+	memset(out, 0, nk);
+	int16_t prev = 0;
+	for (uint64_t i = 0; i < n; i++) {
+		uint32_t v = oracle_zigzag16((int16_t) (in[i] - prev));
+		prev = in[i];
+		uint8_t code;
+		if (v == 0) {
+			code = 0;
+		} else if (v < 256) {
+			*data++ = (uint8_t) v;
+			code = 1;
+		} else {	/* zd < 65536: the four-byte code never occurs */
+			put_u16(data, (uint16_t) v);
+			data += 2;
+			code = 2;
+		}
+		out[i >> 2] |= (uint8_t) (code << (2 * (i & 3)));
+	}
+	*nout = (uint64_t) (data - out);
+	return 0;
+}
+
+static int svb0124_zd_depress(const uint8_t *in, uint64_t n, int16_t *out, uint64_t *nout)
+{
+	const uint8_t *data = in + (n + 3) / 4;
+	uint16_t acc = 0;
+	for (uint64_t i = 0; i < n; i++) {	/* streamvbyte_0124_decode.c scalar form, then trans.c:272-282 */
+		uint8_t code = (in[i >> 2] >> (2 * (i & 3))) & 3;
+		uint32_t v = 0;
+		if (code == 1) {
+			v = *data++;
+		} else if (code == 2) {
+			v = get_u16(data);
+			data += 2;
+		} else if (code == 3) {
+			v = get_u32(data);
+			data += 4;
+		}
+		acc = (uint16_t) (acc + (uint16_t) ((v >> 1) ^ (0u - (v & 1u))));
+		out[i] = (int16_t) acc;
+	}
+	*nout = n;
+	return 0;
+}
+
+/* ---------- uint-zd (press.c:639-687) ----------------------------------------------------- */
+
+/* [first sample i16 LE] then uint_press_16 of zd[1 .. n - 1] (zigdelta_16, trans.c:199-213) at the
+ * width of their maximum: [width u8][fields] (bitpack_be above). */
+static int uint_zd_press(const int16_t *in, uint64_t n, uint8_t *out, uint64_t *nout)
+{
+	if (n == 0)
+		return -1;
+	uint32_t m = (uint32_t) (n - 1);
+	uint32_t *v = malloc((m ? m : 1) * sizeof *v);
+	for (uint32_t i = 0; i < m; i++)
+		v[i] = oracle_zigzag16((int16_t) (in[i + 1] - in[i]));
+	put_u16(out, (uint16_t) in[0]);
+	*nout = 2 + bitpack_be(v, m, minbits_of(max_u32(v, m)), out + 2);
+	free(v);
+	return 0;
+}
+
+static int uint_zd_depress(const uint8_t *in, uint64_t n, int16_t *out, uint64_t *nout)
+{
+	if (n == 0 || in[2] > 16)
+		return -1;
+	uint32_t m = (uint32_t) (n - 1);
+	uint32_t *v = malloc((m ? m : 1) * sizeof *v);
+	bitunpack_be(in + 2, m, v);
+	uint16_t acc = get_u16(in);
+	out[0] = (int16_t) acc;
+	for (uint32_t i = 0; i < m; i++) {	/* trans.c:251-258 */
+		acc = (uint16_t) (acc + (uint16_t) ((v[i] >> 1) ^ (0u - (v[i] & 1u))));
+		out[i + 1] = (int16_t) acc;
+	}
+	free(v);
+	*nout = n;
+	return 0;
+}
+
 /* ---------- uniform adapter ------------------------------------------------ */
 
 uint64_t oracle_bound(int method, uint64_t n)
@@ -903,6 +993,8 @@ uint64_t oracle_bound(int method, uint64_t n)
 		return 2 + vb1e2_bound((uint32_t) (n - 1));
 	case ORC_EX_ZD:							/* press.c:8461-8464 */
 		return svb32_bound(2 + vb1e2_bound((uint32_t) (n - 1)));
+	case ORC_SVB0124_ZD: return svb32_bound(n);			/* press.c:1616-1619, 1531-1535 */
+	case ORC_UINT_ZD: return 3 + 2 * n;				/* press.c:654-657 at width 16 */
 	}
 	return 0;
 }
@@ -927,6 +1019,8 @@ int oracle_press(int method, const int16_t *in, uint64_t n, uint8_t *out, uint64
 	case ORC_SHUFF_VBSSE21_ZD: return shuff_lists_zd_press(0, in, (uint32_t) n, out, nout);
 	case ORC_VBBE21_ZD: return vbbe21_zd_press(in, (uint32_t) n, out, nout);
 	case ORC_SHUFF_VBBE21_ZD: return shuff_lists_zd_press(1, in, (uint32_t) n, out, nout);
+	case ORC_SVB0124_ZD: return svb0124_zd_press(in, n, out, nout);
+	case ORC_UINT_ZD: return uint_zd_press(in, n, out, nout);
 	}
 	return -1;
 }
@@ -948,6 +1042,8 @@ int oracle_depress(int method, const uint8_t *in, uint64_t nbytes, uint64_t n,
 	case ORC_SHUFF_VBSSE21_ZD: return shuff_lists_zd_depress(0, in, nbytes, n, out, nout);
 	case ORC_VBBE21_ZD: return vbbe21_zd_depress(in, nbytes, n, out, nout);
 	case ORC_SHUFF_VBBE21_ZD: return shuff_lists_zd_depress(1, in, nbytes, n, out, nout);
+	case ORC_SVB0124_ZD: return svb0124_zd_depress(in, n, out, nout);
+	case ORC_UINT_ZD: return uint_zd_depress(in, n, out, nout);
 	}
 	return -1;
 }

@@ -35,7 +35,9 @@ enum {
 	ORC_SHUFF_VBSSE21_ZD = 8,	/* press.h shuffman_vbsse21_zd_*_16 (a17) */
 	ORC_VBBE21_ZD = 9,	/* press.h vbbe21_zd_*_16 (a18: bit-packed exception lists) */
 	ORC_SHUFF_VBBE21_ZD = 10,	/* press.h shuffman_vbbe21_zd_*_16 (a19) */
-	ORC_NMETHODS = 8
+	ORC_SVB0124_ZD = 11,	/* press.h svb0124_zd_*_16 */
+	ORC_UINT_ZD = 12,	/* press.h uint_zd_*_16 */
+	ORC_NMETHODS = 13
 };
 
 /* Uniform adapter (the same three calls exist with the ref_ prefix in

@@ -16,7 +16,7 @@
 #include "ex_zd.h"
 
 enum { M_SVB16_ZD, M_SVB_ZD, M_VBZ_SVB16_ZD, M_VBZ_SVB_ZD, M_VBE21_ZD,
-       M_VBSSE21_ZD, M_EX_ZD, M_SHUFF_VBE21_ZD, M_SHUFF_VBSSE21_ZD, M_VBBE21_ZD, M_SHUFF_VBBE21_ZD };
+       M_VBSSE21_ZD, M_EX_ZD, M_SHUFF_VBE21_ZD, M_SHUFF_VBSSE21_ZD, M_VBBE21_ZD, M_SHUFF_VBBE21_ZD, M_SVB0124_ZD, M_UINT_ZD };
 
 static huffman_node *g_root;
 static SymbolEncoder g_se;
@@ -54,6 +54,9 @@ uint64_t ref_bound(int method, uint64_t n)
 	case M_SHUFF_VBSSE21_ZD: return shuffman_vbsse21_zd_bound_16((uint32_t) n);
 	case M_VBBE21_ZD: return vbbe21_zd_bound_16((uint32_t) n);
 	case M_SHUFF_VBBE21_ZD: return shuffman_vbbe21_zd_bound_16((uint32_t) n);
+	case M_SVB0124_ZD: return svb0124_zd_bound_16(n);
+	/* (the width is not known before the data is seen; the reference's bound wraps for one sample) */
+	case M_UINT_ZD: return n < 2 ? 8 : uint_zd_bound_16(16, n);
 	}
 	return 0;
 }
@@ -104,6 +107,16 @@ int ref_press(int method, const int16_t *in, uint64_t n, uint8_t *out, uint64_t 
 		if (!g_have_table)
 			return 1;
 		return shuffman_vbbe21_zd_press_16(&g_se, in, (uint32_t) n, out, nout);	/* press.c:4510 */
+	case M_SVB0124_ZD: svb0124_zd_press_16(in, n, out, nout); return 0;	/* press.c:1621 */
+	case M_UINT_ZD: {	/* the two calls of press/test.c:363-378 */
+		uint16_t *zd = NULL;
+		if (n == 0)
+			return -1;
+		uint8_t bits = uint_zd_get_minbits_16(in, n, &zd);	/* press.c:639 */
+		int r = uint_zd_press_16(bits, in[0], n, zd, out, nout);	/* press.c:659 */
+		free(zd);
+		return r;
+	}
 	}
 	return -1;
 }
@@ -147,6 +160,8 @@ int ref_depress(int method, const uint8_t *in, uint64_t nbytes, uint64_t n,
 			return 1;
 		r = shuffman_vbbe21_zd_depress_16(g_root, (uint8_t *) in, nbytes, out, &n32);	/* press.c:4560 */
 		break;
+	case M_SVB0124_ZD: svb0124_zd_depress_16(in, n, out, nout); return 0;	/* press.c:1631 */
+	case M_UINT_ZD: *nout = n; return uint_zd_depress_16(in, n, out, nout);	/* press.c:674 */
 	default: return -1;
 	}
 	*nout = n32;

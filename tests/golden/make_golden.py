@@ -78,7 +78,7 @@ def main():
     hist = [int(x) for x in re.search(r"\{([^}]*)\}", src).group(1).split(",")]
     assert len(hist) == 256 and sum(hist) == 56732772179
     json.dump({"source": "press/gen_huffman.c:11", "counts": hist},
-              open(f"{ROOT}/honours_b200/data/NA12878_zd_hist.json", "w"))
+              open(f"{ROOT}/benchdata/NA12878_zd_hist.json", "w"))
 
     # ---- three-reads.blow5 -------------------------------------------------
     reads = read_blow5(f"{REF}/data/three-reads.blow5")

@@ -12,10 +12,11 @@ pytestmark = pytest.mark.gpu
 
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 IMPLEMENTED = ["svb16_zd", "svb_zd", "vbz_svb16_zd", "vbz_svb_zd",
-               "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd", "shuff_vbsse21_zd", "vbbe21_zd", "shuff_vbbe21_zd"]
+               "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd", "shuff_vbsse21_zd", "vbbe21_zd", "shuff_vbbe21_zd",
+               "svb0124_zd", "uint_zd"]
 HUFF = ("shuff_vbe21_zd", "shuff_vbsse21_zd", "shuff_vbbe21_zd")
 HDR16 = ("shuff_vbsse21_zd", "shuff_vbbe21_zd")    # header length kept in a uint16_t (press.c:4753, 4521)
-EXFAM = IMPLEMENTED[4:]
+EXFAM = IMPLEMENTED[4:11]
 
 
 @pytest.fixture(scope="module")
@@ -130,14 +131,16 @@ def test_long_read_many_tiles(gpu, oracle):
     """one 3.3 M-sample read: > 800 tiles chained by look-back inside one read"""
     rng = np.random.default_rng(11)
     s = rand_read(rng, "spiky", 3_300_001)
-    for method in ("svb16_zd", "vbz_svb_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd", "vbbe21_zd"):
+    for method in ("svb16_zd", "vbz_svb_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd", "vbbe21_zd",
+                   "svb0124_zd", "uint_zd"):
         rc, st = gpu.press(method, s)
         assert rc == 0 and st == oracle.press(method, s)[1]
         rc, back = gpu.depress(method, st, s.size)
         assert rc == 0 and np.array_equal(back, s)
 
 
-@pytest.mark.parametrize("method", ["svb16_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd", "vbbe21_zd"])
+@pytest.mark.parametrize("method", ["svb16_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd", "vbbe21_zd",
+                                    "svb0124_zd", "uint_zd"])
 def test_device_batch_api_torch_pointers(gpu, checker, method):
     """the measured path: device-resident in/out, raw pointers through the C ABI"""
     import torch
