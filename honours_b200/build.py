@@ -35,7 +35,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     extra = os.environ.get("PRESS_GPU_DEFINES", "").split()     # e.g. -DPG_ROLE_TIMING (tools/role_timing.py)
-    cmd = [nvcc, *NVCC_FLAGS, *extra, "-o", LIB, *sources(), "-ldl"]
+    cmd = [nvcc, *NVCC_FLAGS, *extra, "-o", LIB, *sources(), "-ldl", "-lz"]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd))

@@ -115,6 +115,19 @@ def lib() -> C.CDLL:
         L.press_gpu_comm_destroy.restype = None
         L.press_gpu_allgather_offsets.restype = i32
         L.press_gpu_allgather_offsets.argtypes = [vp, u64, vp, vp, vp]
+        L.press_gpu_blow5_open.restype = vp
+        L.press_gpu_blow5_open.argtypes = [C.c_char_p]
+        L.press_gpu_blow5_close.argtypes = [vp]
+        L.press_gpu_blow5_signal_press.restype = i32
+        L.press_gpu_blow5_signal_press.argtypes = [vp]
+        L.press_gpu_blow5_next_batch.restype = C.c_int64
+        L.press_gpu_blow5_next_batch.argtypes = [vp, u64, u64, vp, vp, vp, sz]
+        L.press_gpu_container_write.restype = i32
+        L.press_gpu_container_write.argtypes = [C.c_char_p, i32, u64, vp, vp, vp]
+        L.press_gpu_container_info.restype = i32
+        L.press_gpu_container_info.argtypes = [C.c_char_p, C.POINTER(i32), C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]
+        L.press_gpu_container_read.restype = i32
+        L.press_gpu_container_read.argtypes = [C.c_char_p, vp, vp, vp]
         L.press_gpu_profile_enable.restype = None
         L.press_gpu_profile_enable.argtypes = [i32]
         L.press_gpu_profile_collect.restype = i32
@@ -383,3 +396,59 @@ def pinned_free(arr: np.ndarray) -> None:
 
 
 _pinned: dict[int, int] = {}
+
+
+# ---------------------------------------------------------------------------
+# records in, container out
+
+def blow5_read_all(path: str, max_reads: int = 1 << 16, max_samples: int = 1 << 26):
+    """All records of a BLOW5 file through press_gpu_blow5_* -> (samples int16, offsets uint64, ids,
+    signal_press).  svb-zd coded signals are decoded by the GPU inside the call."""
+    L = lib()
+    f = L.press_gpu_blow5_open(path.encode())
+    if not f:
+        raise PressGpuError(f"cannot open {path}")
+    try:
+        sp = L.press_gpu_blow5_signal_press(f)
+        parts, lens, ids = [], [], []
+        while True:
+            s = np.zeros(max_samples, dtype=np.int16)
+            o = np.zeros(max_reads + 1, dtype=np.uint64)
+            idb = np.zeros(max_reads * 64, dtype=np.uint8)
+            k = L.press_gpu_blow5_next_batch(f, max_reads, max_samples, s.ctypes.data, o.ctypes.data, idb.ctypes.data, 64)
+            if k < 0:
+                raise PressGpuError(last_error() or "blow5 read failed")
+            if k == 0:
+                break
+            parts.append(s[: int(o[k])].copy())
+            lens += np.diff(o[: k + 1].astype(np.int64)).tolist()
+            ids += [bytes(idb[64 * i: 64 * i + 64]).split(b"\0")[0].decode() for i in range(k)]
+        samples = np.concatenate(parts) if parts else np.zeros(0, np.int16)
+        offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+        return samples, offsets, ids, sp
+    finally:
+        L.press_gpu_blow5_close(f)
+
+
+def container_write(path: str, method: str, offsets: np.ndarray, out_offsets: np.ndarray, container: np.ndarray) -> None:
+    offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+    out_offsets = np.ascontiguousarray(out_offsets, dtype=np.uint64)
+    container = np.ascontiguousarray(container, dtype=np.uint8)
+    if lib().press_gpu_container_write(path.encode(), METHODS[method], offsets.size - 1, offsets.ctypes.data,
+                                       out_offsets.ctypes.data, container.ctypes.data) != 0:
+        raise PressGpuError(f"cannot write {path}")
+
+
+def container_read(path: str):
+    """-> (method name, offsets, out_offsets, container bytes)"""
+    L = lib()
+    m, nr, ns, nb = C.c_int(), C.c_uint64(), C.c_uint64(), C.c_uint64()
+    if L.press_gpu_container_info(path.encode(), C.byref(m), C.byref(nr), C.byref(ns), C.byref(nb)) != 0:
+        raise PressGpuError(f"{path}: not a container")
+    off = np.zeros(nr.value + 1, dtype=np.uint64)
+    oo = np.zeros(nr.value + 1, dtype=np.uint64)
+    cont = np.zeros(nb.value + 64, dtype=np.uint8)
+    if L.press_gpu_container_read(path.encode(), off.ctypes.data, oo.ctypes.data, cont.ctypes.data) != 0:
+        raise PressGpuError(f"{path}: truncated container")
+    name = {v: k for k, v in METHODS.items()}[m.value]
+    return name, off, oo, cont[: nb.value]

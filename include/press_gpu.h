@@ -275,6 +275,34 @@ int press_gpu_comm_rank(void);
 int press_gpu_allgather_offsets(const uint64_t *d_out_offsets, uint64_t nreads, uint64_t *d_gathered,
 				uint64_t *d_global, void *stream);
 
+/* ---- 3. records in, container out -------------------------------------
+ * BLOW5 reader: what the reference's benchmark loop does with slow5_open / slow5_get_next
+ * (press/test.h:10-37; press/sigtk/slow5lib/src/slow5.c:805-830, 3314, 3925-3960), for this
+ * library's batch layout.  press_gpu_blow5_next_batch fills h_samples / h_offsets[0 .. k] with the
+ * signals of the next k <= max_reads records (stopping before a read that would pass max_samples;
+ * it comes first in the next batch) and returns k (0: end of file, < 0: error).  ids (optional):
+ * the read ids as C strings, id_stride bytes apart.  Files whose signals are svb-zd coded
+ * (signal-press byte 1) are NOT decoded on the host: the stored [n u32][svb-zd] frames are
+ * PRESS_GPU_VBZ_SVB_ZD streams and go through press_gpu_batch_depress_host.  Record compression:
+ * none or zlib. */
+typedef struct press_gpu_blow5 press_gpu_blow5;
+press_gpu_blow5 *press_gpu_blow5_open(const char *path);
+void press_gpu_blow5_close(press_gpu_blow5 *f);
+int press_gpu_blow5_signal_press(const press_gpu_blow5 *f);	/* 0 raw int16, 1 svb-zd frames */
+int64_t press_gpu_blow5_next_batch(press_gpu_blow5 *f, uint64_t max_reads, uint64_t max_samples,
+				   int16_t *h_samples, uint64_t *h_offsets, char *ids, size_t id_stride);
+
+/* Container file: [magic "PRSGPU1"][method u64][nreads u64][nsamples u64][nbytes u64]
+ * [sample offsets u64 x (nreads + 1)][stream offsets u64 x (nreads + 1)][payload], little endian:
+ * the result of press_gpu_batch_press_host on disk.  _info reads the four counts (to size the
+ * buffers), _read the tables and the payload. */
+int press_gpu_container_write(const char *path, int method, uint64_t nreads, const uint64_t *h_offsets,
+			      const uint64_t *h_out_offsets, const uint8_t *h_container);
+int press_gpu_container_info(const char *path, int *method, uint64_t *nreads, uint64_t *nsamples,
+			     uint64_t *nbytes);
+int press_gpu_container_read(const char *path, uint64_t *h_offsets, uint64_t *h_out_offsets,
+			     uint8_t *h_container);
+
 /* Kernel timing for bench.py's roofline: when enabled every main codec kernel
  * launch is bracketed by CUDA events on its stream.  collect() waits for them
  * and returns, since the last collect, the summed device milliseconds and the

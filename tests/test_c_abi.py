@@ -17,7 +17,7 @@ CABI = os.path.join(ROOT, "tests", "c_abi")
 def _declared_functions():
     src = open(HDR).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    src = re.sub(r"typedef struct.*?}\s*\w+;", "", src, flags=re.S)
+    src = re.sub(r"typedef struct \w+ \{.*?\}\s*\w+;", "", src, flags=re.S)
     return sorted(set(re.findall(r"\b(\w+)\s*\([^;{}]*\)\s*;", src)))
 
 
