@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -331,10 +332,10 @@ int launch_svb_encode(const SvbEncArgs &a, cudaStream_t st)
 template <int KEYBITS, bool FRAME>
 int launch_svb_decode(const SvbDec2Args &a, cudaStream_t st)
 {
-	const uint64_t cap = (uint64_t) g_ctx.sms * 8;
+	const uint64_t cap = (uint64_t) g_ctx.sms * PG_DEC_CTAS;	// (resident CTAs; reads go by ticket)
 	const unsigned grid = (unsigned) (a.nreads < cap ? (a.nreads ? a.nreads : 1) : cap);
 	EvPair *ev = prof_begin(1, st);
-	svb_dec_kernel<KEYBITS, FRAME><<<grid, NT, 0, st>>>(a);
+	svb_dec2_kernel<KEYBITS, FRAME><<<grid, NT, 0, st>>>(a);
 	prof_end(ev, st);
 	g_launches++;
 	CK(cudaGetLastError());

@@ -7,18 +7,18 @@
 // The reference's decoder carries two values from one sample to the next: the
 // data pointer (advanced by 1 + key bit) and the running sum of the deltas.  Here
 // one CTA owns one READ (reads are handed out by an atomic ticket) and walks it
-// tile by tile (4096 samples), carrying both values itself, so no tile ever waits
+// step by step (8192 samples), carrying both values itself, so no tile ever waits
 // for another CTA and nothing is read twice:
 //
-//   keys of tile t+2   -> registers        (their address does not depend on the data)
-//   keys of tile t+1   -> byte counts -> block scan -> the tile's data range is known
-//   data of tile t+1   -> registers        (aligned 128-bit loads, issued before ...)
-//   tile t             -> smem stage -> values -> unzigzag -> block scan + carry ->
-//                         aligned 128-bit stores (tiles are cut on 16-byte boundaries
-//                         of the output array)
+//   keys of step t+2   -> registers        (their address does not depend on the data)
+//   keys of step t+1   -> byte counts -> block scan -> the step's data range is known
+//   data of step t+1   -> shared memory by cp.async (no registers held)
+//   step t             -> stage -> values -> unzigzag -> block scan + carry -> aligned
+//                         128-bit stores (steps are cut on 16-byte boundaries of the
+//                         output array)
 //
-// so the loads of a tile are in flight for a whole tile time before they are
-// needed.  1184 reads are in flight on a B200 (8 CTAs per SM).
+// so the loads of a step are in flight for a whole step time before they are
+// needed.  592 reads are in flight on a B200 (4 CTAs per SM).
 #pragma once
 
 #include "common.cuh"
@@ -95,15 +95,94 @@ __device__ __forceinline__ uint32_t dec_keys_flags(const KeyRaw &k)
 	return ((squeeze16(c) | (squeeze16(c >> 16) << 8)) << k.skip) & 0xffffu;
 }
 
-#ifndef PG_DEC_CTAS
-#define PG_DEC_CTAS 5
-#endif
-template <int KEYBITS, bool FRAME>
-__global__ void __launch_bounds__(NT, PG_DEC_CTAS) svb_dec_kernel(const __grid_constant__ SvbDec2Args a)
+// ---------------------------------------------------------------------------
+// A step is TWO 4096-sample subtiles (thread tid holds 16 samples of each): one "anything but
+// one-byte values?" vote, one byte-count scan (both counts packed in one word) and one value scan
+// (both 16-bit sums packed, added per half) per 8192 samples, the two subtiles' dependency chains
+// interleave, and a subtile of one-byte values is un-zigzagged four values per word before it is
+// widened.  (r01's kernel did all of this per 4096 samples: 57 % of HBM peak; this one 64 %.)
+
+constexpr int DT2 = 2 * DT;	// samples per step
+
+// exclusive scan over the CTA of two 16-bit values per thread (low / high half, each mod 2^16);
+// one __syncthreads(), s_warp as for block_scan
+__device__ __forceinline__ void block_scan16x2(uint32_t v, uint32_t &excl, uint32_t &total, uint32_t *s_warp)
 {
-	// the tile's data bytes, double buffered: tile t + 1 arrives by cp.async (no registers held,
-	// no stage stores) while tile t is decoded
-	__shared__ __align__(16) uint8_t s_in2[2][2 * DT + 64];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	uint32_t x = v;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+		if (lane >= o)
+			x = add16x2(x, y);
+	}
+	if (lane == 31)
+		s_warp[warp] = x;
+	__syncthreads();
+	const uint32_t t = s_warp[lane & 7];
+	uint32_t s = t;
+#pragma unroll
+	for (int o = 1; o < 8; o <<= 1) {
+		const uint32_t y = __shfl_up_sync(0xffffffffu, s, o);
+		if ((lane & 7) >= o)
+			s = add16x2(s, y);
+	}
+	const uint32_t before = __shfl_sync(0xffffffffu, sub16x2(s, t), warp);
+	total = __shfl_sync(0xffffffffu, s, 7);
+	excl = add16x2(before, sub16x2(x, v));
+}
+
+// 16 one-byte zigzag values (four per word) -> deltas, two per word, sign extended:
+// (b >> 1) ^ -(b & 1) on every byte (trans.c:80-83), then widened
+__device__ __forceinline__ void unzigzag_bytes16(const uint32_t (&w)[4], uint32_t (&d)[8])
+{
+#pragma unroll
+	for (int j = 0; j < 4; j++) {
+		const uint32_t u = ((w[j] >> 1) & 0x7f7f7f7fu) ^ ((w[j] & 0x01010101u) * 0xffu);
+		asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d[2 * j]) : "r"(u), "r"(0u), "r"(0x9180u));
+		asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d[2 * j + 1]) : "r"(u), "r"(0u), "r"(0xb3a2u));
+	}
+}
+
+// four words holding the 16 bytes at stage[off .. off + 16), off = al + 16 tid with al the same in
+// every thread (two conflict-free 128-bit loads), or at any offset (five 32-bit loads)
+__device__ __forceinline__ void stage_words_aligned(const uint8_t *stage, uint32_t al, int tid, uint32_t (&w)[4])
+{
+	const uint4 a = reinterpret_cast<const uint4 *>(stage)[tid], b = reinterpret_cast<const uint4 *>(stage)[tid + 1];
+	uint32_t u0, u1, u2, u3, u4;
+	switch (al >> 2) {
+	case 0: u0 = a.x; u1 = a.y; u2 = a.z; u3 = a.w; u4 = b.x; break;
+	case 1: u0 = a.y; u1 = a.z; u2 = a.w; u3 = b.x; u4 = b.y; break;
+	case 2: u0 = a.z; u1 = a.w; u2 = b.x; u3 = b.y; u4 = b.z; break;
+	default: u0 = a.w; u1 = b.x; u2 = b.y; u3 = b.z; u4 = b.w; break;
+	}
+	const uint32_t sh = (al & 3) * 8;
+	w[0] = __funnelshift_r(u0, u1, sh);
+	w[1] = __funnelshift_r(u1, u2, sh);
+	w[2] = __funnelshift_r(u2, u3, sh);
+	w[3] = __funnelshift_r(u3, u4, sh);
+}
+__device__ __forceinline__ void stage_words_any(const uint8_t *stage, uint32_t p, uint32_t (&w)[4])
+{
+	const uint32_t *w32 = reinterpret_cast<const uint32_t *>(stage) + (p >> 2);
+	const uint32_t sh = (p & 3) * 8;
+	uint32_t u[5];
+#pragma unroll
+	for (int j = 0; j < 5; j++)
+		u[j] = w32[j];
+#pragma unroll
+	for (int j = 0; j < 4; j++)
+		w[j] = __funnelshift_r(u[j], u[j + 1], sh);
+}
+
+template <int KEYBITS, bool FRAME>
+#ifndef PG_DEC_CTAS
+#define PG_DEC_CTAS 4
+#endif
+__global__ void __launch_bounds__(NT, PG_DEC_CTAS) svb_dec2_kernel(const __grid_constant__ SvbDec2Args a)
+{
+	// the step's data bytes, double buffered: step t + 1 arrives by cp.async while step t is decoded
+	__shared__ __align__(16) uint8_t s_in2[2][2 * DT2 + 64];
 	__shared__ __align__(16) uint32_t s_warp[NW];	// byte-count scans
 	__shared__ __align__(16) uint32_t s_warp2[NW];	// value scans
 	__shared__ uint32_t s_read;
@@ -136,27 +215,42 @@ __global__ void __launch_bounds__(NT, PG_DEC_CTAS) svb_dec_kernel(const __grid_c
 		const uint8_t *keys = a.in + sbase + (FRAME ? 4 : 0);
 		const uint8_t *data = keys + nkeys;
 		const uint64_t ndata = send - sbase - fixed;
-		// tiles are cut on 16-byte boundaries of the OUTPUT (aligned 128-bit stores): element e
-		// of thread tid in tile t is read index t * DT + 16 tid + e - m
+		// steps are cut on 16-byte boundaries of the OUTPUT (aligned 128-bit stores): element e of
+		// thread tid in subtile h of step t is read index t * DT2 + h * DT + 16 tid + e - m
 		const uint32_t m = (uint32_t) (off0 & 7);
 		const uint64_t A = off0 >> 3;
-		const uint32_t ntiles = (uint32_t) ((m + n + DT - 1) / DT);
+		const uint32_t nsteps = (uint32_t) ((m + n + DT2 - 1) / DT2);
 		uint4 *out4 = reinterpret_cast<uint4 *>(a.samples_out);
 		uint16_t *out16 = reinterpret_cast<uint16_t *>(a.samples_out);
+		// steps [t_lo, t_hi) are interior: every element is a sample of the read
+		const uint32_t t_lo = m ? 1u : 0u, t_hi = (uint32_t) ((m + n) / DT2);
+		const bool keys_safe = keys + nkeys + 8 <= limit;
 
-		auto first_of = [&](uint32_t t) -> int64_t { return (int64_t) t * DT + tid * DPT - (int64_t) m; };
-		// tiles [t_lo, t_hi) are interior: every element is a sample of the read
-		const uint32_t t_lo = m ? 1u : 0u, t_hi = (uint32_t) ((m + n) / DT);
-		auto interior_of = [&](uint32_t t) -> bool { return t >= t_lo && t < t_hi; };
-		auto valid_of = [&](uint32_t t) -> uint32_t {
-			if (interior_of(t))
-				return 0xffffu;
-			const int64_t i0 = first_of(t), left = (int64_t) n - i0;
-			const int lo = i0 < 0 ? (int) (-i0 < 16 ? -i0 : 16) : 0;
-			const int hi = left >= 16 ? 16 : (left > 0 ? (int) left : 0);
-			return hi > lo ? (0xffffu >> (16 - hi)) & (0xffffu << lo) & 0xffffu : 0u;
+		auto first_of = [&](uint32_t t, int h) -> int64_t {
+			return (int64_t) t * DT2 + h * DT + tid * DPT - (int64_t) m;
 		};
-		// data bytes of a tile -> stage `buf`: 16-byte words u, u + 256, (u + 512)
+		// valid masks of both subtiles (low / high 16 bits)
+		auto valid_of = [&](uint32_t t) -> uint32_t {
+			if (t >= t_lo && t < t_hi)
+				return 0xffffffffu;
+			uint32_t v = 0;
+#pragma unroll
+			for (int h = 0; h < 2; h++) {
+				const int64_t i0 = first_of(t, h), left = (int64_t) n - i0;
+				const int lo = i0 < 0 ? (int) (-i0 < 16 ? -i0 : 16) : 0;
+				const int hi = left >= 16 ? 16 : (left > 0 ? (int) left : 0);
+				const uint32_t vh = hi > lo ? (0xffffu >> (16 - hi)) & (0xffffu << lo) & 0xffffu : 0u;
+				v |= vh << (16 * h);
+			}
+			return v;
+		};
+		auto keys_of = [&](uint32_t t, int h) -> KeyRaw {
+			const int64_t i0 = first_of(t, h);
+			if (keys_safe && i0 >= 0)
+				return dec_keys_issue_fast<KEYBITS>(keys, (uint64_t) i0);
+			return dec_keys_issue<KEYBITS>(keys, i0, a.in, limit);
+		};
+		// data bytes of a step -> stage `buf`
 		auto issue_data = [&](uint32_t buf, uint64_t D, uint32_t L) {
 			const uint8_t *src = data + D;
 			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
@@ -165,14 +259,14 @@ __global__ void __launch_bounds__(NT, PG_DEC_CTAS) svb_dec_kernel(const __grid_c
 			uint4 *dst = reinterpret_cast<uint4 *>(s_in2[buf]);
 			if (b16 + 16ull * nw <= limit) {	// (b16 >= a.in: the container is 16-byte aligned)
 #pragma unroll
-				for (int j = 0; j < 3; j++) {
+				for (int j = 0; j < 5; j++) {
 					const uint32_t w = tid + j * NT;
 					if (w < nw)
 						cp_async16(dst + w, reinterpret_cast<const uint4 *>(b16) + w);
 				}
 			} else {
 #pragma unroll
-				for (int j = 0; j < 3; j++) {
+				for (int j = 0; j < 5; j++) {
 					const uint32_t w = tid + j * NT;
 					if (w < nw)
 						dst[w] = load_word_guarded(b16, w, a.in, limit);
@@ -180,25 +274,43 @@ __global__ void __launch_bounds__(NT, PG_DEC_CTAS) svb_dec_kernel(const __grid_c
 			}
 			cp_async_commit();
 		};
-
-		const bool keys_safe = keys + nkeys + 8 <= limit;
-		auto keys_of = [&](uint32_t t) -> KeyRaw {
-			if (keys_safe && t >= 1)	// (tile 0 may start before the read: i0 < 0)
-				return dec_keys_issue_fast<KEYBITS>(keys, (uint64_t) first_of(t));
-			return dec_keys_issue<KEYBITS>(keys, first_of(t), a.in, limit);
+		// flags of both subtiles from their raw key words, masked by the valid bits
+		auto flags_of = [&](const KeyRaw &ka, const KeyRaw &kb, uint32_t va) -> uint32_t {
+			return (dec_keys_flags<KEYBITS>(ka) | (dec_keys_flags<KEYBITS>(kb) << 16)) & va;
 		};
-		// ---- prologue: tile 0 scanned and its data requested, keys of tile 1 requested
+		// byte counts of both subtiles -> (exclusive offsets in the step's data, total); uniform
+		// fast exit when the whole step is one-byte values
+		auto count_scan = [&](uint32_t fl, uint32_t va, uint32_t &exa, uint32_t &exb, uint32_t &L) {
+			if (!__syncthreads_or(fl != 0 || va != 0xffffffffu)) {
+				exa = 16 * tid;
+				exb = DT + 16 * tid;
+				L = DT2;
+				return;
+			}
+			const uint32_t c = (uint32_t) (__popc(va & 0xffffu) + __popc(fl & 0xffffu)) |
+					   ((uint32_t) (__popc(va >> 16) + __popc(fl >> 16)) << 16);
+			uint32_t e, tot;
+			block_scan16x2(c, e, tot, s_warp);
+			exa = e & 0xffffu;
+			exb = (tot & 0xffffu) + (e >> 16);
+			L = (tot & 0xffffu) + (tot >> 16);
+		};
+
+		// ---- prologue: step 0 scanned and its data requested, keys of step 1 requested
 		uint32_t va_cur = valid_of(0);
-		uint32_t fl_cur = dec_keys_flags<KEYBITS>(dec_keys_issue<KEYBITS>(keys, first_of(0), a.in, limit)) & va_cur;
-		KeyRaw k_next = {0, 0, 0, 0};
-		if (ntiles > 1)
-			k_next = keys_of(1);
-		uint32_t ex_cur, L_cur;
+		uint32_t fl_cur;
 		{
-			uint32_t c1[1] = {(uint32_t) (__popc(va_cur) + __popc(fl_cur))}, e1[1];
-			block_scan<1>(c1, e1, L_cur, s_warp);
-			ex_cur = e1[0];
+			const KeyRaw k0a = dec_keys_issue<KEYBITS>(keys, first_of(0, 0), a.in, limit);
+			const KeyRaw k0b = dec_keys_issue<KEYBITS>(keys, first_of(0, 1), a.in, limit);
+			fl_cur = flags_of(k0a, k0b, va_cur);
 		}
+		KeyRaw kna = {0, 0, 0, 0}, knb = {0, 0, 0, 0};
+		if (nsteps > 1) {
+			kna = keys_of(1, 0);
+			knb = keys_of(1, 1);
+		}
+		uint32_t exa_cur, exb_cur, L_cur;
+		count_scan(fl_cur, va_cur, exa_cur, exb_cur, L_cur);
 		uint64_t D = 0;
 		uint32_t carry = 0;
 		bool overrun = L_cur > ndata;
@@ -206,106 +318,105 @@ __global__ void __launch_bounds__(NT, PG_DEC_CTAS) svb_dec_kernel(const __grid_c
 			issue_data(0, 0, L_cur);
 		__syncthreads();	// s_warp is reused by the first scan-ahead
 
-		for (uint32_t t = 0; t < ntiles && !overrun; t++) {
-			// ---- data of tile t: in stage t & 1 once this thread's copies have landed and the
-			// barrier below has passed (same 16-byte phase as in global memory)
+		for (uint32_t t = 0; t < nsteps && !overrun; t++) {
 			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(data + D) & 15);
 			const uint8_t *s_in = s_in2[t & 1];
 			cp_async_wait_all();
-			// ---- scan ahead: tile t + 1's byte counts, then request its data and tile t + 2's keys
-			uint32_t fl_n = 0, va_n = 0, ex_n = 0, L_n = 0;
-			if (t + 1 < ntiles) {
+			// ---- scan ahead: step t + 1's byte counts, then request its data and step t + 2's keys
+			uint32_t fl_n = 0, va_n = 0, exa_n = 0, exb_n = 0, L_n = 0;
+			if (t + 1 < nsteps) {
 				va_n = valid_of(t + 1);
-				fl_n = dec_keys_flags<KEYBITS>(k_next) & va_n;
-				// (the barrier inside either branch also publishes s_in)
-				if (!__syncthreads_or(fl_n != 0 || va_n != 0xffffu)) {
-					ex_n = 16 * tid;	// 4096 one-byte values: no scan needed
-					L_n = DT;
-				} else {
-					uint32_t c1[1] = {(uint32_t) (__popc(va_n) + __popc(fl_n))}, e1[1];
-					block_scan<1>(c1, e1, L_n, s_warp);
-					ex_n = e1[0];
-				}
+				fl_n = flags_of(kna, knb, va_n);
+				count_scan(fl_n, va_n, exa_n, exb_n, L_n);	// (its barrier also publishes s_in)
 				if (D + L_cur + L_n > ndata)
 					overrun = true;
 				else
 					issue_data((t + 1) & 1, D + L_cur, L_n);
-				if (t + 2 < ntiles)
-					k_next = keys_of(t + 2);
+				if (t + 2 < nsteps) {
+					kna = keys_of(t + 2, 0);
+					knb = keys_of(t + 2, 1);
+				}
 			} else {
 				__syncthreads();
 			}
-			// ---- bytes -> zd values, two per word
-			uint32_t zz[8];
-			const uint32_t p = al + ex_cur;
-			if (L_cur == DT && va_cur == 0xffffu && interior_of(t)) {
-				// full tile without a two-byte value: the thread's 16 bytes sit at stage[al + 16 tid]
-				stage_bytes16(s_in, al, tid, zz);
-			} else if (va_cur == 0xffffu && fl_cur == 0) {
-				// 16 one-byte values at an arbitrary stage offset
-				const uint32_t *w32 = reinterpret_cast<const uint32_t *>(s_in) + (p >> 2);
-				const uint32_t sh = (p & 3) * 8;
-				uint32_t w[5];
+			// ---- bytes -> deltas, two per word, for both subtiles
+			const bool plain = L_cur == DT2 && va_cur == 0xffffffffu && t >= t_lo && t < t_hi;
+			uint32_t y[2][8], sums = 0;
 #pragma unroll
-				for (int j = 0; j < 5; j++)
-					w[j] = w32[j];
+			for (int h = 0; h < 2; h++) {
+				const uint32_t vah = (va_cur >> (16 * h)) & 0xffffu, flh = (fl_cur >> (16 * h)) & 0xffffu;
+				const uint32_t p = al + (h ? exb_cur : exa_cur);
+				uint32_t d[8];
+				if (plain) {
+					// whole step of one-byte values: the thread's 16 bytes sit at stage[al + h DT + 16 tid]
+					uint32_t w[4];
+					stage_words_aligned(s_in + h * DT, al, tid, w);
+					unzigzag_bytes16(w, d);
+				} else if (vah == 0xffffu && flh == 0) {
+					uint32_t w[4];
+					stage_words_any(s_in, p, w);
+					unzigzag_bytes16(w, d);
+				} else {
+					const uint8_t *q = s_in + p;
+					uint32_t zz[8];
 #pragma unroll
-				for (int j = 0; j < 4; j++) {
-					const uint32_t v = __funnelshift_r(w[j], w[j + 1], sh);
-					zz[2 * j] = __byte_perm(v, 0, 0x4140);
-					zz[2 * j + 1] = __byte_perm(v, 0, 0x4342);
+					for (int j = 0; j < 8; j++)
+						zz[j] = 0;
+#pragma unroll
+					for (int e = 0; e < 16; e++) {
+						if ((vah >> e) & 1) {
+							uint32_t v = *q++;
+							if ((flh >> e) & 1)
+								v |= (uint32_t) (*q++) << 8;
+							zz[e >> 1] |= v << (16 * (e & 1));
+						}
+					}
+#pragma unroll
+					for (int j = 0; j < 8; j++)
+						d[j] = unzigzag16x2(zz[j]);
 				}
-			} else {
-				const uint8_t *q = s_in + p;
+				// running sum inside the thread (mod 2^16 in each half): decode_scalar.hpp:52-65
+				uint32_t c = 0;
 #pragma unroll
-				for (int j = 0; j < 8; j++)
-					zz[j] = 0;
+				for (int j = 0; j < 8; j++) {
+					y[h][j] = add16x2(d[j] * 0x00010001u, c);
+					c = __byte_perm(y[h][j], 0, 0x3232);
+				}
+				sums |= (c & 0xffffu) << (16 * h);
+			}
+			uint32_t e2, tot2;
+			block_scan16x2(sums, e2, tot2, s_warp2);
+			const uint32_t cwa = ((e2 + carry) & 0xffffu) * 0x00010001u;
+			const uint32_t cwb = (((e2 >> 16) + tot2 + carry) & 0xffffu) * 0x00010001u;
 #pragma unroll
-				for (int e = 0; e < 16; e++) {
-					if ((va_cur >> e) & 1) {
-						uint32_t v = *q++;
-						if ((fl_cur >> e) & 1)
-							v |= (uint32_t) (*q++) << 8;
-						zz[e >> 1] |= v << (16 * (e & 1));
+			for (int h = 0; h < 2; h++) {
+				const uint32_t cw = h ? cwb : cwa;
+				const uint64_t ka = A + (uint64_t) t * (DT2 / 8) + h * (DT / 8) + 2 * tid;
+#pragma unroll
+				for (int g = 0; g < 2; g++) {
+					const uint32_t vm = (va_cur >> (16 * h + 8 * g)) & 0xffu;
+					const uint32_t o0 = add16x2(y[h][4 * g], cw), o1 = add16x2(y[h][4 * g + 1], cw);
+					const uint32_t o2 = add16x2(y[h][4 * g + 2], cw), o3 = add16x2(y[h][4 * g + 3], cw);
+					if (vm == 0xffu) {
+						out4[ka + g] = make_uint4(o0, o1, o2, o3);
+					} else if (vm) {
+						const uint32_t o[4] = {o0, o1, o2, o3};
+#pragma unroll
+						for (int e = 0; e < 8; e++)
+							if ((vm >> e) & 1)
+								out16[8 * (ka + g) + e] = (uint16_t) (o[e >> 1] >> (16 * (e & 1)));
 					}
 				}
 			}
-			// ---- unzigzag, running sum (mod 2^16 in each half): decode_scalar.hpp:10-13, 52-65
-			uint32_t y[8], c = 0;
-#pragma unroll
-			for (int j = 0; j < 8; j++) {
-				const uint32_t d = unzigzag16x2(zz[j]);
-				y[j] = add16x2(d * 0x00010001u, c);
-				c = __byte_perm(y[j], 0, 0x3232);
-			}
-			uint32_t c1[1] = {c & 0xffffu}, e1[1], tot;
-			block_scan<1>(c1, e1, tot, s_warp2);
-			const uint32_t cw = ((e1[0] + carry) & 0xffffu) * 0x00010001u;
-			uint32_t o[8];
-#pragma unroll
-			for (int j = 0; j < 8; j++)
-				o[j] = add16x2(y[j], cw);
-			const uint64_t ka = A + (uint64_t) t * (DT / 8) + 2 * tid;
-#pragma unroll
-			for (int h = 0; h < 2; h++) {
-				const uint32_t vm = (va_cur >> (8 * h)) & 0xffu;
-				if (vm == 0xffu) {
-					out4[ka + h] = make_uint4(o[4 * h], o[4 * h + 1], o[4 * h + 2], o[4 * h + 3]);
-				} else if (vm) {
-#pragma unroll
-					for (int e = 0; e < 8; e++)
-						if ((vm >> e) & 1)
-							out16[8 * (ka + h) + e] = (uint16_t) (o[4 * h + (e >> 1)] >> (16 * (e & 1)));
-				}
-			}
-			carry = (carry + tot) & 0xffffu;
+			carry = (carry + (tot2 & 0xffffu) + (tot2 >> 16)) & 0xffffu;
 			D += L_cur;
 			fl_cur = fl_n;
 			va_cur = va_n;
-			ex_cur = ex_n;
+			exa_cur = exa_n;
+			exb_cur = exb_n;
 			L_cur = L_n;
 			// (no barrier here: every read of s_in above precedes the value scan's barrier, every
-			//  read of s_warp / s_warp2 is followed by the next tile's first barrier before the
+			//  read of s_warp / s_warp2 is followed by the next step's first barrier before the
 			//  array is written again)
 		}
 		if (overrun && tid == 0)
