@@ -5,10 +5,10 @@
 //                      decoded into a pool (sorted positions, values)
 //   huff_decode(read)  SHUFF only: bitstream -> one-byte symbols in a scratch payload
 //                      (self-synchronising parallel decode, see below)
-//   ex_decode  (read)  one CTA walks one read tile by tile: payload + exceptions ->
-//                      unzigzag -> running sum (trans.c:260-270) carried by the CTA from
-//                      tile to tile -> << q -> samples; the next tile's payload bytes
-//                      are requested before the current tile is processed
+//   ex_decode2 (read)  one CTA walks one read step by step (two 4096-sample subtiles): payload
+//                      + exceptions -> unzigzag -> running sum (trans.c:260-270) carried by the
+//                      CTA from step to step -> << q -> samples; the next step's payload bytes
+//                      are requested before the current step is processed
 #pragma once
 
 #include "exfam.cuh"
@@ -561,17 +561,92 @@ __global__ void __launch_bounds__(NT, 5) huff_decode_kernel(const __grid_constan
 }
 
 // ---------------------------------------------------------------------------
-// payload + exceptions -> samples
+// payload + exceptions -> samples, TWO 4096-sample subtiles per step (thread tid holds 16 samples
+// of each): one exception vote and one value scan (both 16-bit sums packed, added per half) per
+// 8192 samples, the subtiles' chains interleave, and a subtile without exceptions is un-zigzagged
+// four values per word before it is widened (cf. svb_dec.cuh)
 
-__global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant__ ExDecArgs a)
+constexpr int XT2 = 2 * XT;
+
+// two 16-bit exclusive scans over the CTA in one (low / high half, each mod 2^16); one barrier
+__device__ __forceinline__ void block_scan_pair(uint32_t v, uint32_t &excl, uint32_t &total, uint32_t *s_warp)
 {
-	// the tile's payload bytes, double buffered: tile t + 1 arrives by cp.async (no registers
-	// held, no stage stores) while tile t is decoded
-	__shared__ __align__(16) uint8_t s_stage2[2][XT + 64];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	uint32_t x = v;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+		if (lane >= o)
+			x = add16x2(x, y);
+	}
+	if (lane == 31)
+		s_warp[warp] = x;
+	__syncthreads();
+	const uint32_t t = s_warp[lane & 7];
+	uint32_t s = t;
+#pragma unroll
+	for (int o = 1; o < 8; o <<= 1) {
+		const uint32_t y = __shfl_up_sync(0xffffffffu, s, o);
+		if ((lane & 7) >= o)
+			s = add16x2(s, y);
+	}
+	const uint32_t before = __shfl_sync(0xffffffffu, sub16x2(s, t), warp);
+	total = __shfl_sync(0xffffffffu, s, 7);
+	excl = add16x2(before, sub16x2(x, v));
+}
+
+// 16 one-byte zigzag values (four per word) -> deltas, two per word, sign extended
+__device__ __forceinline__ void unzigzag_bytes_x16(const uint32_t (&w)[4], uint32_t (&d)[8])
+{
+#pragma unroll
+	for (int j = 0; j < 4; j++) {
+		const uint32_t u = ((w[j] >> 1) & 0x7f7f7f7fu) ^ ((w[j] & 0x01010101u) * 0xffu);	// trans.c:80-83 per byte
+		asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d[2 * j]) : "r"(u), "r"(0u), "r"(0x9180u));
+		asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d[2 * j + 1]) : "r"(u), "r"(0u), "r"(0xb3a2u));
+	}
+}
+
+// four words holding the 16 bytes at stage[off .. off + 16), off = al + 16 tid with al the same in
+// every thread (two conflict-free 128-bit loads), or at any offset (five 32-bit loads)
+__device__ __forceinline__ void stage_words_aligned(const uint8_t *stage, uint32_t al, int tid, uint32_t (&w)[4])
+{
+	const uint4 a = reinterpret_cast<const uint4 *>(stage)[tid], b = reinterpret_cast<const uint4 *>(stage)[tid + 1];
+	uint32_t u0, u1, u2, u3, u4;
+	switch (al >> 2) {
+	case 0: u0 = a.x; u1 = a.y; u2 = a.z; u3 = a.w; u4 = b.x; break;
+	case 1: u0 = a.y; u1 = a.z; u2 = a.w; u3 = b.x; u4 = b.y; break;
+	case 2: u0 = a.z; u1 = a.w; u2 = b.x; u3 = b.y; u4 = b.z; break;
+	default: u0 = a.w; u1 = b.x; u2 = b.y; u3 = b.z; u4 = b.w; break;
+	}
+	const uint32_t sh = (al & 3) * 8;
+	w[0] = __funnelshift_r(u0, u1, sh);
+	w[1] = __funnelshift_r(u1, u2, sh);
+	w[2] = __funnelshift_r(u2, u3, sh);
+	w[3] = __funnelshift_r(u3, u4, sh);
+}
+__device__ __forceinline__ void stage_words_any(const uint8_t *stage, uint32_t p, uint32_t (&w)[4])
+{
+	const uint32_t *w32 = reinterpret_cast<const uint32_t *>(stage) + (p >> 2);
+	const uint32_t sh = (p & 3) * 8;
+	uint32_t u[5];
+#pragma unroll
+	for (int j = 0; j < 5; j++)
+		u[j] = w32[j];
+#pragma unroll
+	for (int j = 0; j < 4; j++)
+		w[j] = __funnelshift_r(u[j], u[j + 1], sh);
+}
+
+
+__global__ void __launch_bounds__(NT, 4) ex_decode2_kernel(const __grid_constant__ ExDecArgs a)
+{
+	// the step's payload bytes, double buffered: step t + 1 arrives by cp.async while step t is decoded
+	__shared__ __align__(16) uint8_t s_stage2[2][XT2 + 64];
 	__shared__ __align__(16) uint32_t s_warp[NW];
-	__shared__ uint32_t s_read, s_e;
+	__shared__ uint32_t s_cnt[NW];
+	__shared__ uint32_t s_read, s_e[2];
 	__shared__ uint2 s_ex[NT];	// the next 256 exceptions of the read (position, value)
-	const int tid = threadIdx.x;
+	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	const bool shuff = ex_is_huff(a.method);
 	const uint8_t *lim_lo = shuff ? a.paybuf : a.in;
 	const uint8_t *lim_hi = shuff ? a.paybuf + ((a.offsets[a.nreads] + 15) & ~15ull) : a.in + a.in_bytes;
@@ -591,187 +666,213 @@ __global__ void __launch_bounds__(NT, 6) ex_decode_kernel(const __grid_constant_
 		const uint64_t off0 = __ldg(a.offsets + r), rend = __ldg(a.offsets + r + 1), n = rend - off0;
 		const uint32_t m = (uint32_t) (off0 & 7);
 		const uint64_t A = off0 >> 3;
-		const uint32_t nt = (uint32_t) ((m + n + XT - 1) / XT);
+		const uint32_t nt4 = (uint32_t) ((m + n + XT - 1) / XT);	// 4096-sample subtiles of the read
+		const uint32_t nsteps = (nt4 + 1) / 2;
 		const uint32_t nex = a.r_nex[r], q = a.r_q[r], zd0 = a.r_zd0[r];
 		const uint2 *ex = a.pool + a.r_pool[r];
 		const uint8_t *pbase = shuff ? a.paybuf + off0 : a.in + pay0;
-
-		// v-indices of the read before tile t (ex_v_before), in 32 bits: 0 for the first tile,
-		// everything for t >= nt, t * XT - m - 1 in between (below n - 1 there)
 		const uint32_t nm1 = (uint32_t) (n - 1);
-		auto vb = [&](uint32_t t) { return t == 0 ? 0u : t >= nt ? nm1 : t * (uint32_t) XT - m - 1u; };
-		// may every 16-byte word the walk can touch be loaded without a look at the limits?
+		// v-indices (sample index - 1) of the read before subtile tt: 0 for the first, everything
+		// from the end on, tt * XT - m - 1 in between
+		auto vb = [&](uint32_t tt) { return tt == 0 ? 0u : tt >= nt4 ? nm1 : tt * (uint32_t) XT - m - 1u; };
 		const bool safe = pbase - 16 >= lim_lo && pbase + (uint64_t) nm1 + 48 <= lim_hi;
-		// payload bytes of a tile -> stage `buf` (16-byte word tid, and word 256 by thread 0)
+		// payload bytes of a step -> stage `buf`
 		auto issue = [&](uint32_t buf, uint32_t j_lo, uint32_t j_hi, uint32_t e_lo) {
 			const uint8_t *src = pbase + (j_lo - e_lo);
 			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(src) & 15);
 			const uint32_t nw = (al + (j_hi - j_lo) + 15) >> 4;	// (a few bytes more than needed when
-			const uint8_t *b16 = src - al;				//  the tile holds exceptions)
+			const uint8_t *b16 = src - al;				//  the step holds exceptions)
 			uint4 *dst = reinterpret_cast<uint4 *>(s_stage2[buf]);
-			if (safe || (b16 >= lim_lo && b16 + 16ull * nw <= lim_hi)) {
-				if ((uint32_t) tid < nw)
-					cp_async16(dst + tid, reinterpret_cast<const uint4 *>(b16) + tid);
-				if (tid == 0 && nw > NT)
-					cp_async16(dst + NT, reinterpret_cast<const uint4 *>(b16) + NT);
-			} else {
-				if ((uint32_t) tid < nw)
-					dst[tid] = load_word_guarded(b16, tid, lim_lo, lim_hi);
-				if (tid == 0 && nw > NT)
-					dst[NT] = load_word_guarded(b16, NT, lim_lo, lim_hi);
+			const bool fastld = safe || (b16 >= lim_lo && b16 + 16ull * nw <= lim_hi);
+#pragma unroll
+			for (int j = 0; j < 3; j++) {
+				const uint32_t w = tid + j * NT;
+				if (w < nw && (j < 2 || tid == 0)) {
+					if (fastld)
+						cp_async16(dst + w, reinterpret_cast<const uint4 *>(b16) + w);
+					else
+						dst[w] = load_word_guarded(b16, w, lim_lo, lim_hi);
+				}
 			}
 			cp_async_commit();
 		};
-		const uint32_t t_hi = (uint32_t) ((m + n) / XT);	// tiles [1, t_hi) lie inside the read
-		// the read's next 256 exceptions travel with the payload: requested one tile ahead,
-		// staged in shared memory, so the per-tile and per-thread searches never go to HBM
+		const uint32_t t_hi4 = (uint32_t) ((m + n) / XT);	// subtiles [1, t_hi4) lie inside the read
 		uint2 exreg = make_uint2(0xffffffffu, 0u);
 		auto issue_ex = [&](uint32_t e0) {
 			exreg = e0 + tid < nex ? ex[e0 + tid] : make_uint2(0xffffffffu, 0u);
 		};
 		uint32_t e_lo = 0, carry = 0;
-		uint32_t j_lo = 0, j_hi = vb(1), j_nx = vb(2);	// v-indices before tiles t, t + 1, t + 2
-		issue(0, j_lo, j_hi, 0);
+		issue(0, vb(0), vb(2), 0);
 		if (nex)
 			issue_ex(0);
-		for (uint32_t t = 0; t < nt; t++, j_lo = j_hi, j_hi = j_nx, j_nx = vb(t + 2)) {
-			const uint32_t p_lo = j_lo - e_lo;
+		for (uint32_t t = 0; t < nsteps; t++) {
+			const uint32_t j0 = vb(2 * t), j1 = vb(2 * t + 1), j2 = vb(2 * t + 2);
+			const uint32_t p_lo = j0 - e_lo;	// payload index of the step's first byte
 			const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(pbase + p_lo) & 15);
 			const uint8_t *s_stage = s_stage2[t & 1];	// complete once the barrier below has passed
 			cp_async_wait_all();
-			uint32_t e_hi = 0;
+			uint32_t e_mid = e_lo, e_hi = e_lo;
 			const uint2 *xs = ex;	// where exceptions [e_lo, e_hi) are read from
 			if (!nex) {
 				__syncthreads();
 			} else {
 				s_ex[tid] = exreg;
-				// exceptions before the end of this tile = staged positions below j_hi
-				const uint32_t k = (uint32_t) __syncthreads_count(exreg.x < j_hi);
-				if (k < NT) {
-					e_hi = e_lo + k;
+				// staged exceptions before the end of each subtile (one barrier for both counts)
+				const uint32_t c1 = __popc(__ballot_sync(0xffffffffu, exreg.x < j1));
+				const uint32_t c2 = __popc(__ballot_sync(0xffffffffu, exreg.x < j2));
+				if (lane == 0)
+					s_cnt[warp] = c1 | (c2 << 16);
+				__syncthreads();
+				uint32_t k = 0;
+#pragma unroll
+				for (int w = 0; w < NW; w++)
+					k += s_cnt[w];
+				const uint32_t k1 = k & 0xffffu, k2 = k >> 16;
+				if (k2 < NT) {
+					e_mid = e_lo + k1;
+					e_hi = e_lo + k2;
 					xs = s_ex - e_lo;
-				} else {	// more than 255 in one tile: lower_bound over the whole list
-					if (tid == 0) {
+				} else {	// more than 255 in one step: lower_bound over the whole list
+					if (tid < 2) {
+						const uint32_t key = tid ? j2 : j1;
 						uint32_t lo = e_lo, hi = nex;
 						while (lo < hi) {
 							const uint32_t mid = (lo + hi) >> 1;
-							if (ex[mid].x < j_hi)
+							if (ex[mid].x < key)
 								lo = mid + 1;
 							else
 								hi = mid;
 						}
-						s_e = lo;
+						s_e[tid] = lo;
 					}
 					__syncthreads();
-					e_hi = s_e;
+					e_mid = s_e[0];
+					e_hi = s_e[1];
 				}
 			}
-			if (t + 1 < nt) {
-				issue((t + 1) & 1, j_hi, j_nx, e_hi);
+			if (t + 1 < nsteps) {
+				issue((t + 1) & 1, j2, vb(2 * t + 4), e_hi);
 				if (nex)
 					issue_ex(e_hi);
 			}
-			// ---- zd values of the thread's 16 elements
-			const uint64_t ka = A + (uint64_t) t * XG + 2 * tid;
-			const int64_t f = (int64_t) t * XT - m;		// read index of the tile's first element
-			const bool interior = t >= 1 && t < t_hi;
-			const uint32_t valid = interior ? 0xffffu
-							: group_valid(ka, off0, rend) | (group_valid(ka + 1, off0, rend) << 8);
-			const int64_t i0 = f + 16 * tid;
-			uint32_t zz[8];
-			const uint8_t *st = s_stage + al;
-			if (interior && e_hi == e_lo) {
-				// no exception in the tile: the thread's 16 payload bytes sit at stage[al + 16 tid]
-				stage_bytes16(s_stage, al, tid, zz);
-			} else {
-#pragma unroll
-				for (int j = 0; j < 8; j++)
-					zz[j] = 0;
-				if (valid) {
-					const int64_t jf = i0 + (__ffs(valid) - 1) - 1;	// v-index of the first valid element (-1: zd0)
-					uint32_t e = e_lo;
-					if (e_hi > e_lo) {
-						uint32_t lo = e_lo, hi = e_hi;
-						const int64_t key = jf < 0 ? 0 : jf;
-						while (lo < hi) {
-							const uint32_t mid = (lo + hi) >> 1;
-							if ((int64_t) xs[mid].x < key)
-								lo = mid + 1;
-							else
-								hi = mid;
-						}
-						e = lo;
-					}
-					uint32_t nextpos = e < e_hi ? xs[e].x : 0xffffffffu;
-					if (valid == 0xffffu && jf >= 0 && (uint64_t) nextpos >= (uint64_t) jf + 16) {
-						// no exception among the thread's 16 values: 16 payload bytes in a row
-						const uint32_t pp = al + ((uint32_t) jf - e - p_lo);
-						const uint32_t *w32 = reinterpret_cast<const uint32_t *>(s_stage) + (pp >> 2);
-						const uint32_t sh = (pp & 3) * 8;
-						uint32_t w[5];
-#pragma unroll
-						for (int j = 0; j < 5; j++)
-							w[j] = w32[j];
-#pragma unroll
-						for (int j = 0; j < 4; j++) {
-							const uint32_t v = __funnelshift_r(w[j], w[j + 1], sh);
-							zz[2 * j] = __byte_perm(v, 0, 0x4140);
-							zz[2 * j + 1] = __byte_perm(v, 0, 0x4342);
-						}
-					} else
-#pragma unroll
-					for (int el = 0; el < 16; el++) {
-						if ((valid >> el) & 1) {
-							const int64_t j = i0 + el - 1;
-							uint32_t z;
-							if (j < 0) {
-								z = zd0;
-							} else if ((uint32_t) j == nextpos) {
-								z = xs[e].y;
-								e++;
-								nextpos = e < e_hi ? xs[e].x : 0xffffffffu;
-							} else {
-								z = st[(uint32_t) j - e - p_lo];
-							}
-							zz[el >> 1] |= (z & 0xffffu) << (16 * (el & 1));
-						}
-					}
-				}
-			}
-			// ---- unzigzag, running sum inside the thread (mod 2^16 in each half), then over the CTA
-			uint32_t y[8], c = 0;
-#pragma unroll
-			for (int j = 0; j < 8; j++) {
-				const uint32_t d = unzigzag16x2(zz[j]);
-				y[j] = add16x2(d * 0x00010001u, c);
-				c = __byte_perm(y[j], 0, 0x3232);
-			}
-			uint32_t c1[1] = {c & 0xffffu}, ex1[1], tot;
-			block_scan<1>(c1, ex1, tot, s_warp);
-			const uint32_t cw = ((ex1[0] + carry) & 0xffffu) * 0x00010001u;
-			uint32_t o[8];
-#pragma unroll
-			for (int j = 0; j < 8; j++) {
-				o[j] = add16x2(y[j], cw);
-				if (q)
-					o[j] = shl16x2(o[j], q);	// ex_zd.c:396-401
-			}
+			uint32_t y[2][8], sums = 0, valid2 = 0;
 #pragma unroll
 			for (int h = 0; h < 2; h++) {
-				const uint32_t vm = (valid >> (8 * h)) & 0xffu;
-				if (vm == 0xffu) {
-					out4[ka + h] = make_uint4(o[4 * h], o[4 * h + 1], o[4 * h + 2], o[4 * h + 3]);
-				} else if (vm) {
+				const uint32_t tt = 2 * t + h;
+				const uint32_t el = h ? e_mid : e_lo, eh = h ? e_hi : e_mid, jl = h ? j1 : j0;
+				const uint64_t ka = A + (uint64_t) tt * XG + 2 * tid;
+				const int64_t f = (int64_t) tt * XT - m;		// read index of the subtile's first element
+				const bool interior = tt >= 1 && tt < t_hi4;
+				const uint32_t valid = interior ? 0xffffu
+								: tt < nt4 ? group_valid(ka, off0, rend) | (group_valid(ka + 1, off0, rend) << 8) : 0u;
+				valid2 |= valid << (16 * h);
+				const int64_t i0 = f + 16 * tid;
+				uint32_t d[8];
+				const uint32_t rel = (jl - el) - p_lo;	// stage offset of the subtile's first payload byte
+				if (interior && eh == el) {
+					// no exception in the subtile: the thread's 16 payload bytes sit at stage[al + rel + 16 tid]
+					uint32_t w[4];
+					if ((rel & 15) == 0)
+						stage_words_aligned(s_stage + rel, al, tid, w);
+					else
+						stage_words_any(s_stage, al + rel + 16 * tid, w);
+					unzigzag_bytes_x16(w, d);
+				} else {
+					uint32_t zz[8];
 #pragma unroll
-					for (int e = 0; e < 8; e++)
-						if ((vm >> e) & 1)
-							out16[8 * (ka + h) + e] = (uint16_t) (o[4 * h + (e >> 1)] >> (16 * (e & 1)));
+					for (int j = 0; j < 8; j++)
+						zz[j] = 0;
+					bool bytes = false;
+					if (valid) {
+						const int64_t jf = i0 + (__ffs(valid) - 1) - 1;	// v-index of the first valid element (-1: zd0)
+						uint32_t e = el;
+						if (eh > el) {
+							uint32_t lo = el, hi = eh;
+							const int64_t key = jf < 0 ? 0 : jf;
+							while (lo < hi) {
+								const uint32_t mid = (lo + hi) >> 1;
+								if ((int64_t) xs[mid].x < key)
+									lo = mid + 1;
+								else
+									hi = mid;
+							}
+							e = lo;
+						}
+						uint32_t nextpos = e < eh ? xs[e].x : 0xffffffffu;
+						if (valid == 0xffffu && jf >= 0 && (uint64_t) nextpos >= (uint64_t) jf + 16) {
+							// no exception among the thread's 16 values: 16 payload bytes in a row
+							uint32_t w[4];
+							stage_words_any(s_stage, al + ((uint32_t) jf - e - p_lo), w);
+							unzigzag_bytes_x16(w, d);
+							bytes = true;
+						} else {
+							const uint8_t *st = s_stage + al;
+#pragma unroll
+							for (int el16 = 0; el16 < 16; el16++) {
+								if ((valid >> el16) & 1) {
+									const int64_t j = i0 + el16 - 1;
+									uint32_t z;
+									if (j < 0) {
+										z = zd0;
+									} else if ((uint32_t) j == nextpos) {
+										z = xs[e].y;
+										e++;
+										nextpos = e < eh ? xs[e].x : 0xffffffffu;
+									} else {
+										z = st[(uint32_t) j - e - p_lo];
+									}
+									zz[el16 >> 1] |= (z & 0xffffu) << (16 * (el16 & 1));
+								}
+							}
+						}
+					}
+					if (!bytes) {
+#pragma unroll
+						for (int j = 0; j < 8; j++)
+							d[j] = unzigzag16x2(zz[j]);
+					}
+				}
+				// running sum inside the thread (mod 2^16 in each half), then over the CTA
+				uint32_t c = 0;
+#pragma unroll
+				for (int j = 0; j < 8; j++) {
+					y[h][j] = add16x2(d[j] * 0x00010001u, c);
+					c = __byte_perm(y[h][j], 0, 0x3232);
+				}
+				sums |= (c & 0xffffu) << (16 * h);
+			}
+			uint32_t e2, tot2;
+			block_scan_pair(sums, e2, tot2, s_warp);
+			const uint32_t cwa = ((e2 + carry) & 0xffffu) * 0x00010001u;
+			const uint32_t cwb = (((e2 >> 16) + tot2 + carry) & 0xffffu) * 0x00010001u;
+#pragma unroll
+			for (int h = 0; h < 2; h++) {
+				const uint32_t cw = h ? cwb : cwa;
+				const uint64_t ka = A + (uint64_t) (2 * t + h) * XG + 2 * tid;
+#pragma unroll
+				for (int g = 0; g < 2; g++) {
+					const uint32_t vm = (valid2 >> (16 * h + 8 * g)) & 0xffu;
+					uint32_t o[4];
+#pragma unroll
+					for (int j = 0; j < 4; j++) {
+						o[j] = add16x2(y[h][4 * g + j], cw);
+						if (q)
+							o[j] = shl16x2(o[j], q);	// ex_zd.c:396-401
+					}
+					if (vm == 0xffu) {
+						out4[ka + g] = make_uint4(o[0], o[1], o[2], o[3]);
+					} else if (vm) {
+#pragma unroll
+						for (int e = 0; e < 8; e++)
+							if ((vm >> e) & 1)
+								out16[8 * (ka + g) + e] = (uint16_t) (o[e >> 1] >> (16 * (e & 1)));
+					}
 				}
 			}
-			carry = (carry + tot) & 0xffffu;
+			carry = (carry + (tot2 & 0xffffu) + (tot2 >> 16)) & 0xffffu;
 			e_lo = e_hi;
-			// (no barrier here: the stage and s_ex are read before the scan's barrier and
-			//  rewritten after it; s_warp is rewritten after the next tile's first barrier)
+			// (no barrier here: the stage and s_ex are read before the scan's barrier and rewritten
+			//  after it; s_warp / s_cnt are rewritten after the next step's first barrier)
 		}
 	}
 }

@@ -104,77 +104,6 @@ __device__ __forceinline__ uint32_t dec_keys_flags(const KeyRaw &k)
 
 constexpr int DT2 = 2 * DT;	// samples per step
 
-// exclusive scan over the CTA of two 16-bit values per thread (low / high half, each mod 2^16);
-// one __syncthreads(), s_warp as for block_scan
-__device__ __forceinline__ void block_scan16x2(uint32_t v, uint32_t &excl, uint32_t &total, uint32_t *s_warp)
-{
-	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	uint32_t x = v;
-#pragma unroll
-	for (int o = 1; o < 32; o <<= 1) {
-		const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-		if (lane >= o)
-			x = add16x2(x, y);
-	}
-	if (lane == 31)
-		s_warp[warp] = x;
-	__syncthreads();
-	const uint32_t t = s_warp[lane & 7];
-	uint32_t s = t;
-#pragma unroll
-	for (int o = 1; o < 8; o <<= 1) {
-		const uint32_t y = __shfl_up_sync(0xffffffffu, s, o);
-		if ((lane & 7) >= o)
-			s = add16x2(s, y);
-	}
-	const uint32_t before = __shfl_sync(0xffffffffu, sub16x2(s, t), warp);
-	total = __shfl_sync(0xffffffffu, s, 7);
-	excl = add16x2(before, sub16x2(x, v));
-}
-
-// 16 one-byte zigzag values (four per word) -> deltas, two per word, sign extended:
-// (b >> 1) ^ -(b & 1) on every byte (trans.c:80-83), then widened
-__device__ __forceinline__ void unzigzag_bytes16(const uint32_t (&w)[4], uint32_t (&d)[8])
-{
-#pragma unroll
-	for (int j = 0; j < 4; j++) {
-		const uint32_t u = ((w[j] >> 1) & 0x7f7f7f7fu) ^ ((w[j] & 0x01010101u) * 0xffu);
-		asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d[2 * j]) : "r"(u), "r"(0u), "r"(0x9180u));
-		asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d[2 * j + 1]) : "r"(u), "r"(0u), "r"(0xb3a2u));
-	}
-}
-
-// four words holding the 16 bytes at stage[off .. off + 16), off = al + 16 tid with al the same in
-// every thread (two conflict-free 128-bit loads), or at any offset (five 32-bit loads)
-__device__ __forceinline__ void stage_words_aligned(const uint8_t *stage, uint32_t al, int tid, uint32_t (&w)[4])
-{
-	const uint4 a = reinterpret_cast<const uint4 *>(stage)[tid], b = reinterpret_cast<const uint4 *>(stage)[tid + 1];
-	uint32_t u0, u1, u2, u3, u4;
-	switch (al >> 2) {
-	case 0: u0 = a.x; u1 = a.y; u2 = a.z; u3 = a.w; u4 = b.x; break;
-	case 1: u0 = a.y; u1 = a.z; u2 = a.w; u3 = b.x; u4 = b.y; break;
-	case 2: u0 = a.z; u1 = a.w; u2 = b.x; u3 = b.y; u4 = b.z; break;
-	default: u0 = a.w; u1 = b.x; u2 = b.y; u3 = b.z; u4 = b.w; break;
-	}
-	const uint32_t sh = (al & 3) * 8;
-	w[0] = __funnelshift_r(u0, u1, sh);
-	w[1] = __funnelshift_r(u1, u2, sh);
-	w[2] = __funnelshift_r(u2, u3, sh);
-	w[3] = __funnelshift_r(u3, u4, sh);
-}
-__device__ __forceinline__ void stage_words_any(const uint8_t *stage, uint32_t p, uint32_t (&w)[4])
-{
-	const uint32_t *w32 = reinterpret_cast<const uint32_t *>(stage) + (p >> 2);
-	const uint32_t sh = (p & 3) * 8;
-	uint32_t u[5];
-#pragma unroll
-	for (int j = 0; j < 5; j++)
-		u[j] = w32[j];
-#pragma unroll
-	for (int j = 0; j < 4; j++)
-		w[j] = __funnelshift_r(u[j], u[j + 1], sh);
-}
-
 template <int KEYBITS, bool FRAME>
 #ifndef PG_DEC_CTAS
 #define PG_DEC_CTAS 4
@@ -290,7 +219,7 @@ __global__ void __launch_bounds__(NT, PG_DEC_CTAS) svb_dec2_kernel(const __grid_
 			const uint32_t c = (uint32_t) (__popc(va & 0xffffu) + __popc(fl & 0xffffu)) |
 					   ((uint32_t) (__popc(va >> 16) + __popc(fl >> 16)) << 16);
 			uint32_t e, tot;
-			block_scan16x2(c, e, tot, s_warp);
+			block_scan_pair(c, e, tot, s_warp);
 			exa = e & 0xffffu;
 			exb = (tot & 0xffffu) + (e >> 16);
 			L = (tot & 0xffffu) + (tot >> 16);
@@ -351,11 +280,11 @@ __global__ void __launch_bounds__(NT, PG_DEC_CTAS) svb_dec2_kernel(const __grid_
 					// whole step of one-byte values: the thread's 16 bytes sit at stage[al + h DT + 16 tid]
 					uint32_t w[4];
 					stage_words_aligned(s_in + h * DT, al, tid, w);
-					unzigzag_bytes16(w, d);
+					unzigzag_bytes_x16(w, d);
 				} else if (vah == 0xffffu && flh == 0) {
 					uint32_t w[4];
 					stage_words_any(s_in, p, w);
-					unzigzag_bytes16(w, d);
+					unzigzag_bytes_x16(w, d);
 				} else {
 					const uint8_t *q = s_in + p;
 					uint32_t zz[8];
@@ -385,7 +314,7 @@ __global__ void __launch_bounds__(NT, PG_DEC_CTAS) svb_dec2_kernel(const __grid_
 				sums |= (c & 0xffffu) << (16 * h);
 			}
 			uint32_t e2, tot2;
-			block_scan16x2(sums, e2, tot2, s_warp2);
+			block_scan_pair(sums, e2, tot2, s_warp2);
 			const uint32_t cwa = ((e2 + carry) & 0xffffu) * 0x00010001u;
 			const uint32_t cwb = (((e2 >> 16) + tot2 + carry) & 0xffffu) * 0x00010001u;
 #pragma unroll
