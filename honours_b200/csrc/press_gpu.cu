@@ -89,8 +89,14 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 int ensure_init()
 {
-	if (g_ctx.ready)
+	if (g_ctx.ready) {
+		// a host thread other than the one that called press_gpu_init starts on device 0: the
+		// library's streams and buffers live on g_ctx.device
+		int d = -1;
+		if (cudaGetDevice(&d) != cudaSuccess || d != g_ctx.device)
+			CK(cudaSetDevice(g_ctx.device));
 		return 0;
+	}
 	return press_gpu_init(-1);
 }
 
