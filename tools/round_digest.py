@@ -12,10 +12,13 @@ import profile_digest as pd
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 G = os.path.join(ROOT, "gpurun_out")
-P = os.path.join(ROOT, "profiles")
 tag = sys.argv[1]
+# (on the GPU box the digests go to a directory under gpurun_out/, the only one that travels back;
+#  the .ncu-rep files themselves are too large to bring home)
+P = os.path.abspath(sys.argv[2]) if len(sys.argv) > 2 else os.path.join(ROOT, "profiles")
+os.makedirs(P, exist_ok=True)
 METHODS = ["svb16_zd", "svb_zd", "vbz_svb16_zd", "vbz_svb_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd",
-           "shuff_vbsse21_zd", "vbbe21_zd", "shuff_vbbe21_zd"]
+           "shuff_vbsse21_zd", "vbbe21_zd", "shuff_vbbe21_zd", "svb0124_zd", "uint_zd", "shuff_vbe21_zd_nosidecar"]
 
 
 def last_json(path):
@@ -35,8 +38,8 @@ for a, b in [(f"pytest_gpu_{tag}.log", f"{tag}_pytest_gpu.log"), (f"smoke_{tag}.
 
 pd.launches(os.path.join(G, f"launches_svb16_zd_{tag}.csv"), os.path.join(P, f"{tag}_svb16_zd_launches.txt"))
 pd.kernels(os.path.join(G, f"prof_svb16_zd_{tag}.ncu-rep"), os.path.join(P, f"{tag}_svb16_zd_kernels.txt"))
-caps = {"vbe21_zd": ["ex_count", "ex_emit_bytes", "ex_decode"],
-        "shuff_vbe21_zd": ["ex_count", "ex_emit_kernel", "huff_decode"]}
+caps = {"vbe21_zd": ["ex_count", "ex_emit_bytes", "ex_decode2"],
+        "shuff_vbe21_zd": ["ex_count", "ex_emit_kernel", "huff_fused"]}
 for m, ks in caps.items():
     lc = os.path.join(G, f"launches_{m}_{tag}.csv")
     if os.path.exists(lc):
@@ -83,18 +86,17 @@ try:
     NS8K = b["config"]["samples_per_gpu"]
     alg8 = b["kernels"]["encode"]["alg_bytes_per_launch"]
     kf = os.path.join(P, f"{tag}_svb16_zd_kernels.txt")
-    for nm, kname in (("encode", "svb_enc_kernel"), ("decode", "svb_dec_kernel")):
+    for nm, kname in (("encode", "svb_enc_kernel"), ("decode", "svb_dec2_kernel")):
         traffic[f"svb16_zd_{nm}"] = {"dram_bytes": dram(kf, kname), "alg_bytes": alg8,
                                      "source": f"profiles/{tag}_svb16_zd_kernels.txt (ncu --set full, bench.py --reads 8000, {kname}<1,0>)"}
 except Exception as e:
     print("svb16 traffic:", e)
-for m, enc, dec, bps in (("vbe21_zd", ["ex_count", "ex_emit_bytes"], ["ex_decode"], 1.0002),
-                         ("shuff_vbe21_zd", ["ex_count", "ex_emit_kernel"], ["huff_decode", "ex_decode"], 0.6788)):
+for m, enc, dec, bps in (("vbe21_zd", ["ex_count", "ex_emit_bytes"], ["ex_decode2"], 1.0002),
+                         ("shuff_vbe21_zd", ["ex_count", "ex_emit_kernel"], ["huff_fused"], 0.6788)):
     try:
         alg = (2.0 + bps) * NS20K
         for nm, ks in (("encode", enc), ("decode", dec)):
-            # (the Huffman methods' ex_decode is the kernel captured under vbe21_zd)
-            tot = sum(dram(os.path.join(P, f"{tag}_{'vbe21_zd' if k == 'ex_decode' else m}_{k}_kernels.txt")) for k in ks)
+            tot = sum(dram(os.path.join(P, f"{tag}_{m}_{k}_kernels.txt")) for k in ks)
             traffic[f"{m}_{nm}"] = {"dram_bytes": tot, "alg_bytes": alg,
                                     "source": f"profiles/{tag}_{m}_*_kernels.txt (ncu --set full, bench.py --method {m} --reads 20000; "
                                               + " + ".join(ks) + ")"}

@@ -3,7 +3,7 @@
 TAG=${1:-r01b}; READS=${2:-20000}
 mkdir -p gpurun_out
 for p in 0 4.28e-5 1e-3 1e-2 1e-1 0.5; do
-  timeout 900 python bench.py --method ex_zd --reads $READS --p-ex $p --steps 2 --warmup 1 --no-e2e --no-cpu-baseline \
+  timeout 900 python bench.py --method ex_zd --reads $READS --p-ex $p --steps 2 --warmup 1 --methods= --no-e2e --no-cpu-baseline \
       > gpurun_out/sweep_ex_zd_${p}_$TAG.json 2> gpurun_out/sweep_ex_zd_${p}_$TAG.err
   python - <<PY
 import json
