@@ -71,7 +71,25 @@ struct ExArgs {
 	uint64_t pool_cap;
 	const uint32_t *huff_enc;	// 256 x (code | length << 24)
 	uint16_t *sidecar;		// HUFF, optional: see huff_fused.cuh (null: none)
+	uint8_t *lowb;			// byte payloads: low bytes of the zd values of every tile that lies inside
+					// a read, as sweep 1 computed them (1 B/sample; see ex_lowb_ptr)
 };
+
+// Sweep 1 leaves the 16 low bytes of a thread's zd values where sweep 2 finds them with one aligned
+// 128-bit load: tile t of the read whose first 16-byte sample group is A, thread tid.  (Only slices
+// (512 samples, one warp) wholly inside a read are kept: they share no sample group with another read; the 8-byte
+// phase of A is taken out so that the address is 16-byte aligned.)
+__device__ __forceinline__ uint4 *ex_lowb_ptr(uint8_t *lowb, uint64_t A, uint32_t t, int tid)
+{
+	return reinterpret_cast<uint4 *>(lowb + 8 * (A + (A & 1))) + (uint64_t) t * (XT / 16) + tid;
+}
+
+// ask L2 for the line holding p (no register waits for it): the walks below keep one tile in
+// registers and two more on their way from HBM
+__device__ __forceinline__ void prefetch_l2(const void *p)
+{
+	asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
 
 // per-halfword arithmetic shift right (ex_zd.c:383-394 on int16)
 __device__ __forceinline__ uint32_t sar16x2(uint32_t x, uint32_t q)
@@ -516,7 +534,6 @@ __global__ void __launch_bounds__(NT, 5) ex_count_kernel(const __grid_constant__
 		const uint64_t n = T.rend - T.off0, A = T.off0 >> 3;
 		const uint32_t nt = T.ntiles;
 		const uint64_t rec0 = (uint64_t) g0 * NW;
-		const uint32_t t_hi = (uint32_t) ((T.m + n) / XT);	// tiles [1, t_hi) lie inside the read
 		uint32_t q = 0, bits_thr = 0;
 		for (int pass = 0; pass < 2; pass++) {
 			// the walk: no CTA barrier, every warp runs through its 512-sample slice of every tile
@@ -531,12 +548,20 @@ __global__ void __launch_bounds__(NT, 5) ex_count_kernel(const __grid_constant__
 				const ExRaw C = W;
 				if (t + 1 < nt)
 					ex_issue(a.samples, a.nsamples, T.k0 + XG, W);
+				if (t + 3 < nt)
+					prefetch_l2(a.samples + T.k0 + 3 * XG + 2 * tid);
 				ExVals v;
-				if (t >= 1 && t < t_hi) {
+				// (the warp's 512-sample slice lies inside the read, past its first sample)
+				const int64_t f = (int64_t) t * XT - T.m + 512 * warp;
+				if (f >= 1 && f + 512 <= (int64_t) n) {
 					uint32_t orw;
 					(void) ex_compute_fast(C, q, v, orw);
 					or_thr |= orw;
 					v.i0 = (int64_t) t * XT - T.m + 16 * tid;
+					if (!HUFF)	// (ex-zd: the pass with the final q comes last)
+						*ex_lowb_ptr(a.lowb, A, t, tid) =
+							make_uint4(__byte_perm(v.z[0], v.z[1], 0x6420), __byte_perm(v.z[2], v.z[3], 0x6420),
+								   __byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420));
 				} else {
 					ex_compute(C, T, q, v);
 					or_thr |= v.orv;
@@ -863,9 +888,72 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_kernel(const __grid_constant__ 
 // A warp knows where its 512-sample slice goes from the record prefix alone
 // (values before the slice minus exceptions before the slice), so the eight warps
 // of the CTA run through the read independently.  A slice without exception inside
-// the read is 32 x 16 bytes: re-phased to the destination's 16-byte alignment with
-// shuffles and stored as aligned 128-bit words; anything else goes through a
-// per-warp staging line.
+// the read is 32 x 16 low bytes as sweep 1 left them (ex_lowb_ptr): one aligned
+// 128-bit load per lane, re-phased to the destination's 16-byte alignment with
+// shuffles and stored as aligned 128-bit words; anything else is computed again
+// from the samples and goes through a per-warp staging line.
+
+// 32 lanes x 16 payload bytes (qv) -> D[0, 512), any alignment
+__device__ __forceinline__ void ex_store_slice(const uint32_t (&qv)[4], uint8_t *D, int lane)
+{
+	const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(D) & 15);
+	if (s == 0) {
+		reinterpret_cast<uint4 *>(D)[lane] = make_uint4(qv[0], qv[1], qv[2], qv[3]);
+		return;
+	}
+	uint32_t c[8];
+#pragma unroll
+	for (int j = 0; j < 4; j++) {
+		c[j] = __shfl_up_sync(0xffffffffu, qv[j], 1);
+		c[4 + j] = qv[j];
+	}
+	// aligned word `lane` = bytes [16 - s, 32 - s) of (previous lane's, own) 32 bytes
+	const uint32_t sh = 16 - s, bs = (sh & 3) * 8;
+	uint32_t u0, u1, u2, u3, u4;
+	switch (sh >> 2) {
+	case 0: u0 = c[0]; u1 = c[1]; u2 = c[2]; u3 = c[3]; u4 = c[4]; break;
+	case 1: u0 = c[1]; u1 = c[2]; u2 = c[3]; u3 = c[4]; u4 = c[5]; break;
+	case 2: u0 = c[2]; u1 = c[3]; u2 = c[4]; u3 = c[5]; u4 = c[6]; break;
+	default: u0 = c[3]; u1 = c[4]; u2 = c[5]; u3 = c[6]; u4 = c[7]; break;
+	}
+	uint8_t *Wd = D - s;
+	if (lane > 0)
+		reinterpret_cast<uint4 *>(Wd)[lane] = make_uint4(__funnelshift_r(u0, u1, bs), __funnelshift_r(u1, u2, bs),
+								  __funnelshift_r(u2, u3, bs), __funnelshift_r(u3, u4, bs));
+	// head: the first 16 - s bytes of lane 0; tail: the last s bytes of lane 31
+	uint32_t h[4], tl[4];
+#pragma unroll
+	for (int j = 0; j < 4; j++) {
+		h[j] = __shfl_sync(0xffffffffu, qv[j], 0);
+		tl[j] = __shfl_sync(0xffffffffu, qv[j], 31);
+	}
+	if ((uint32_t) lane < sh) {
+		const uint32_t wv = lane < 4 ? h[0] : lane < 8 ? h[1] : lane < 12 ? h[2] : h[3];
+		D[lane] = (uint8_t) (wv >> (8 * (lane & 3)));
+	}
+	if ((uint32_t) lane < s) {
+		const uint32_t b = sh + lane;	// byte of lane 31's 16
+		const uint32_t wv = b < 4 ? tl[0] : b < 8 ? tl[1] : b < 12 ? tl[2] : tl[3];
+		Wd[512 + lane] = (uint8_t) (wv >> (8 * (b & 3)));
+	}
+}
+
+// the bytes of qv selected by `ne`, lane after lane -> D (through the warp's staging line)
+__device__ __forceinline__ void ex_store_slice_packed(const uint32_t (&qv)[4], uint32_t ne, uint8_t *D, uint8_t *line, int lane)
+{
+	const uint32_t cnt = __popc(ne);
+	const uint32_t inc = warp_inc_scan(cnt, lane);
+	const uint32_t L = __shfl_sync(0xffffffffu, inc, 31);
+	uint8_t *p = line + (reinterpret_cast<uintptr_t>(D) & 7) + inc - cnt;
+#pragma unroll
+	for (int e = 0; e < 16; e++)
+		if ((ne >> e) & 1)
+			*p++ = (uint8_t) ((qv[e >> 2] >> (8 * (e & 3))));
+	__syncwarp();
+	warp_copy_out(line, D, L, lane);
+	__syncwarp();
+}
+
 __global__ void __launch_bounds__(NT, 5) ex_emit_bytes_kernel(const __grid_constant__ ExArgs a)
 {
 	__shared__ __align__(16) uint8_t s_line[NW][512 + 16];
@@ -873,6 +961,7 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_bytes_kernel(const __grid_const
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	if (a.hdr->error & (ERR_CAPACITY | ERR_SCRATCH))
 		return;
+	uint8_t *line = s_line[warp];
 	for (;;) {
 		__syncthreads();
 		if (tid == 0)
@@ -888,99 +977,126 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_bytes_kernel(const __grid_const
 		uint32_t g0;
 		(void) ex_read_tile0(a, r, T, g0);
 		const uint64_t n = T.rend - T.off0, A = T.off0 >> 3;
-		const uint32_t nt = T.ntiles, nex = a.r_nex[r];
+		const uint32_t nt = T.ntiles;
 		const uint32_t q = a.method == PRESS_GPU_EX_ZD ? a.r_q[r] : 0u;
 		const uint64_t rec0 = (uint64_t) g0 * NW + warp;
-		const uint32_t t_hi = (uint32_t) ((T.m + n) / XT);
-		uint8_t *dst = a.out + a.out_offsets[r];
-		ExRaw W;
-		ex_issue(a.samples, a.nsamples, A, W);
-		uint32_t eb_n = __ldg(a.t_eb + rec0), nx_n = __ldg(a.t_nex + rec0);
-		uint8_t *pay = dst + hdr;	// first payload byte of the read
+		uint8_t *pay = a.out + a.out_offsets[r] + hdr;	// first payload byte of the read
 		const int64_t mm = (int64_t) n - 1;
-#pragma unroll 2
-		for (uint32_t t = 0; t < nt; t++) {
+		// a slice at one of the read's ends: samples again, element masks, no prefetch
+		auto edge_slice = [&](uint32_t t) {
+			const int64_t f = (int64_t) t * XT - T.m + 512 * warp;	// read index of the slice's first element
+			if (f >= (int64_t) n)
+				return;
 			T.t = t;
 			T.k0 = A + (uint64_t) t * XG;
-			const ExRaw C = W;
-			const uint32_t eb = eb_n, nx = nx_n;
-			if (t + 1 < nt) {
-				ex_issue(a.samples, a.nsamples, T.k0 + XG, W);
-				eb_n = __ldg(a.t_eb + rec0 + (uint64_t) (t + 1) * NW);
-				nx_n = __ldg(a.t_nex + rec0 + (uint64_t) (t + 1) * NW);
-			}
+			ExRaw C;
+			ex_issue(a.samples, a.nsamples, T.k0, C);
+			const uint32_t eb = __ldg(a.t_eb + rec0 + (uint64_t) t * NW);
 			// values of the read before this slice, minus the exceptions among them
-			int64_t vb = (int64_t) t * XT - T.m + 512 * warp - 1;
-			vb = vb < 0 ? 0 : (vb < mm ? vb : mm);
-			uint8_t *D = pay + ((uint64_t) vb - eb);
-			const bool interior = t >= 1 && t < t_hi;
+			const int64_t vb = f - 1 < 0 ? 0 : (f - 1 < mm ? f - 1 : mm);
 			ExVals v;
-			if (interior) {
-				uint32_t orw;
-				(void) ex_compute_fast(C, q, v, orw);
-			} else {
-				ex_compute(C, T, q, v);
+			ex_compute(C, T, q, v);
+			const uint32_t qv[4] = {__byte_perm(v.z[0], v.z[1], 0x6420), __byte_perm(v.z[2], v.z[3], 0x6420),
+						__byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420)};
+			ex_store_slice_packed(qv, v.valid & ~v.exc & ~v.first, pay + ((uint64_t) vb - eb), line, lane);
+		};
+		edge_slice(0);
+		// tiles [1, t_in): the warp's slice lies inside the read
+		const uint64_t span = T.m + n;
+		const uint32_t t_in = span >= 512u * (warp + 1) ? (uint32_t) ((span - 512u * (warp + 1)) / XT) + 1 : 0u;
+		if (t_in > 1) {
+			// records two tiles ahead, data one tile ahead; every address advances by a constant.
+			// The data of a slice without exception are its low bytes, loaded at the DESTINATION's
+			// 16-byte phase s (five 32-bit words per lane + the < 16 bytes either side), so that
+			// lane j holds the aligned output word j after four funnel shifts; of a slice with
+			// an exception, the samples.
+			const uint8_t *lp = reinterpret_cast<const uint8_t *>(ex_lowb_ptr(a.lowb, A, 1, 32 * warp));
+			const uint4 *sp = a.samples + A + XG + 2 * tid;
+			const uint32_t *pe = a.t_eb + rec0 + NW, *pn = a.t_nex + rec0 + NW;
+			uint8_t *Db = pay + (XT - T.m + 512 * warp - 1);
+			uint32_t eb1 = __ldg(pe), nx1 = __ldg(pn), eb2 = 0, nx2 = 0;
+			if (t_in > 2) {
+				eb2 = __ldg(pe + NW);
+				nx2 = __ldg(pn + NW);
 			}
-			uint32_t qv[4] = {__byte_perm(v.z[0], v.z[1], 0x6420), __byte_perm(v.z[2], v.z[3], 0x6420),
-					  __byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420)};
-			if (interior && nx == 0) {
-				const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(D) & 15);
-				if (s == 0) {
-					reinterpret_cast<uint4 *>(D)[lane] = make_uint4(qv[0], qv[1], qv[2], qv[3]);
+			uint32_t W[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+			auto issue = [&](uint32_t nx, const uint8_t *D) {
+				if (nx == 0) {
+					const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(D) & 15);
+					if (lane > 0 || s == 0) {
+						const uint32_t *p = reinterpret_cast<const uint32_t *>(lp + ((16 * lane - (int) s) & ~3));
+#pragma unroll
+						for (int k = 0; k < 5; k++)
+							W[k] = __ldcs(p + k);
+					}
+					if (s && (uint32_t) lane < 16 - s)
+						W[5] = __ldcs(lp + lane);
+					if ((uint32_t) lane < s)
+						W[6] = __ldcs(lp + 512 - s + lane);
 				} else {
-					uint32_t c[8];
+					const uint4 xa = __ldg(sp), xb = __ldg(sp + 1);
+					W[0] = xa.x; W[1] = xa.y; W[2] = xa.z; W[3] = xa.w;
+					W[4] = xb.x; W[5] = xb.y; W[6] = xb.z; W[7] = xb.w;
+					if (lane == 0)
+						W[8] = __ldg(reinterpret_cast<const uint16_t *>(sp) - 1);
+				}
+			};
+			issue(nx1, Db - eb1);
+			if (t_in > 2)
+				prefetch_l2(lp + XT + 16 * lane);
+			if (t_in > 3)
+				prefetch_l2(lp + 2 * XT + 16 * lane);
+#pragma unroll 2
+			for (uint32_t t = 1; t < t_in; t++) {
+				uint32_t C[9];
 #pragma unroll
-					for (int j = 0; j < 4; j++) {
-						c[j] = __shfl_up_sync(0xffffffffu, qv[j], 1);
-						c[4 + j] = qv[j];
-					}
-					// aligned word `lane` = bytes [16 - s, 32 - s) of (previous lane's, own) 32 bytes
-					const uint32_t sh = 16 - s, bs = (sh & 3) * 8;
-					uint32_t u0, u1, u2, u3, u4;
-					switch (sh >> 2) {
-					case 0: u0 = c[0]; u1 = c[1]; u2 = c[2]; u3 = c[3]; u4 = c[4]; break;
-					case 1: u0 = c[1]; u1 = c[2]; u2 = c[3]; u3 = c[4]; u4 = c[5]; break;
-					case 2: u0 = c[2]; u1 = c[3]; u2 = c[4]; u3 = c[5]; u4 = c[6]; break;
-					default: u0 = c[3]; u1 = c[4]; u2 = c[5]; u3 = c[6]; u4 = c[7]; break;
-					}
-					uint8_t *Wd = D - s;
-					if (lane > 0)
-						reinterpret_cast<uint4 *>(Wd)[lane] =
-							make_uint4(__funnelshift_r(u0, u1, bs), __funnelshift_r(u1, u2, bs),
-								   __funnelshift_r(u2, u3, bs), __funnelshift_r(u3, u4, bs));
-					// head: the first 16 - s bytes of lane 0; tail: the last s bytes of lane 31
-					uint32_t h[4], tl[4];
-#pragma unroll
-					for (int j = 0; j < 4; j++) {
-						h[j] = __shfl_sync(0xffffffffu, qv[j], 0);
-						tl[j] = __shfl_sync(0xffffffffu, qv[j], 31);
-					}
-					if ((uint32_t) lane < sh) {
-						const uint32_t wv = lane < 4 ? h[0] : lane < 8 ? h[1] : lane < 12 ? h[2] : h[3];
-						D[lane] = (uint8_t) (wv >> (8 * (lane & 3)));
-					}
-					if ((uint32_t) lane < s) {
-						const uint32_t b = sh + lane;	// byte of lane 31's 16
-						const uint32_t wv = b < 4 ? tl[0] : b < 8 ? tl[1] : b < 12 ? tl[2] : tl[3];
-						Wd[512 + lane] = (uint8_t) (wv >> (8 * (b & 3)));
+				for (int k = 0; k < 9; k++)
+					C[k] = W[k];
+				const uint32_t eb = eb1, nx = nx1;
+				uint8_t *D = Db - eb;
+				eb1 = eb2;
+				nx1 = nx2;
+				lp += XT;
+				sp += XG;
+				pe += NW;
+				pn += NW;
+				Db += XT;
+				if (t + 3 < t_in)
+					prefetch_l2(lp + 2 * XT + 16 * lane);
+				if (t + 1 < t_in) {
+					issue(nx1, Db - eb1);
+					if (t + 2 < t_in) {
+						eb2 = __ldg(pe + NW);
+						nx2 = __ldg(pn + NW);
 					}
 				}
-			} else {
-				const uint32_t ne = v.valid & ~v.exc & ~v.first;
-				const uint32_t cnt = __popc(ne);
-				const uint32_t inc = warp_inc_scan(cnt, lane);
-				const uint32_t L = __shfl_sync(0xffffffffu, inc, 31);
-				uint8_t *line = s_line[warp];
-				uint8_t *p = line + (reinterpret_cast<uintptr_t>(D) & 7) + inc - cnt;
-#pragma unroll
-				for (int e = 0; e < 16; e++)
-					if ((ne >> e) & 1)
-						*p++ = (uint8_t) ((qv[e >> 2] >> (8 * (e & 3))));
-				__syncwarp();
-				warp_copy_out(line, D, L, lane);
-				__syncwarp();
+				if (nx == 0) {
+					const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(D) & 15), bs = ((16 - s) & 3) * 8;
+					uint8_t *Wd = D - s;
+					if (lane > 0 || s == 0)
+						reinterpret_cast<uint4 *>(Wd)[lane] =
+							make_uint4(__funnelshift_r(C[0], C[1], bs), __funnelshift_r(C[1], C[2], bs),
+								   __funnelshift_r(C[2], C[3], bs), __funnelshift_r(C[3], C[4], bs));
+					if (s && (uint32_t) lane < 16 - s)
+						D[lane] = (uint8_t) C[5];
+					if ((uint32_t) lane < s)
+						Wd[512 + lane] = (uint8_t) C[6];
+				} else {
+					ExRaw R;
+					R.xa = make_uint4(C[0], C[1], C[2], C[3]);
+					R.xb = make_uint4(C[4], C[5], C[6], C[7]);
+					R.prev0 = C[8];
+					ExVals v;
+					uint32_t orw;
+					(void) ex_compute_fast(R, q, v, orw);
+					const uint32_t qv[4] = {__byte_perm(v.z[0], v.z[1], 0x6420), __byte_perm(v.z[2], v.z[3], 0x6420),
+								__byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420)};
+					ex_store_slice_packed(qv, ~v.exc & 0xffffu, D, line, lane);
+				}
 			}
 		}
+		for (uint32_t t = t_in > 1 ? t_in : 1u; t < nt; t++)
+			edge_slice(t);
 	}
 }
 

@@ -144,9 +144,10 @@ ScratchLayout scratch_layout(int method, uint64_t nreads, uint64_t nsamples, dou
 		}
 		l.x_r8[0] = o;		o += align_up((nreads + 1) * 8, 256);
 		l.x_r8[1] = o;		o += align_up((nreads + 1) * 8, 256);
+		// 1 B/sample: Huffman methods, decode without a side-car: the payload between bit decode and
+		// sample decode; byte-payload methods, encode: the low bytes sweep 1 leaves for sweep 2
 		l.x_paybuf = o;
-		if (ex_is_huff(method))
-			o += align_up(nsamples + 64, 256);
+		o += align_up(nsamples + 128, 256);
 		l.x_pool = o;
 		if (pool_frac < 0)
 			pool_frac = default_pool_frac();
