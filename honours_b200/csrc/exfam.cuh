@@ -35,6 +35,12 @@ namespace pg {
 constexpr int XT = 4096;		// samples per tile
 constexpr int XG = XT / 8;		// 16-byte groups per tile
 constexpr uint32_t X_FAIL = 0xffffffffu;	// r_hdr of a read that has no stream (empty, ex-zd cap)
+#ifndef PG_PF_COUNT
+#define PG_PF_COUNT 3	// sweep 1: tiles ahead of the walk asked from L2
+#endif
+#ifndef PG_PF_EMIT
+#define PG_PF_EMIT 3	// sweep 2
+#endif
 constexpr int X_STAGE = 24 * XT / 8 + 64;	// payload stage: 4096 codes of the longest length accepted
 						// (24 bits, press_gpu_set_huffman_table), + phase + slack
 
@@ -498,8 +504,11 @@ __device__ __forceinline__ bool ex_read_tile0(const ExArgs &a, uint64_t r, ExTil
 // ---------------------------------------------------------------------------
 // sweep 1: counts, exception capture, stream size
 
+#ifndef PG_COUNT_CTAS
+#define PG_COUNT_CTAS 4
+#endif
 template <bool HUFF>
-__global__ void __launch_bounds__(NT, 5) ex_count_kernel(const __grid_constant__ ExArgs a)
+__global__ void __launch_bounds__(NT, PG_COUNT_CTAS) ex_count_kernel(const __grid_constant__ ExArgs a)
 {
 	__shared__ __align__(16) uint32_t s_warp[NW];
 	__shared__ uint32_t s_read, s_or, s_nex, s_base2;
@@ -548,8 +557,8 @@ __global__ void __launch_bounds__(NT, 5) ex_count_kernel(const __grid_constant__
 				const ExRaw C = W;
 				if (t + 1 < nt)
 					ex_issue(a.samples, a.nsamples, T.k0 + XG, W);
-				if (t + 3 < nt)
-					prefetch_l2(a.samples + T.k0 + 3 * XG + 2 * tid);
+				if (t + PG_PF_COUNT < nt)
+					prefetch_l2(a.samples + T.k0 + PG_PF_COUNT * XG + 2 * tid);
 				ExVals v;
 				// (the warp's 512-sample slice lies inside the read, past its first sample)
 				const int64_t f = (int64_t) t * XT - T.m + 512 * warp;
@@ -954,7 +963,10 @@ __device__ __forceinline__ void ex_store_slice_packed(const uint32_t (&qv)[4], u
 	__syncwarp();
 }
 
-__global__ void __launch_bounds__(NT, 5) ex_emit_bytes_kernel(const __grid_constant__ ExArgs a)
+#ifndef PG_EMIT_CTAS
+#define PG_EMIT_CTAS 4	// (64 registers: the walk's pointers and the prefetched slice stay in registers)
+#endif
+__global__ void __launch_bounds__(NT, PG_EMIT_CTAS) ex_emit_bytes_kernel(const __grid_constant__ ExArgs a)
 {
 	__shared__ __align__(16) uint8_t s_line[NW][512 + 16];
 	__shared__ uint32_t s_read;
@@ -962,36 +974,37 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_bytes_kernel(const __grid_const
 	if (a.hdr->error & (ERR_CAPACITY | ERR_SCRATCH))
 		return;
 	uint8_t *line = s_line[warp];
+	uint32_t next = tid == 0 ? atomicAdd(&a.hdr->ticket2, 1u) : 0u;	// (the ticket after this one is asked for a read early)
 	for (;;) {
 		__syncthreads();
 		if (tid == 0)
-			s_read = atomicAdd(&a.hdr->ticket2, 1u);
+			s_read = next;
 		__syncthreads();
 		const uint64_t r = s_read;
 		if (r >= a.nreads)
 			break;
-		const uint32_t hdr = a.r_hdr[r];
-		if (hdr == X_FAIL)
-			continue;
+		if (tid == 0)
+			next = atomicAdd(&a.hdr->ticket2, 1u);
 		ExTile T;
 		uint32_t g0;
 		(void) ex_read_tile0(a, r, T, g0);
+		const uint32_t hdr = __ldg(a.r_hdr + r);
+		const uint32_t q = a.method == PRESS_GPU_EX_ZD ? __ldg(a.r_q + r) : 0u;
+		const uint64_t oo = a.out_offsets[r];
+		if (hdr == X_FAIL)
+			continue;
 		const uint64_t n = T.rend - T.off0, A = T.off0 >> 3;
 		const uint32_t nt = T.ntiles;
-		const uint32_t q = a.method == PRESS_GPU_EX_ZD ? a.r_q[r] : 0u;
 		const uint64_t rec0 = (uint64_t) g0 * NW + warp;
-		uint8_t *pay = a.out + a.out_offsets[r] + hdr;	// first payload byte of the read
+		uint8_t *pay = a.out + oo + hdr;	// first payload byte of the read
 		const int64_t mm = (int64_t) n - 1;
-		// a slice at one of the read's ends: samples again, element masks, no prefetch
-		auto edge_slice = [&](uint32_t t) {
+		// a slice at one of the read's ends: samples again, element masks
+		auto edge_finish = [&](uint32_t t, const ExRaw &C, uint32_t eb) {
 			const int64_t f = (int64_t) t * XT - T.m + 512 * warp;	// read index of the slice's first element
 			if (f >= (int64_t) n)
 				return;
 			T.t = t;
 			T.k0 = A + (uint64_t) t * XG;
-			ExRaw C;
-			ex_issue(a.samples, a.nsamples, T.k0, C);
-			const uint32_t eb = __ldg(a.t_eb + rec0 + (uint64_t) t * NW);
 			// values of the read before this slice, minus the exceptions among them
 			const int64_t vb = f - 1 < 0 ? 0 : (f - 1 < mm ? f - 1 : mm);
 			ExVals v;
@@ -1000,92 +1013,110 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_bytes_kernel(const __grid_const
 						__byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420)};
 			ex_store_slice_packed(qv, v.valid & ~v.exc & ~v.first, pay + ((uint64_t) vb - eb), line, lane);
 		};
-		edge_slice(0);
+		auto edge_slice = [&](uint32_t t) {
+			if ((int64_t) t * XT - T.m + 512 * warp >= (int64_t) n)
+				return;
+			ExRaw C;
+			ex_issue(a.samples, a.nsamples, A + (uint64_t) t * XG, C);
+			edge_finish(t, C, __ldg(a.t_eb + rec0 + (uint64_t) t * NW));
+		};
+		// the samples of tiles t_in and t_in + 1 (the read's last slices of this warp) asked from L2
+		auto prefetch_tail = [&](uint32_t t_in) {
+#pragma unroll
+			for (int k = 0; k < 2; k++) {
+				const uint64_t g = A + (uint64_t) (t_in + k) * XG + 2 * tid;
+				if (t_in + k < nt && 8 * g + 16 <= a.nsamples)
+					prefetch_l2(a.samples + g);
+			}
+		};
 		// tiles [1, t_in): the warp's slice lies inside the read
 		const uint64_t span = T.m + n;
 		const uint32_t t_in = span >= 512u * (warp + 1) ? (uint32_t) ((span - 512u * (warp + 1)) / XT) + 1 : 0u;
+		// everything the start of the read needs is asked for at once: tile 0's samples, the
+		// first records, the first low bytes (L2)
+		ExRaw E0;
+		ex_issue(a.samples, a.nsamples, A, E0);
+		const uint32_t eb0 = __ldg(a.t_eb + rec0);
 		if (t_in > 1) {
-			// records two tiles ahead, data one tile ahead; every address advances by a constant.
-			// The data of a slice without exception are its low bytes, loaded at the DESTINATION's
-			// 16-byte phase s (five 32-bit words per lane + the < 16 bytes either side), so that
-			// lane j holds the aligned output word j after four funnel shifts; of a slice with
-			// an exception, the samples.
+			// records two tiles ahead, low bytes one tile ahead (in registers; PG_PF_EMIT tiles
+			// ahead in L2); every address advances by a constant.  The low bytes are loaded at the
+			// DESTINATION's 16-byte phase s: five 32-bit words per lane, so that lane j holds the
+			// aligned output word j after four funnel shifts, and one byte for each of the < 16
+			// bytes either side.  A slice with an exception is computed again from its samples
+			// (asked from L2 when its record arrives).
 			const uint8_t *lp = reinterpret_cast<const uint8_t *>(ex_lowb_ptr(a.lowb, A, 1, 32 * warp));
 			const uint4 *sp = a.samples + A + XG + 2 * tid;
-			const uint32_t *pe = a.t_eb + rec0 + NW, *pn = a.t_nex + rec0 + NW;
+			const uint32_t *pe = a.t_eb + rec0 + NW;
+			const ptrdiff_t dnx = a.t_nex - a.t_eb;
 			uint8_t *Db = pay + (XT - T.m + 512 * warp - 1);
-			uint32_t eb1 = __ldg(pe), nx1 = __ldg(pn), eb2 = 0, nx2 = 0;
+			uint32_t eb1 = __ldg(pe), nx1 = __ldg(pe + dnx), eb2 = 0, nx2 = 0;
 			if (t_in > 2) {
 				eb2 = __ldg(pe + NW);
-				nx2 = __ldg(pn + NW);
+				nx2 = __ldg(pe + dnx + NW);
 			}
-			uint32_t W[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+			for (int k = 0; k < PG_PF_EMIT; k++)
+				if (t_in > 1 + k)
+					prefetch_l2(lp + k * XT + 16 * lane);
+			prefetch_tail(t_in);
+			edge_finish(0, E0, eb0);
+			uint32_t W[6] = {0, 0, 0, 0, 0, 0};
+			// byte k of the slice that lane < 16 copies by itself: the 16 - s bytes before the first
+			// aligned word, the s bytes after the last one
 			auto issue = [&](uint32_t nx, const uint8_t *D) {
 				if (nx == 0) {
 					const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(D) & 15);
 					if (lane > 0 || s == 0) {
-						const uint32_t *p = reinterpret_cast<const uint32_t *>(lp + ((16 * lane - (int) s) & ~3));
-#pragma unroll
-						for (int k = 0; k < 5; k++)
-							W[k] = __ldcs(p + k);
+						const uint8_t *p = lp + ((16 * lane - (int) s) & ~3);
+						asm("ld.global.cs.u32 %0, [%5];\n\tld.global.cs.u32 %1, [%5+4];\n\tld.global.cs.u32 %2, [%5+8];\n\t"
+						    "ld.global.cs.u32 %3, [%5+12];\n\tld.global.cs.u32 %4, [%5+16];"
+						    : "=r"(W[0]), "=r"(W[1]), "=r"(W[2]), "=r"(W[3]), "=r"(W[4])
+						    : "l"(p));
 					}
-					if (s && (uint32_t) lane < 16 - s)
-						W[5] = __ldcs(lp + lane);
-					if ((uint32_t) lane < s)
-						W[6] = __ldcs(lp + 512 - s + lane);
+					if (s && lane < 16)
+						W[5] = __ldcs(lp + ((uint32_t) lane < 16 - s ? lane : 496 + lane));
 				} else {
-					const uint4 xa = __ldg(sp), xb = __ldg(sp + 1);
-					W[0] = xa.x; W[1] = xa.y; W[2] = xa.z; W[3] = xa.w;
-					W[4] = xb.x; W[5] = xb.y; W[6] = xb.z; W[7] = xb.w;
-					if (lane == 0)
-						W[8] = __ldg(reinterpret_cast<const uint16_t *>(sp) - 1);
+					prefetch_l2(sp);
 				}
 			};
 			issue(nx1, Db - eb1);
-			if (t_in > 2)
-				prefetch_l2(lp + XT + 16 * lane);
-			if (t_in > 3)
-				prefetch_l2(lp + 2 * XT + 16 * lane);
 #pragma unroll 2
 			for (uint32_t t = 1; t < t_in; t++) {
-				uint32_t C[9];
+				uint32_t C[6];
 #pragma unroll
-				for (int k = 0; k < 9; k++)
+				for (int k = 0; k < 6; k++)
 					C[k] = W[k];
 				const uint32_t eb = eb1, nx = nx1;
 				uint8_t *D = Db - eb;
+				const uint4 *spc = sp;
 				eb1 = eb2;
 				nx1 = nx2;
 				lp += XT;
 				sp += XG;
 				pe += NW;
-				pn += NW;
 				Db += XT;
-				if (t + 3 < t_in)
-					prefetch_l2(lp + 2 * XT + 16 * lane);
+				if (t + PG_PF_EMIT < t_in)
+					prefetch_l2(lp + (PG_PF_EMIT - 1) * XT + 16 * lane);
 				if (t + 1 < t_in) {
 					issue(nx1, Db - eb1);
 					if (t + 2 < t_in) {
 						eb2 = __ldg(pe + NW);
-						nx2 = __ldg(pn + NW);
+						nx2 = __ldg(pe + dnx + NW);
 					}
 				}
 				if (nx == 0) {
 					const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(D) & 15), bs = ((16 - s) & 3) * 8;
-					uint8_t *Wd = D - s;
 					if (lane > 0 || s == 0)
-						reinterpret_cast<uint4 *>(Wd)[lane] =
+						reinterpret_cast<uint4 *>(D - s)[lane] =
 							make_uint4(__funnelshift_r(C[0], C[1], bs), __funnelshift_r(C[1], C[2], bs),
 								   __funnelshift_r(C[2], C[3], bs), __funnelshift_r(C[3], C[4], bs));
-					if (s && (uint32_t) lane < 16 - s)
-						D[lane] = (uint8_t) C[5];
-					if ((uint32_t) lane < s)
-						Wd[512 + lane] = (uint8_t) C[6];
+					if (s && lane < 16)
+						D[(uint32_t) lane < 16 - s ? lane : 496 + lane] = (uint8_t) C[5];
 				} else {
 					ExRaw R;
-					R.xa = make_uint4(C[0], C[1], C[2], C[3]);
-					R.xb = make_uint4(C[4], C[5], C[6], C[7]);
-					R.prev0 = C[8];
+					R.xa = __ldg(spc);
+					R.xb = __ldg(spc + 1);
+					R.prev0 = lane == 0 ? __ldg(reinterpret_cast<const uint16_t *>(spc) - 1) : 0u;
 					ExVals v;
 					uint32_t orw;
 					(void) ex_compute_fast(R, q, v, orw);
@@ -1094,6 +1125,8 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_bytes_kernel(const __grid_const
 					ex_store_slice_packed(qv, ~v.exc & 0xffffu, D, line, lane);
 				}
 			}
+		} else {
+			edge_finish(0, E0, eb0);
 		}
 		for (uint32_t t = t_in > 1 ? t_in : 1u; t < nt; t++)
 			edge_slice(t);

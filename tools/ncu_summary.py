@@ -22,6 +22,14 @@ while i < len(rows):
         st = {h: sum(f(r, h) for r in body) for h in stalls}
         print("stalls:", ", ".join(f"{h[6:]}={v / max(tot_samp, 1):.1%}" for h, v in sorted(st.items(), key=lambda x: -x[1])[:8]))
         print("shared wavefronts", int(sum(f(r, "L1 Wavefronts Shared") for r in body)), "ideal", int(sum(f(r, "L1 Wavefronts Shared Ideal") for r in body)))
+        # how often each SASS line ran (rounded): separates per-read code from the tile loop
+        cls = collections.Counter(); cl_n = collections.Counter()
+        for r in body:
+            e = f(r, "Instructions Executed")
+            if e > 0:
+                k = float(f"{e:.2g}")
+                cls[k] += e; cl_n[k] += 1
+        print("by execution count:", ", ".join(f"{int(k)}x: {cl_n[k]} lines = {v / max(tot_inst, 1):.0%}" for k, v in cls.most_common(8)))
         body.sort(key=lambda r: -f(r, "# Samples"))
         for r in body[:top]:
             print(f"{f(r, '# Samples') / max(tot_samp, 1):6.1%} inst={int(f(r, 'Instructions Executed')):>10}  {r[col['Source']][:110]}")
