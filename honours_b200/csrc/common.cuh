@@ -141,4 +141,11 @@ __device__ __forceinline__ uint32_t squeeze16(uint32_t k)
 	return k;
 }
 
+// ask L2 for the line holding p (no register waits for it): the per-read walks keep one step in
+// registers / shared memory and a few more on their way from HBM
+__device__ __forceinline__ void prefetch_l2(const void *p)
+{
+	asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
 }  // namespace pg

@@ -90,13 +90,6 @@ __device__ __forceinline__ uint4 *ex_lowb_ptr(uint8_t *lowb, uint64_t A, uint32_
 	return reinterpret_cast<uint4 *>(lowb + 8 * (A + (A & 1))) + (uint64_t) t * (XT / 16) + tid;
 }
 
-// ask L2 for the line holding p (no register waits for it): the walks below keep one tile in
-// registers and two more on their way from HBM
-__device__ __forceinline__ void prefetch_l2(const void *p)
-{
-	asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
-}
-
 // per-halfword arithmetic shift right (ex_zd.c:383-394 on int16)
 __device__ __forceinline__ uint32_t sar16x2(uint32_t x, uint32_t q)
 {
