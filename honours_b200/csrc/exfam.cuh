@@ -738,20 +738,67 @@ __global__ void __launch_bounds__(NT) ex_header_kernel(const __grid_constant__ E
 }
 
 // ---------------------------------------------------------------------------
-// sweep 2: header + payload
+// sweep 2, Huffman payloads (huffman.c:848-887: codes back to back, first bit of the stream
+// in bit 0 of byte 0).  One CTA per read, a tile of 4096 samples per step:
+//   1. every thread packs the codes of its 16 symbols into a private column of shared memory
+//      (one table lookup per symbol: code and length side by side) and notes the bit count in
+//      front of the one symbol that opens a side-car group;
+//   2. one block scan of the bit counts gives every thread its place in the tile's bitstream;
+//   3. the thread ORs its first and last word into the tile's stage (they are shared with its
+//      neighbours) and stores the words in between;
+//   4. the stage goes out as aligned 128-bit words and is left zeroed; the bits of the last,
+//      partial byte are carried into the next tile.
 
-template <bool HUFF>
-__global__ void __launch_bounds__(NT, 5) ex_emit_kernel(const __grid_constant__ ExArgs a)
+constexpr int HE_MAXW = 13;	// words of a thread's column: 16 codes of 24 bits, + 1
+
+// step 1.  ALL: the thread's 16 elements are payload symbols.  `tgt`: index (among the thread's
+// symbols) of the one whose bit offset is wanted in `cap`.  Returns the thread's bit count.
+template <bool ALL>
+__device__ __forceinline__ uint32_t he_pack(const uint32_t (&qv)[4], uint32_t ne, uint32_t tgt, const uint32_t *lut,
+					     uint32_t *col, uint32_t &cap)
 {
-	__shared__ __align__(16) uint8_t s_stage[HUFF ? X_STAGE : XT + 64];
+	uint32_t lo = 0, n = 0, nb = 0, cnt = 0;
+#pragma unroll
+	for (int e = 0; e < 16; e++) {
+		if (ALL || ((ne >> e) & 1)) {
+			// (32-bit entries, code | length << 24: the frequent symbols 0..31 sit in 32 different banks)
+			const uint32_t cl = lut[(qv[e >> 2] >> (8 * (e & 3))) & 0xffu], c = cl & 0xffffffu, l = cl >> 24;
+			if ((ALL ? (uint32_t) e : cnt) == tgt)
+				cap = nb;
+			cnt++;
+			lo |= c << n;
+			const uint32_t hi = __funnelshift_l(c, 0u, n);	// the code's bits past the word
+			n += l;
+			nb += l;
+			if (n >= 32) {
+				*col = lo;
+				col += NT;
+				lo = hi;
+				n -= 32;
+			}
+		}
+	}
+	if (n)
+		*col = lo;
+	return nb;
+}
+
+__global__ void __launch_bounds__(NT, 4) huff_emit_kernel(const __grid_constant__ ExArgs a)
+{
+	__shared__ __align__(16) uint8_t s_stage[X_STAGE];
+	__shared__ uint32_t s_col[HE_MAXW * NT];
+	__shared__ uint32_t s_lut[256];
 	__shared__ __align__(16) uint32_t s_warp[NW];
-	__shared__ uint32_t s_lut[HUFF ? 256 : 1];
-	__shared__ uint32_t s_read;
-	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	__shared__ uint32_t s_read, s_carry;
+	const int tid = threadIdx.x;
 	if (a.hdr->error & (ERR_CAPACITY | ERR_SCRATCH))
 		return;
-	if (HUFF)
+	{
 		s_lut[tid] = a.huff_enc[tid];
+		for (int w = tid; w < X_STAGE / 16; w += NT)
+			reinterpret_cast<uint4 *>(s_stage)[w] = make_uint4(0, 0, 0, 0);
+	}
+	uint32_t *sw = reinterpret_cast<uint32_t *>(s_stage);
 	for (;;) {
 		__syncthreads();
 		if (tid == 0)
@@ -767,121 +814,103 @@ __global__ void __launch_bounds__(NT, 5) ex_emit_kernel(const __grid_constant__ 
 		uint32_t g0;
 		(void) ex_read_tile0(a, r, T, g0);
 		const uint64_t n = T.rend - T.off0, A = T.off0 >> 3;
-		const uint32_t nt = T.ntiles, nex = a.r_nex[r];
-		const uint32_t q = a.method == PRESS_GPU_EX_ZD ? a.r_q[r] : 0u;
-		uint8_t *dst = a.out + a.out_offsets[r];
+		const uint32_t nt = T.ntiles;
+		uint8_t *pay = a.out + a.out_offsets[r] + hdr;	// first payload byte of the read
+		uint16_t *sc = a.sidecar ? a.sidecar + (T.off0 >> 4) + r : nullptr;
 		ExRaw W;
 		ex_issue(a.samples, a.nsamples, A, W);
-		uint8_t *pay = dst + hdr;	// first payload byte of the read
-		uint64_t pos = 0;		// payload bytes (bits when HUFF) written so far
-		uint32_t carryb = 0;		// HUFF: the bits of the last, still partial byte
-		uint32_t psym = 0;		// HUFF: payload symbols written so far (side-car index)
-		uint16_t *sc = HUFF && a.sidecar ? a.sidecar + (T.off0 >> 4) + r : nullptr;
+		uint64_t pos = 0;	// payload bits written so far
+		uint32_t carryb = 0;	// the bits of the last, still partial byte
+		uint32_t psym = 0;	// payload symbols written so far (side-car index)
 		for (uint32_t t = 0; t < nt; t++) {
 			T.t = t;
 			T.k0 = A + (uint64_t) t * XG;
 			const ExRaw C = W;
 			if (t + 1 < nt)
 				ex_issue(a.samples, a.nsamples, T.k0 + XG, W);
+			if (t + PG_PF_COUNT < nt)
+				prefetch_l2(a.samples + T.k0 + PG_PF_COUNT * XG + 2 * tid);
 			const int64_t f = (int64_t) t * XT - T.m;
-			const bool interior = f >= 1 && f + XT <= (int64_t) n;
 			ExVals v;
-			uint32_t hi = 1;
-			if (interior) {
+			if (f >= 1 && f + XT <= (int64_t) n) {
 				uint32_t orw;
-				hi = ex_compute_fast(C, q, v, orw);
+				(void) ex_compute_fast(C, 0, v, orw);
 			} else {
-				ex_compute(C, T, q, v);
+				ex_compute(C, T, 0, v);
 			}
 			const uint32_t ne = v.valid & ~v.exc & ~v.first;
-			if (!HUFF) {
-				uint32_t ex1[1] = {16u * tid}, tot = XT;
-				if (__syncthreads_or(hi)) {	// exceptions or a read boundary in the tile: count
-					uint32_t c1[1] = {(uint32_t) __popc(ne)};
-					block_scan<1>(c1, ex1, tot, s_warp);
+			const uint32_t qv[4] = {__byte_perm(v.z[0], v.z[1], 0x6420), __byte_perm(v.z[2], v.z[3], 0x6420),
+						__byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420)};
+			// payload index of the thread's first symbol
+			uint32_t si = psym + 16 * tid, nsym = XT;
+			const bool all = !__syncthreads_or(ne != 0xffffu);
+			if (!all) {
+				uint32_t c1[1] = {(uint32_t) __popc(ne)}, e1[1];
+				block_scan<1>(c1, e1, nsym, s_warp);
+				si = psym + e1[0];
+				__syncthreads();	// (s_warp is written again below)
+			}
+			psym += nsym;
+			// 1. codes -> the thread's column
+			const uint32_t tgt = (0u - si) & 15u;
+			uint32_t cap = 0xffffffffu;
+			const uint32_t len = all ? he_pack<true>(qv, ne, tgt, s_lut, s_col + tid, cap)
+						 : he_pack<false>(qv, ne, tgt, s_lut, s_col + tid, cap);
+			// 2. place in the tile's bitstream.  The stage mirrors global memory from the 16-byte
+			// word holding the tile's first bit
+			uint32_t l1[1] = {len}, x1[1], tot;
+			block_scan<1>(l1, x1, tot, s_warp);
+			const uint64_t G = 8 * (uint64_t) (pay - a.out) + pos;
+			const uint32_t s0 = (uint32_t) (G & 127), e0 = s0 + tot;
+			if (tid == 0 && carryb)	// the earlier tiles' bits of the first byte
+				atomicOr(sw + (s0 >> 5), carryb << (8 * ((s0 >> 3) & 3)));
+			if (sc && cap != 0xffffffffu)	// side-car: the bit offset (in the read's bitstream) of every 16th symbol
+				sc[(si + tgt) >> 4] = (uint16_t) (pos + x1[0] + cap);
+			// 3. column -> stage
+			if (len) {
+				const uint32_t bp = s0 + x1[0], sh = bp & 31, nw = (len + 31) >> 5;
+				const uint32_t last = (sh + len - 1) >> 5;
+				uint32_t *d = sw + (bp >> 5);
+				const uint32_t *col = s_col + tid;
+				uint32_t prev = 0;
+				for (uint32_t j = 0; j <= last; j++) {
+					const uint32_t cur = j < nw ? col[j * NT] : 0u;
+					const uint32_t o = __funnelshift_l(prev, cur, sh);
+					if (j == 0 || j == last)
+						atomicOr(d + j, o);
+					else
+						d[j] = o;
+					prev = cur;
 				}
-				if (ne == 0xffffu && (ex1[0] & 7) == 0) {
-					uint2 *p = reinterpret_cast<uint2 *>(s_stage + ex1[0]);
-					p[0] = make_uint2(__byte_perm(v.z[0], v.z[1], 0x6420), __byte_perm(v.z[2], v.z[3], 0x6420));
-					p[1] = make_uint2(__byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420));
-				} else {
-					uint8_t *p = s_stage + ex1[0];
-#pragma unroll
-					for (int e = 0; e < 16; e++)
-						if ((ne >> e) & 1)
-							*p++ = (uint8_t) ex_elem(v, e);
-				}
-				__syncthreads();
-				block_copy_out(s_stage, pay + pos, tot);
-				pos += tot;
-			} else {
-				// code lengths -> bit position of every symbol (huffman.c:848-887: codes back
-				// to back, first bit of the stream in bit 0 of byte 0)
-				// (one scan for both running values: bits of a tile < 2^17, symbols <= 4096)
-				const uint32_t bits = ex_code_bits(v, ne, s_lut);
-				uint32_t c1[1] = {bits | ((uint32_t) __popc(ne) << 17)}, ex1[1], tot;
-				block_scan<1>(c1, ex1, tot, s_warp);
-				uint32_t si = psym + (ex1[0] >> 17);	// payload index of the thread's first symbol
-				psym += tot >> 17;
-				ex1[0] &= 0x1ffffu;
-				tot &= 0x1ffffu;
-				// the stage mirrors global memory from the 16-byte word holding the tile's first bit
-				const uint64_t G = 8 * (uint64_t) (pay - a.out) + pos;
-				const uint32_t s0 = (uint32_t) (G & 127), e0 = s0 + tot;
-				const uint32_t nwords = (e0 + 31) >> 5;
-				uint32_t *sw = reinterpret_cast<uint32_t *>(s_stage);
-				for (uint32_t w = tid; w < nwords + 4; w += NT)
-					sw[w] = 0;
-				__syncthreads();
-				if (tid == 0 && carryb)	// the earlier tiles' bits of the first byte
-					atomicOr(sw + (s0 >> 5), carryb << (8 * ((s0 >> 3) & 3)));
-				uint32_t bp = s0 + ex1[0];
-				uint64_t acc = 0;	// bits not yet written, bit 0 = stage bit (bp & ~31)
-				uint32_t nacc = bp & 31, word = bp >> 5;
-#pragma unroll
-				for (int e = 0; e < 16; e++) {
-					if ((ne >> e) & 1) {
-						const uint32_t c = s_lut[ex_elem(v, e)];
-						// side-car: the bit offset (in the read's bitstream) of every 16th symbol
-						if (sc && (si & 15u) == 0)
-							sc[si >> 4] = (uint16_t) (pos + (32u * word + nacc - s0));
-						si++;
-						acc |= (uint64_t) (c & 0xffffffu) << nacc;
-						nacc += c >> 24;
-						if (nacc >= 32) {
-							atomicOr(sw + word, (uint32_t) acc);
-							acc >>= 32;
-							nacc -= 32;
-							word++;
-						}
-					}
-				}
-				if (acc)
-					atomicOr(sw + word, (uint32_t) acc);
-				__syncthreads();
-				const bool last = t + 1 == nt;
-				uint8_t *gb = a.out + ((G >> 7) << 4);	// global address of stage byte 0
-				// bytes [fb, lb) are complete: the first one thanks to the carried bits, the
-				// last partial one only at the end of the stream (zero padded, huffman.c:886)
-				const uint32_t fb = s0 >> 3, lb = (e0 >> 3) + ((last && (e0 & 7)) ? 1 : 0);
-				if (lb > fb) {
-					const uint32_t w0 = (fb + 15) >> 4, w1 = lb >> 4;	// wholly covered 16-byte words
-					if (w1 > w0) {
-						for (uint32_t w = w0 + tid; w < w1; w += NT)
-							reinterpret_cast<uint4 *>(gb)[w] = reinterpret_cast<const uint4 *>(s_stage)[w];
-						for (uint32_t b = fb + tid; b < (w0 << 4); b += NT)
-							gb[b] = s_stage[b];
-						for (uint32_t b = (w1 << 4) + tid; b < lb; b += NT)
-							gb[b] = s_stage[b];
-					} else {
-						for (uint32_t b = fb + tid; b < lb; b += NT)
-							gb[b] = s_stage[b];
-					}
-				}
-				carryb = (!last && (e0 & 7)) ? s_stage[e0 >> 3] : 0u;
-				pos += tot;
 			}
 			__syncthreads();
+			// 4. bytes [fb, lb) are complete: the first one thanks to the carried bits, the last
+			// partial one only at the end of the stream (zero padded, huffman.c:886)
+			const bool lastt = t + 1 == nt;
+			uint8_t *gb = a.out + ((G >> 7) << 4);	// global address of stage byte 0
+			const uint32_t fb = s0 >> 3, lb = (e0 >> 3) + ((lastt && (e0 & 7)) ? 1 : 0);
+			const uint32_t cw = e0 >> 7;	// the 16-byte word holding the partial byte
+			for (uint32_t w = tid; w <= cw; w += NT) {
+				const uint4 x = reinterpret_cast<const uint4 *>(s_stage)[w];
+				reinterpret_cast<uint4 *>(s_stage)[w] = make_uint4(0, 0, 0, 0);
+				if (w == cw) {
+					const uint32_t xs[4] = {x.x, x.y, x.z, x.w};
+					const uint32_t b = (e0 >> 3) & 15;
+					s_carry = (!lastt && (e0 & 7)) ? (xs[b >> 2] >> (8 * (b & 3))) & 0xffu : 0u;
+				}
+				const uint32_t lo = w << 4, hi = lo + 16;
+				if (lo >= fb && hi <= lb) {
+					reinterpret_cast<uint4 *>(gb)[w] = x;
+				} else {
+					const uint32_t xs[4] = {x.x, x.y, x.z, x.w};
+					const uint32_t b0 = lo < fb ? fb : lo, b1 = hi > lb ? lb : hi;
+					for (uint32_t b = b0; b < b1; b++)
+						gb[b] = (uint8_t) (xs[(b >> 2) & 3] >> (8 * (b & 3)));
+				}
+			}
+			__syncthreads();
+			carryb = s_carry;
+			pos += tot;
 		}
 	}
 }
