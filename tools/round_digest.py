@@ -39,7 +39,7 @@ for a, b in [(f"pytest_gpu_{tag}.log", f"{tag}_pytest_gpu.log"), (f"smoke_{tag}.
 pd.launches(os.path.join(G, f"launches_svb16_zd_{tag}.csv"), os.path.join(P, f"{tag}_svb16_zd_launches.txt"))
 pd.kernels(os.path.join(G, f"prof_svb16_zd_{tag}.ncu-rep"), os.path.join(P, f"{tag}_svb16_zd_kernels.txt"))
 caps = {"vbe21_zd": ["ex_count", "ex_emit_bytes", "ex_decode2"],
-        "shuff_vbe21_zd": ["ex_count", "ex_emit_kernel", "huff_fused"]}
+        "shuff_vbe21_zd": ["ex_count", "huff_emit", "huff_fused"]}
 for m, ks in caps.items():
     lc = os.path.join(G, f"launches_{m}_{tag}.csv")
     if os.path.exists(lc):
@@ -92,7 +92,7 @@ try:
 except Exception as e:
     print("svb16 traffic:", e)
 for m, enc, dec, bps in (("vbe21_zd", ["ex_count", "ex_emit_bytes"], ["ex_decode2"], 1.0002),
-                         ("shuff_vbe21_zd", ["ex_count", "ex_emit_kernel"], ["huff_fused"], 0.6788)):
+                         ("shuff_vbe21_zd", ["ex_count", "huff_emit"], ["huff_fused"], 0.6788)):
     try:
         alg = (2.0 + bps) * NS20K
         for nm, ks in (("encode", enc), ("decode", dec)):
