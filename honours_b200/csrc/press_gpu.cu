@@ -7,6 +7,7 @@
 
 #include <cuda_runtime.h>
 #include <stdarg.h>
+#include <stddef.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -615,3 +616,145 @@ void press_gpu_host_free(void *p)
 
 #include "host_paths.inc"
 #include "comm.inc"
+
+// ---------------------------------------------------------------------------------------------
+// svb16-zd compression of a batch with NO allocation anywhere in the call
+// (no counterpart in the reference: added
+// for callers that cannot call cudaMalloc -- CUDA graph capture, tight
+// serving loops, harnesses that forbid it).
+//
+// press_gpu_batch_press takes its scratch (per-tile status words, the plan tables, the 256-byte
+// header with the error word) from the caller.  Here the same kernels run on a file-scope device
+// array of a fixed, modest size: every GPU that loads the library holds
+// PRESS_GPU_STATIC_SCRATCH_BYTES of it until the process exits.  All calls share the array and it
+// keeps the last call's contents: the part that must start at zero (header + status words) is
+// cleared on the stream at the start of every call, and two calls that overlap on the GPU (two
+// streams, or two host threads without ordering between their streams) RACE on it.
+//
+// g_static_scratch below is, in host code, a host-side stand-in for the symbol, not a device
+// address: the address is looked up once per device with cudaGetSymbolAddress, with that device
+// current, and that pointer is what the kernels get.
+
+namespace {
+
+static __device__ __align__(256) unsigned char g_static_scratch[PRESS_GPU_STATIC_SCRATCH_BYTES];
+
+constexpr int STATIC_MAX_DEV = 64;
+std::mutex g_static_mutex;
+uint8_t *g_static_ptr[STATIC_MAX_DEV];	// device address of g_static_scratch, per device
+int g_static_grid[STATIC_MAX_DEV];		// resident CTAs of the encoder, per device
+
+// once per device, with that device current: the array's device address, the encoder's shared-memory
+// attribute and its cooperative grid
+int static_setup(int dev)
+{
+	std::lock_guard<std::mutex> lock(g_static_mutex);
+	if (g_static_ptr[dev])
+		return 0;
+	void *p = nullptr;
+	cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+	if (e != cudaSuccess || !p) {
+		set_err("static scratch: cudaGetSymbolAddress failed on device %d (%s)", dev, cudaGetErrorString(e));
+		return -1;
+	}
+	if (reinterpret_cast<uintptr_t>(p) & 255) {
+		set_err("static scratch: device address is not 256-byte aligned");
+		return -1;
+	}
+	auto kernel = svb_enc_kernel<1, false>;
+	const size_t smem = sizeof(EnSmem);
+	CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+	int per_sm = 0, sms = 0;
+	CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, EN_THREADS, smem));
+	CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+	if (per_sm < 1 || sms < 1) {
+		set_err("static scratch: svb_enc_kernel does not fit on an SM (%zu B shared)", smem);
+		return -1;
+	}
+	int grid = per_sm * sms;
+	if (grid > EN_MAX_GRID)
+		grid = EN_MAX_GRID;
+	g_static_grid[dev] = grid;
+	g_static_ptr[dev] = static_cast<uint8_t *>(p);
+	return 0;
+}
+
+}  // namespace
+
+extern "C" int press_gpu_svb16_zd_press_static(const int16_t *d_samples, const uint64_t *d_offsets, uint64_t nreads,
+						uint64_t nsamples, uint8_t *d_out, uint64_t out_capacity,
+						uint64_t *d_out_offsets, uint32_t *d_status, void *stream)
+{
+	if (ensure_init())
+		return -1;
+	if (nreads > PRESS_GPU_STATIC_MAX_READS || nsamples > PRESS_GPU_STATIC_MAX_SAMPLES) {
+		set_err("press_gpu_svb16_zd_press_static: %llu reads / %llu samples exceed the static scratch's limits "
+			"(%llu reads, %llu samples): split the batch or use press_gpu_batch_press",
+			(unsigned long long) nreads, (unsigned long long) nsamples,
+			(unsigned long long) PRESS_GPU_STATIC_MAX_READS, (unsigned long long) PRESS_GPU_STATIC_MAX_SAMPLES);
+		return -1;
+	}
+	const ScratchLayout l = scratch_layout(PRESS_GPU_SVB16_ZD, nreads, nsamples, 0.0);
+	if (l.total > (size_t) PRESS_GPU_STATIC_SCRATCH_BYTES) {	// (cannot happen within the limits above)
+		set_err("press_gpu_svb16_zd_press_static: batch needs %zu B of scratch, the static array holds %llu",
+			l.total, (unsigned long long) PRESS_GPU_STATIC_SCRATCH_BYTES);
+		return -1;
+	}
+	if (reinterpret_cast<uintptr_t>(d_samples) & 15) {
+		set_err("d_samples must be 16-byte aligned");
+		return -1;
+	}
+	int dev = -1;
+	CK(cudaGetDevice(&dev));
+	if (dev < 0 || dev >= STATIC_MAX_DEV) {
+		set_err("static scratch: device %d out of range", dev);
+		return -1;
+	}
+	if (!g_static_ptr[dev] && static_setup(dev))
+		return -1;
+	uint8_t *scr = g_static_ptr[dev];
+	cudaStream_t st = (cudaStream_t) stream;	// NULL = the CUDA default stream
+
+	CK(cudaMemsetAsync(d_out_offsets, 0xff, (nreads + 1) * sizeof(uint64_t), st));
+	// header (tickets, error word) and status words start at zero; the plan tables are rewritten
+	CK(cudaMemsetAsync(scr, 0, l.zero_bytes, st));
+	PlanArgs pa;
+	pa.offsets = d_offsets;
+	pa.nreads = nreads;
+	pa.tiling = TILING_ALIGNED;
+	pa.tile = EN_TS;
+	pa.frame = 0;
+	pa.keydiv = 8;
+	pa.fixed = 0;
+	pa.tile_start = reinterpret_cast<uint32_t *>(scr + l.tile_start);
+	pa.kx = reinterpret_cast<uint64_t *>(scr + l.kx);
+	pa.hdr = reinterpret_cast<Hdr *>(scr + l.hdr);
+	plan_scan_kernel<<<1, 1024, 0, st>>>(pa);
+	g_launches++;
+	if (nreads) {
+		const unsigned blocks = (unsigned) ((nreads * 32 + 255) / 256);
+		plan_fill_kernel<<<blocks, 256, 0, st>>>(pa.tile_start, nreads, reinterpret_cast<uint32_t *>(scr + l.tile_read));
+		g_launches++;
+	}
+	SvbEncArgs a;
+	a.samples = reinterpret_cast<const uint4 *>(d_samples);
+	a.nsamples = nsamples;
+	a.offsets = d_offsets;
+	a.nreads = nreads;
+	a.out = d_out;
+	a.out_cap = out_capacity;
+	a.out_offsets = d_out_offsets;
+	a.hdr = reinterpret_cast<Hdr *>(scr + l.hdr);
+	a.tile_start = reinterpret_cast<const uint32_t *>(scr + l.tile_start);
+	a.tile_read = reinterpret_cast<const uint32_t *>(scr + l.tile_read);
+	a.kx = reinterpret_cast<const uint64_t *>(scr + l.kx);
+	a.status = reinterpret_cast<uint64_t *>(scr + l.status);
+	void *params[] = {&a};
+	CK(cudaLaunchCooperativeKernel((const void *) svb_enc_kernel<1, false>, dim3(g_static_grid[dev]), dim3(EN_THREADS),
+				       params, sizeof(EnSmem), st));
+	g_launches++;
+	if (d_status)	// the error word of this call (press_gpu_batch_status's bits), device to device
+		CK(cudaMemcpyAsync(d_status, scr + l.hdr + offsetof(Hdr, error), sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+	CK(cudaGetLastError());
+	return 0;
+}

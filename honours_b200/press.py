@@ -102,6 +102,8 @@ def lib() -> C.CDLL:
         L.press_gpu_batch_depress_sidecar.argtypes = [i32, vp, vp, u64, vp, u64, u64, vp, vp, sz, vp, sz, vp]
         L.press_gpu_batch_status.restype = i32
         L.press_gpu_batch_status.argtypes = [vp, vp]
+        L.press_gpu_svb16_zd_press_static.restype = i32
+        L.press_gpu_svb16_zd_press_static.argtypes = [vp, vp, u64, u64, vp, u64, vp, vp, vp]
         L.press_gpu_batch_press_host.restype = i32
         L.press_gpu_batch_press_host.argtypes = [i32, vp, vp, u64, vp, u64, vp]
         L.press_gpu_batch_depress_host.restype = i32
@@ -280,6 +282,20 @@ def batch_press(method: str, d_samples: int, d_offsets: int, nreads: int, nsampl
     rc = lib().press_gpu_batch_press(METHODS[method], d_samples, d_offsets, nreads, nsamples,
                                      d_out, out_capacity, d_out_offsets, d_scratch,
                                      scratch_bytes, stream)
+    if rc != 0:
+        raise PressGpuError(last_error())
+
+
+STATIC_MAX_READS = 4096             # include/press_gpu.h PRESS_GPU_STATIC_MAX_READS
+STATIC_MAX_SAMPLES = 1 << 25        # PRESS_GPU_STATIC_MAX_SAMPLES
+
+
+def svb16_zd_press_static(d_samples: int, d_offsets: int, nreads: int, nsamples: int, d_out: int,
+                          out_capacity: int, d_out_offsets: int, d_status: int = 0, stream: int = 0) -> None:
+    """press_gpu_svb16_zd_press_static: svb16-zd batch compression on the library's static device
+    scratch (no allocation in the call; limits above; calls overlapping on the GPU race)."""
+    rc = lib().press_gpu_svb16_zd_press_static(d_samples, d_offsets, nreads, nsamples, d_out, out_capacity,
+                                               d_out_offsets, d_status, stream)
     if rc != 0:
         raise PressGpuError(last_error())
 

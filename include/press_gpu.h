@@ -303,6 +303,29 @@ int press_gpu_container_info(const char *path, int *method, uint64_t *nreads, ui
 int press_gpu_container_read(const char *path, uint64_t *h_offsets, uint64_t *h_out_offsets,
 			     uint8_t *h_container);
 
+/* svb16-zd compression of a batch (method PRESS_GPU_SVB16_ZD; same kernels, same container bytes as
+ * press_gpu_batch_press) that ALLOCATES NOTHING: no cudaMalloc / cudaFree or allocating library
+ * routine in the call, and no scratch argument.  No counterpart in the reference: added
+ * for callers that cannot allocate (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).
+ * The scratch is a file-scope device array of PRESS_GPU_STATIC_SCRATCH_BYTES that every GPU loading
+ * the library holds until the process exits; hence the limits: nreads <= PRESS_GPU_STATIC_MAX_READS
+ * and nsamples <= PRESS_GPU_STATIC_MAX_SAMPLES, larger batches are rejected (-1, press_gpu_last_error)
+ * -- split them or use press_gpu_batch_press.  ALL calls share the array: it keeps the last call's
+ * contents (what must start at zero is cleared on `stream` at the start of each call), and calls
+ * that overlap on the GPU -- different streams, or host threads without ordering between their
+ * streams -- RACE on it: keep them on one stream or order them with events.
+ * The first call on a device also does the one-time set-up (library context, the array's device
+ * address, kernel attributes): make it once before a graph capture.
+ * d_status (device, may be NULL) receives this call's error word (press_gpu_batch_status's bits:
+ * bit 0 = out_capacity exceeded) by a device-to-device copy on `stream`. */
+#define PRESS_GPU_STATIC_MAX_READS 4096ull
+#define PRESS_GPU_STATIC_MAX_SAMPLES 33554432ull	/* 2^25: 64 MiB of raw int16 signal */
+#define PRESS_GPU_STATIC_SCRATCH_BYTES 262144ull	/* 256 KiB */
+int press_gpu_svb16_zd_press_static(const int16_t *d_samples, const uint64_t *d_offsets, uint64_t nreads,
+				    uint64_t nsamples, uint8_t *d_out, uint64_t out_capacity,
+				    uint64_t *d_out_offsets, uint32_t *d_status, void *stream);
+
 /* Kernel timing for bench.py's roofline: when enabled every main codec kernel
  * launch is bracketed by CUDA events on its stream.  collect() waits for them
  * and returns, since the last collect, the summed device milliseconds and the
