@@ -543,7 +543,7 @@ __global__ void __launch_bounds__(NT, PG_COUNT_CTAS) ex_count_kernel(const __gri
 			bits_thr = 0;
 			ExRaw W;
 			ex_issue(a.samples, a.nsamples, A, W);
-#pragma unroll 2
+#pragma unroll(HUFF ? 1 : 2)	// (the Huffman variant's body is long: unrolled twice it misses the instruction cache)
 			for (uint32_t t = 0; t < nt; t++) {
 				T.t = t;
 				T.k0 = A + (uint64_t) t * XG;

@@ -8,5 +8,6 @@ for K in "$@"; do
 import sys; sys.path.insert(0, 'tools'); import profile_digest as pd
 pd.kernels('gpurun_out/full_${M}_${K}_$TAG.ncu-rep', 'gpurun_out/digest_${M}_${K}_$TAG.txt')"
   head -60 gpurun_out/digest_${M}_${K}_$TAG.txt | cut -c1-150
+  ncu -i gpurun_out/full_${M}_${K}_$TAG.ncu-rep --page source --csv > gpurun_out/sass_${M}_${K}_$TAG.csv 2>/dev/null
 done
 rm -f gpurun_out/*.ncu-rep
