@@ -67,7 +67,7 @@ struct ExArgs {
 	uint8_t *out;			// encode out (16-byte aligned)
 	uint64_t out_cap;
 	uint64_t *out_offsets;		// [nreads + 1]
-	Hdr *hdr;			// aux[0] = pool entries used
+	Hdr *hdr;			// aux[0] = pool entries handed out (in chunks, see ex_count_kernel)
 	const uint32_t *tile_start, *tile_read;
 	uint32_t *t_nex, *t_pool, *t_eb;	// per (tile, warp): exceptions in the slice, pool position, prefix
 	uint32_t *r_nex, *r_q, *r_hdr, *r_pool;			// per read
@@ -510,6 +510,14 @@ __global__ void __launch_bounds__(NT, PG_COUNT_CTAS) ex_count_kernel(const __gri
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	if (HUFF)
 		s_len[tid] = a.huff_enc[tid];
+	// pool chunk of a warp: 1/16 of the pool at most is held in unfinished chunks; none when the pool
+	// is small or has its full size (then every entry may be needed: the retry of the host paths)
+	uint32_t chunk = 0, wleft = 0;
+	unsigned long long wbase = 0;
+	if (a.pool_cap <= a.nsamples) {
+		const uint64_t c = a.pool_cap / (16ull * gridDim.x * NW);
+		chunk = c >= 16 ? (uint32_t) (c < 1024 ? c : 1024) : 0u;
+	}
 	for (;;) {
 		__syncthreads();
 		if (tid == 0) {
@@ -575,10 +583,26 @@ __global__ void __launch_bounds__(NT, PG_COUNT_CTAS) ex_count_kernel(const __gri
 					const uint32_t cnt = __popc(v.exc);
 					const uint32_t inc = warp_inc_scan(cnt, lane);
 					slice_nex = __shfl_sync(0xffffffffu, inc, 31);
-					unsigned long long b64 = 0;
-					if (lane == 0)
-						b64 = atomicAdd((unsigned long long *) &a.hdr->aux[0], (unsigned long long) slice_nex);
-					b64 = __shfl_sync(0xffffffffu, b64, 0);
+					// pool space: from the warp's own chunk (one global atomic per `chunk` entries: at
+					// exception rates >= 1e-3 an atomic per slice on one address was the whole sweep's
+					// bound), else asked for directly
+					unsigned long long b64 = wbase;
+					if (slice_nex <= wleft) {
+						wbase += slice_nex;
+						wleft -= slice_nex;
+					} else {
+						// (a new chunk gives up the old one's rest, < slice_nex < chunk / 2 entries)
+						const bool refill = 2 * slice_nex < chunk;
+						const uint32_t take = refill ? chunk : slice_nex;
+						if (lane == 0)
+							b64 = atomicAdd((unsigned long long *) &a.hdr->aux[0], (unsigned long long) take);
+						b64 = __shfl_sync(0xffffffffu, b64, 0);
+						if (refill) {
+							const bool fits = b64 + take <= a.pool_cap;
+							wbase = b64 + slice_nex;
+							wleft = fits ? take - slice_nex : 0u;
+						}
+					}
 					base = (uint32_t) b64;
 					if (b64 + slice_nex <= a.pool_cap) {
 						uint2 *p = a.pool + b64 + inc - cnt;

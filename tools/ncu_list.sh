@@ -3,7 +3,7 @@
 TAG=$1; READS=$2; shift 2
 mkdir -p gpurun_out
 for m in "$@"; do
-  SHORT="python bench.py --method $m --reads $READS --steps 1 --warmup 1 --methods= --no-e2e --no-cpu-baseline"
+  SHORT="python bench.py --method $m --reads $READS --steps 1 --warmup 1 --methods= --no-e2e --no-cpu-baseline $EXTRA"
   $SHORT > gpurun_out/plain_${m}_$TAG.log 2>&1 &&
   ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
       --log-file gpurun_out/launches_${m}_$TAG.csv $SHORT > gpurun_out/ncu_list_${m}_$TAG.log 2>&1
