@@ -606,10 +606,22 @@ __global__ void __launch_bounds__(NT, PG_COUNT_CTAS) ex_count_kernel(const __gri
 					base = (uint32_t) b64;
 					if (b64 + slice_nex <= a.pool_cap) {
 						uint2 *p = a.pool + b64 + inc - cnt;
+						if (__reduce_max_sync(0xffffffffu, cnt) <= 2) {
+							// few exceptions: one turn per exception, its value picked by selects
+							// (v.z stays in registers)
+							for (uint32_t mk = v.exc; mk; mk &= mk - 1) {
+								const uint32_t e = __ffs(mk) - 1, j = e >> 1;
+								const uint32_t lo4 = (j & 2) ? ((j & 1) ? v.z[3] : v.z[2]) : ((j & 1) ? v.z[1] : v.z[0]);
+								const uint32_t hi4 = (j & 2) ? ((j & 1) ? v.z[7] : v.z[6]) : ((j & 1) ? v.z[5] : v.z[4]);
+								const uint32_t w = (j & 4) ? hi4 : lo4;
+								*p++ = make_uint2((uint32_t) (v.i0 + e - 1), (w >> (16 * (e & 1))) & 0xffffu);
+							}
+						} else {
 #pragma unroll
-						for (int e = 0; e < 16; e++)	// (static indices: v.z stays in registers)
-							if ((v.exc >> e) & 1)
-								*p++ = make_uint2((uint32_t) (v.i0 + e - 1), ex_elem(v, e));
+							for (int e = 0; e < 16; e++)	// (static indices: v.z stays in registers)
+								if ((v.exc >> e) & 1)
+									*p++ = make_uint2((uint32_t) (v.i0 + e - 1), ex_elem(v, e));
+						}
 					} else if (lane == 0) {
 						atomicOr(&a.hdr->error, ERR_SCRATCH);
 					}

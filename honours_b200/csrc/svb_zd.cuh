@@ -103,17 +103,20 @@ __device__ __forceinline__ void warp_copy_out(const uint8_t *stage, uint8_t *dst
 	uint8_t *gbase = dst - a;
 	const uint32_t end = a + len;
 	const uint32_t nwords = (end + 7) >> 3;
-	for (uint32_t q = lane; q < nwords; q += 32) {
-		const uint32_t lo = q << 3, hi = lo + 8;
-		if (lo >= a && hi <= end) {
-			*reinterpret_cast<uint64_t *>(gbase + lo) =
-				*reinterpret_cast<const uint64_t *>(stage + lo);
-		} else {
-			const uint32_t b0 = lo < a ? a : lo, b1 = hi > end ? end : hi;
-			for (uint32_t b = b0; b < b1; b++)
-				gbase[b] = stage[b];
-		}
+	// whole 8-byte words by their lanes; the < 8 bytes of the first and of the last word by a lane each
+	const uint32_t w0 = (a + 7) >> 3, w1 = end >> 3;
+	if (w1 >= w0) {
+		for (uint32_t q = w0 + lane; q < w1; q += 32)
+			*reinterpret_cast<uint64_t *>(gbase + 8 * q) = *reinterpret_cast<const uint64_t *>(stage + 8 * q);
+		const uint32_t nh = 8 * w0 - a, ntl = end - 8 * w1;
+		if ((uint32_t) lane < nh)
+			gbase[a + lane] = stage[a + lane];
+		else if ((uint32_t) lane - 8 < ntl)
+			gbase[8 * w1 + lane - 8] = stage[8 * w1 + lane - 8];
+	} else if ((uint32_t) lane < len) {	// inside one word
+		gbase[a + lane] = stage[a + lane];
 	}
+	(void) nwords;
 }
 
 // Zero `len` bytes at `dst` (any alignment) with 32-bit stores where possible.  One warp.
