@@ -232,19 +232,20 @@ __device__ __forceinline__ uint32_t ex_compute_fast(const ExRaw &w, uint32_t q, 
 	return hi;
 }
 
-// sum of the code lengths of the thread's non-exception values
-__device__ __forceinline__ uint32_t ex_code_bits(const ExVals &v, uint32_t ne, const uint32_t *lut)
+// sum of the code lengths of the thread's non-exception values (lut: 256 lengths, one byte each:
+// symbols s and s + 128 are the only ones that meet in a bank)
+__device__ __forceinline__ uint32_t ex_code_bits(const ExVals &v, uint32_t ne, const uint8_t *lut)
 {
 	uint32_t bits = 0;
 	if (ne == 0xffffu) {
 #pragma unroll
 		for (int j = 0; j < 8; j++)
-			bits += (lut[v.z[j] & 0xffffu] >> 24) + (lut[v.z[j] >> 16] >> 24);
+			bits += (uint32_t) lut[v.z[j] & 0xffffu] + lut[v.z[j] >> 16];
 	} else {
 #pragma unroll
 		for (int e = 0; e < 16; e++)
 			if ((ne >> e) & 1)
-				bits += lut[(v.z[e >> 1] >> (16 * (e & 1))) & 0xffffu] >> 24;
+				bits += lut[(v.z[e >> 1] >> (16 * (e & 1))) & 0xffffu];
 	}
 	return bits;
 }
@@ -506,10 +507,10 @@ __global__ void __launch_bounds__(NT, PG_COUNT_CTAS) ex_count_kernel(const __gri
 	__shared__ __align__(16) uint32_t s_warp[NW];
 	__shared__ uint32_t s_read, s_or, s_nex, s_base2;
 	__shared__ unsigned long long s_bits;
-	__shared__ uint32_t s_len[HUFF ? 256 : 1];
+	__shared__ uint8_t s_len[HUFF ? 256 : 4];
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	if (HUFF)
-		s_len[tid] = a.huff_enc[tid];
+		s_len[tid] = (uint8_t) (a.huff_enc[tid] >> 24);
 	// pool chunk of a warp: 1/16 of the pool at most is held in unfinished chunks; none when the pool
 	// is small or has its full size (then every entry may be needed: the retry of the host paths)
 	uint32_t chunk = 0, wleft = 0;
@@ -776,64 +777,127 @@ __global__ void __launch_bounds__(NT) ex_header_kernel(const __grid_constant__ E
 // ---------------------------------------------------------------------------
 // sweep 2, Huffman payloads (huffman.c:848-887: codes back to back, first bit of the stream
 // in bit 0 of byte 0).  One CTA per read, a tile of 4096 samples per step:
-//   1. every thread packs the codes of its 16 symbols into a private column of shared memory
-//      (one table lookup per symbol: code and length side by side) and notes the bit count in
-//      front of the one symbol that opens a side-car group;
+//   1. every thread looks its 16 symbols up (one table word per symbol: code << 8 | length) and
+//      adds up the lengths -- the thread's bit count, known before a single bit is placed -- and
+//      the bit count in front of the one symbol that opens a side-car group;
 //   2. one block scan of the bit counts gives every thread its place in the tile's bitstream;
-//   3. the thread ORs its first and last word into the tile's stage (they are shared with its
-//      neighbours) and stores the words in between;
+//   3. the thread appends its codes, at the stage's own word alignment, to a register and stores
+//      every word it completes; the stage's words are written once, with plain stores, except
+//      the one word a thread shares with the thread before (see he_put);
 //   4. the stage goes out as aligned 128-bit words and is left zeroed; the bits of the last,
 //      partial byte are carried into the next tile.
-
-constexpr int HE_MAXW = 13;	// words of a thread's column: 16 codes of 24 bits, + 1
+// A shared-memory atomic costs about 2 cycles per LANE on this part: one ORed word per thread and
+// tile is as much LSU time as four table lookups, which is why the words shared by neighbours go
+// through a shuffle instead (an earlier form with two atomicOr per thread spent half its time there).
 
 // step 1.  ALL: the thread's 16 elements are payload symbols.  `tgt`: index (among the thread's
-// symbols) of the one whose bit offset is wanted in `cap`.  Returns the thread's bit count.
+// symbols) of the one whose bit offset is wanted in `cap`.  The lengths are added as whole table
+// words: the low byte of a sum of up to 8 entries is the sum of their lengths (8 x 24 < 256).
 template <bool ALL>
-__device__ __forceinline__ uint32_t he_pack(const uint32_t (&qv)[4], uint32_t ne, uint32_t tgt, const uint32_t *lut,
-					     uint32_t *col, uint32_t &cap)
+__device__ __forceinline__ uint32_t he_lookup(const uint32_t (&qv)[4], uint32_t ne, uint32_t tgt, const uint32_t (&lut)[256],
+					       uint32_t (&e)[16], uint32_t &cap)
 {
-	uint32_t lo = 0, n = 0, nb = 0, cnt = 0;
 #pragma unroll
-	for (int e = 0; e < 16; e++) {
-		if (ALL || ((ne >> e) & 1)) {
-			// (32-bit entries, code | length << 24: the frequent symbols 0..31 sit in 32 different banks)
-			const uint32_t cl = lut[(qv[e >> 2] >> (8 * (e & 3))) & 0xffu], c = cl & 0xffffffu, l = cl >> 24;
-			if ((ALL ? (uint32_t) e : cnt) == tgt)
+	for (int i = 0; i < 16; i++) {
+		e[i] = lut[(qv[i >> 2] >> (8 * (i & 3))) & 0xffu];
+		if (!ALL && !((ne >> i) & 1))
+			e[i] = 0;
+	}
+	uint32_t ps[8], qs[4];
+#pragma unroll
+	for (int k = 0; k < 8; k++)
+		ps[k] = e[2 * k] + e[2 * k + 1];
+#pragma unroll
+	for (int j = 0; j < 4; j++)
+		qs[j] = ps[2 * j] + ps[2 * j + 1];
+	const uint32_t o0 = (qs[0] + qs[1]) & 0xffu, o1 = (qs[2] + qs[3]) & 0xffu;
+	if (ALL) {
+		// (tgt is the same in every thread of a tile without exceptions)
+		uint32_t c = 0;
+		switch (tgt & 7u) {
+		case 0: c = 0; break;
+		case 1: c = tgt & 8u ? e[8] : e[0]; break;
+		case 2: c = tgt & 8u ? ps[4] : ps[0]; break;
+		case 3: c = tgt & 8u ? ps[4] + e[10] : ps[0] + e[2]; break;
+		case 4: c = tgt & 8u ? qs[2] : qs[0]; break;
+		case 5: c = tgt & 8u ? qs[2] + e[12] : qs[0] + e[4]; break;
+		case 6: c = tgt & 8u ? qs[2] + ps[6] : qs[0] + ps[2]; break;
+		default: c = tgt & 8u ? qs[2] + ps[6] + e[14] : qs[0] + ps[2] + e[6]; break;
+		}
+		cap = (c & 0xffu) + (tgt & 8u ? o0 : 0u);
+	} else {
+		uint32_t cnt = 0, nb = 0;
+#pragma unroll
+		for (int i = 0; i < 16; i++) {
+			if (((ne >> i) & 1) && cnt++ == tgt)
 				cap = nb;
-			cnt++;
-			lo |= c << n;
-			const uint32_t hi = __funnelshift_l(c, 0u, n);	// the code's bits past the word
-			n += l;
-			nb += l;
-			if (n >= 32) {
-				*col = lo;
-				col += NT;
-				lo = hi;
-				n -= 32;
-			}
+			nb += e[i] & 0xffu;
 		}
 	}
-	if (n)
-		*col = lo;
-	return nb;
+	return o0 + o1;
 }
 
-__global__ void __launch_bounds__(NT, 4) huff_emit_kernel(const __grid_constant__ ExArgs a)
+// step 3.  The thread's codes appended to a0 (what its first word holds already below bit
+// pos & 31), every completed word but the first stored at sa onwards (sa: shared-memory address of
+// the word holding bit pos; it follows the words).  The first completed word comes back in `first`
+// (got: there was one), the bits after the last completed word are the return value.
+// EDGE = false: 8 codes are 32 bits at least, so the first word is complete after the eighth.
+template <bool EDGE>
+__device__ __forceinline__ uint32_t he_put(const uint32_t (&e)[16], uint32_t a0, uint32_t pos, uint32_t &sa, uint32_t &first,
+					    bool &got)
+{
+	got = false;
+	first = 0;
+#pragma unroll
+	for (int i = 0; i < 16; i++) {
+		const uint32_t c = e[i] >> 8;
+		a0 |= __funnelshift_l(0u, c, pos);	// (shifts by pos & 31)
+		const uint32_t a1 = __funnelshift_l(c, 0u, pos);
+		const uint32_t np = pos + (e[i] & 0xffu);
+		if ((np ^ pos) & 32u) {		// a code is 24 bits at most: one word boundary at most
+			if (EDGE || i < 8) {
+				if (got)
+					asm volatile("st.shared.u32 [%0], %1;" ::"r"(sa), "r"(a0) : "memory");
+				else
+					first = a0;
+				got = true;
+			} else {
+				asm volatile("st.shared.u32 [%0], %1;" ::"r"(sa), "r"(a0) : "memory");
+			}
+			sa += 4;
+			a0 = a1;
+		}
+		pos = np;
+	}
+	return a0;
+}
+
+__device__ __forceinline__ void sred_or(uint32_t saddr, uint32_t v)	// OR into a shared-memory word, no result wanted
+{
+	asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(saddr), "r"(v) : "memory");
+}
+
+#ifndef PG_HE_CTAS
+#define PG_HE_CTAS 4
+#endif
+__global__ void __launch_bounds__(NT, PG_HE_CTAS) huff_emit_kernel(const __grid_constant__ ExArgs a)
 {
 	__shared__ __align__(16) uint8_t s_stage[X_STAGE];
-	__shared__ uint32_t s_col[HE_MAXW * NT];
 	__shared__ uint32_t s_lut[256];
 	__shared__ __align__(16) uint32_t s_warp[NW];
 	__shared__ uint32_t s_read, s_carry;
 	const int tid = threadIdx.x;
 	if (a.hdr->error & (ERR_CAPACITY | ERR_SCRATCH))
 		return;
-	{
-		s_lut[tid] = a.huff_enc[tid];
-		for (int w = tid; w < X_STAGE / 16; w += NT)
-			reinterpret_cast<uint4 *>(s_stage)[w] = make_uint4(0, 0, 0, 0);
-	}
+	const uint32_t x = a.huff_enc[tid];	// code | length << 24 -> code << 8 | length
+	s_lut[tid] = (x << 8) | (x >> 24);
+	for (int w = tid; w < X_STAGE / 16; w += NT)
+		reinterpret_cast<uint4 *>(s_stage)[w] = make_uint4(0, 0, 0, 0);
+	if (tid == 0)
+		s_carry = 0;
+	// the plain-store path wants 8 codes to be 32 bits at least (he_put)
+	const bool tab_ok = __syncthreads_and((x >> 24) >= 4);
+	const uint32_t stage_sa = (uint32_t) __cvta_generic_to_shared(s_stage);
 	uint32_t *sw = reinterpret_cast<uint32_t *>(s_stage);
 	for (;;) {
 		__syncthreads();
@@ -856,7 +920,11 @@ __global__ void __launch_bounds__(NT, 4) huff_emit_kernel(const __grid_constant_
 		ExRaw W;
 		ex_issue(a.samples, a.nsamples, A, W);
 		uint64_t pos = 0;	// payload bits written so far
-		uint32_t carryb = 0;	// the bits of the last, still partial byte
+		// (the bits of the last, still partial byte wait in s_carry: 0 at every read's start)
+		// exceptions in the tile's eight slices, as sweep 1 counted them: a tile without any inside
+		// the read takes the path without masks and without the symbol-count scan
+		const uint4 *rec = reinterpret_cast<const uint4 *>(a.t_nex + (uint64_t) g0 * NW);
+		uint4 ra = __ldg(rec), rb = __ldg(rec + 1);
 		uint32_t psym = 0;	// payload symbols written so far (side-car index)
 		for (uint32_t t = 0; t < nt; t++) {
 			T.t = t;
@@ -867,8 +935,14 @@ __global__ void __launch_bounds__(NT, 4) huff_emit_kernel(const __grid_constant_
 			if (t + PG_PF_COUNT < nt)
 				prefetch_l2(a.samples + T.k0 + PG_PF_COUNT * XG + 2 * tid);
 			const int64_t f = (int64_t) t * XT - T.m;
+			const bool inside = f >= 1 && f + XT <= (int64_t) n;
+			const bool all = inside && !(ra.x | ra.y | ra.z | ra.w | rb.x | rb.y | rb.z | rb.w);
+			if (t + 1 < nt) {
+				ra = __ldg(rec + 2 * (t + 1));
+				rb = __ldg(rec + 2 * (t + 1) + 1);
+			}
 			ExVals v;
-			if (f >= 1 && f + XT <= (int64_t) n) {
+			if (inside) {
 				uint32_t orw;
 				(void) ex_compute_fast(C, 0, v, orw);
 			} else {
@@ -879,7 +953,6 @@ __global__ void __launch_bounds__(NT, 4) huff_emit_kernel(const __grid_constant_
 						__byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420)};
 			// payload index of the thread's first symbol
 			uint32_t si = psym + 16 * tid, nsym = XT;
-			const bool all = !__syncthreads_or(ne != 0xffffu);
 			if (!all) {
 				uint32_t c1[1] = {(uint32_t) __popc(ne)}, e1[1];
 				block_scan<1>(c1, e1, nsym, s_warp);
@@ -887,37 +960,47 @@ __global__ void __launch_bounds__(NT, 4) huff_emit_kernel(const __grid_constant_
 				__syncthreads();	// (s_warp is written again below)
 			}
 			psym += nsym;
-			// 1. codes -> the thread's column
+			// 1. table words, the thread's bit count
 			const uint32_t tgt = (0u - si) & 15u;
-			uint32_t cap = 0xffffffffu;
-			const uint32_t len = all ? he_pack<true>(qv, ne, tgt, s_lut, s_col + tid, cap)
-						 : he_pack<false>(qv, ne, tgt, s_lut, s_col + tid, cap);
+			const bool plain = all && tab_ok;	// (the same in every thread)
+			uint32_t cap = 0xffffffffu, e[16];
+			const uint32_t len = all ? he_lookup<true>(qv, ne, tgt, s_lut, e, cap) : he_lookup<false>(qv, ne, tgt, s_lut, e, cap);
 			// 2. place in the tile's bitstream.  The stage mirrors global memory from the 16-byte
 			// word holding the tile's first bit
 			uint32_t l1[1] = {len}, x1[1], tot;
 			block_scan<1>(l1, x1, tot, s_warp);
 			const uint64_t G = 8 * (uint64_t) (pay - a.out) + pos;
 			const uint32_t s0 = (uint32_t) (G & 127), e0 = s0 + tot;
-			if (tid == 0 && carryb)	// the earlier tiles' bits of the first byte
-				atomicOr(sw + (s0 >> 5), carryb << (8 * ((s0 >> 3) & 3)));
 			if (sc && cap != 0xffffffffu)	// side-car: the bit offset (in the read's bitstream) of every 16th symbol
 				sc[(si + tgt) >> 4] = (uint16_t) (pos + x1[0] + cap);
-			// 3. column -> stage
-			if (len) {
-				const uint32_t bp = s0 + x1[0], sh = bp & 31, nw = (len + 31) >> 5;
-				const uint32_t last = (sh + len - 1) >> 5;
-				uint32_t *d = sw + (bp >> 5);
-				const uint32_t *col = s_col + tid;
-				uint32_t prev = 0;
-				for (uint32_t j = 0; j <= last; j++) {
-					const uint32_t cur = j < nw ? col[j * NT] : 0u;
-					const uint32_t o = __funnelshift_l(prev, cur, sh);
-					if (j == 0 || j == last)
-						atomicOr(d + j, o);
-					else
-						d[j] = o;
-					prev = cur;
-				}
+			// 3. codes -> stage
+			const uint32_t bp = s0 + x1[0];
+			const uint32_t fw = stage_sa + ((bp >> 3) & ~3u);	// the thread's first word
+			uint32_t sa = fw, first;
+			bool got;
+			// the tile's first word opens with the carried byte (written before the scan's barrier,
+			// rewritten after the next one)
+			const uint32_t carried = tid == 0 ? s_carry << (8 * ((s0 >> 3) & 3)) : 0u;
+			if (plain) {
+				// every thread has 64 bits or more: its first word is shared with the thread before and
+				// nobody else, whose bits there are what that thread has left over at its end.  Across
+				// warps (and only there) the two halves are ORed into the zeroed stage.
+				const uint32_t left = he_put<false>(e, carried, bp, sa, first, got);
+				const uint32_t before = __shfl_up_sync(0xffffffffu, left, 1);
+				if (tid & 31)
+					asm volatile("st.shared.u32 [%0], %1;" ::"r"(fw), "r"(first | before) : "memory");
+				else
+					sred_or(fw, first);
+				if ((tid & 31) == 31)
+					sred_or(sa, left);
+			} else {
+				// exceptions, or an end of the read: nothing is known about the neighbours' lengths, so
+				// the thread's first and last words are ORed in (the words in between are its own)
+				const uint32_t left = he_put<true>(e, carried, bp, sa, first, got);
+				if (got)
+					sred_or(fw, first);
+				if (left)
+					sred_or(sa, left);
 			}
 			__syncthreads();
 			// 4. bytes [fb, lb) are complete: the first one thanks to the carried bits, the last
@@ -928,24 +1011,19 @@ __global__ void __launch_bounds__(NT, 4) huff_emit_kernel(const __grid_constant_
 			const uint32_t cw = e0 >> 7;	// the 16-byte word holding the partial byte
 			for (uint32_t w = tid; w <= cw; w += NT) {
 				const uint4 x = reinterpret_cast<const uint4 *>(s_stage)[w];
-				reinterpret_cast<uint4 *>(s_stage)[w] = make_uint4(0, 0, 0, 0);
-				if (w == cw) {
-					const uint32_t xs[4] = {x.x, x.y, x.z, x.w};
-					const uint32_t b = (e0 >> 3) & 15;
-					s_carry = (!lastt && (e0 & 7)) ? (xs[b >> 2] >> (8 * (b & 3))) & 0xffu : 0u;
-				}
+				if (w == cw)
+					s_carry = (!lastt && (e0 & 7)) ? s_stage[e0 >> 3] : 0u;
 				const uint32_t lo = w << 4, hi = lo + 16;
 				if (lo >= fb && hi <= lb) {
 					reinterpret_cast<uint4 *>(gb)[w] = x;
 				} else {
-					const uint32_t xs[4] = {x.x, x.y, x.z, x.w};
 					const uint32_t b0 = lo < fb ? fb : lo, b1 = hi > lb ? lb : hi;
 					for (uint32_t b = b0; b < b1; b++)
-						gb[b] = (uint8_t) (xs[(b >> 2) & 3] >> (8 * (b & 3)));
+						gb[b] = s_stage[b];
 				}
+				reinterpret_cast<uint4 *>(s_stage)[w] = make_uint4(0, 0, 0, 0);
 			}
-			__syncthreads();
-			carryb = s_carry;
+			// (no barrier here: the next tile's scan has one between these stage writes and its ORs)
 			pos += tot;
 		}
 	}
