@@ -11,16 +11,25 @@
 //
 // Neither has a header whose length depends on the data, but both need one number per read before
 // the first byte of the NEXT read can be placed (data-byte count / width), so encode is a size
-// sweep, a scan, and the coding sweep.  These are coverage methods, written for clarity: one CTA
-// per read (ticket), tiles of 4096 values cut at multiples of 4096 INSIDE the read (so 16 values
-// per thread are 4 whole key bytes / 2 x width whole bytes), 16-bit sample loads.
+// sweep, a scan, and the coding sweep.  One CTA per read (ticket), tiles of 4096 values cut at
+// multiples of 4096 INSIDE the read (so 16 values per thread are 4 whole key bytes, and a tile of
+// width-bit fields ends on a byte).  Global memory is touched by whole warps on neighbouring
+// addresses only: samples come in through a padded shared-memory tile, streams leave (and enter)
+// through a stage that mirrors the 16-byte words of the container.  Both payloads are written by
+// the bit packer of the Huffman emitter (he_put, exfam.cuh): a svb0124 data section is the values
+// themselves as "codes" of 0, 8 or 16 bits; a uint-zd payload is the bit-reversed fields as codes
+// of `width` bits, with the bits of every byte reversed on the way out (most significant bit
+// first, press.c:285-397).
 #pragma once
 
 #include "exfam.cuh"
+#include "exfam_dec.cuh"
 
 namespace pg {
 
-constexpr int MT = 4096;	// values per tile, 16 per thread
+constexpr int MT = 4096;			// values per tile, 16 per thread
+constexpr int MC_XPAD = MT + 2 * (MT / 16);	// the tile's samples, two of padding after every 16
+constexpr int MC_STAGE = 2 * MT + 64;		// stream bytes of a tile (<= 2 per value) + phase + slack
 
 struct McArgs {
 	int method;
@@ -48,6 +57,11 @@ __device__ __forceinline__ uint32_t mc_minbits(uint32_t mx)	// press.c:461-471
 {
 	return mx ? 32u - __clz(mx) : 0u;
 }
+// bit 15 / 31 = (low / high halfword != 0)
+__device__ __forceinline__ uint32_t mc_nz16x2(uint32_t z)
+{
+	return (((z & 0x7fff7fffu) + 0x7fff7fffu) | z) & 0x80008000u;
+}
 
 // CTA-wide sum / max of one value per thread (two barriers)
 __device__ __forceinline__ uint64_t mc_block_sum(uint64_t v, uint64_t *s_w)
@@ -64,13 +78,18 @@ __device__ __forceinline__ uint64_t mc_block_sum(uint64_t v, uint64_t *s_w)
 	return t;
 }
 
-// size sweep: data bytes (SVB0124_ZD) / width (UINT_ZD) of every read -> r_size, r_aux
+// size sweep: data bytes (SVB0124_ZD) / width (UINT_ZD) of every read -> r_size, r_aux.  The read's
+// whole 16-byte sample groups are taken as 128-bit loads, eight zd values at a time on 16-bit pairs;
+// the up to 8 samples in front of the first whole group and the up to 7 after the last one by a
+// thread each.
 __global__ void __launch_bounds__(NT) mc_size_kernel(const __grid_constant__ McArgs a)
 {
 	__shared__ uint64_t s_w[NW];
 	__shared__ uint32_t s_read;
 	const int tid = threadIdx.x;
 	const bool svb = a.method == PRESS_GPU_SVB0124_ZD;
+	const uint4 *s4 = reinterpret_cast<const uint4 *>(a.samples);
+	const uint16_t *s16 = reinterpret_cast<const uint16_t *>(a.samples);
 	for (;;) {
 		__syncthreads();
 		if (tid == 0)
@@ -79,25 +98,47 @@ __global__ void __launch_bounds__(NT) mc_size_kernel(const __grid_constant__ McA
 		const uint64_t r = s_read;
 		if (r >= a.nreads)
 			break;
-		const uint64_t off0 = a.offsets[r], n = a.offsets[r + 1] - off0;
-		const int16_t *s = a.samples + off0;
-		uint64_t acc = 0;	// SVB0124: data bytes; UINT_ZD: max value
-		for (uint64_t i = tid; i < n; i += NT) {
-			const int32_t prev = i ? (int32_t) __ldg(s + i - 1) : 0;
-			const uint32_t z = mc_zigzag((int32_t) __ldg(s + i) - prev);
-			if (svb)
-				acc += (z != 0) + (z >= 256u);
-			else if (i)
-				acc = z > acc ? z : acc;
+		const uint64_t off0 = a.offsets[r], rend = a.offsets[r + 1], n = rend - off0;
+		uint32_t cnt = 0, mx = 0;	// SVB0124: data bytes (of this thread: < 2^32); UINT_ZD: max value, both halves
+		// one value: sample i of the read
+		auto single = [&](uint64_t i) {
+			const int32_t prev = i ? (int32_t) (int16_t) __ldg(s16 + off0 + i - 1) : 0;
+			const uint32_t z = mc_zigzag((int32_t) (int16_t) __ldg(s16 + off0 + i) - prev);
+			cnt += (z != 0) + (z >= 256u);
+			if (i)
+				mx = z > mx ? z : mx;
+		};
+		const uint64_t g0 = (off0 >> 3) + 1, g1 = rend >> 3;	// whole groups [g0, g1) past the read's first sample
+		const uint64_t head = 8 * g0 - off0 < n ? 8 * g0 - off0 : n;
+		if ((uint64_t) tid < head)
+			single(tid);
+		uint32_t mx2 = 0;
+		for (uint64_t k = g0 + tid; k < g1; k += NT) {
+			const uint4 x = __ldg(s4 + k);
+			uint32_t z[4];
+			zd_group(x, __ldg(s16 + 8 * k - 1), -1, z);
+#pragma unroll
+			for (int j = 0; j < 4; j++) {
+				// (bits 15 / 31: value != 0; bits 14 / 30: value >= 256)
+				cnt += __popc(mc_nz16x2(z[j]) | (mc_nz16x2(z[j] & 0xff00ff00u) >> 1));
+				mx2 = __vmaxu2(mx2, z[j]);
+			}
 		}
+		if (g1 >= g0) {
+			const uint64_t t0 = 8 * g1 - off0;	// the samples after the last whole group
+			if (t0 + tid < n && t0 >= head)
+				single(t0 + tid);
+		}
+		mx2 = (mx2 & 0xffffu) > (mx2 >> 16) ? (mx2 & 0xffffu) : (mx2 >> 16);
+		mx = mx2 > mx ? mx2 : mx;
 		if (svb) {
-			const uint64_t tot = mc_block_sum(acc, s_w);
+			const uint64_t tot = mc_block_sum(cnt, s_w);
 			if (tid == 0) {
 				a.r_size[r] = (n + 3) / 4 + tot;
 				a.r_aux[r] = 0;
 			}
 		} else {
-			uint32_t mx = __reduce_max_sync(0xffffffffu, (uint32_t) acc);
+			mx = __reduce_max_sync(0xffffffffu, mx);
 			__syncthreads();
 			if ((tid & 31) == 0)
 				s_w[tid >> 5] = mx;
@@ -115,35 +156,115 @@ __global__ void __launch_bounds__(NT) mc_size_kernel(const __grid_constant__ McA
 	}
 }
 
-// the thread's 16 values of tile t: zd of samples i0 .. i0 + 15 (UINT_ZD: of samples i0 + 1 ..), 0 past the end
-__device__ __forceinline__ void mc_load16(const int16_t *s, uint64_t n, uint64_t i0, bool uintzd, uint32_t (&z)[16],
-					   uint32_t &cnt)
+// The tile's samples base[t0 .. t0 + 4096) (zeros past nval) through shared memory: every warp loads
+// 32 neighbouring samples at a time, every thread then finds its 16 in 8 words of its own (the
+// padding puts the threads 9 words apart: no bank is met twice).  z: zd of the 16, two per word;
+// prev_tile: the sample before the tile's first.  One barrier inside; the caller has one between
+// this call's reads of s_x and the next call.
+__device__ __forceinline__ void mc_tile_zd(const int16_t *base, uint64_t nval, uint64_t t0, uint32_t prev_tile, uint16_t *s_x,
+					   uint32_t (&z)[8])
 {
-	const uint64_t first = uintzd ? i0 + 1 : i0;	// sample index of value 0
-	int32_t prev = first && first - 1 < n ? (int32_t) __ldg(s + first - 1) : 0;
-	cnt = 0;
+	const int tid = threadIdx.x;
+	const uint16_t *b = reinterpret_cast<const uint16_t *>(base) + t0;
+	const uint64_t left = nval - t0;
 #pragma unroll
-	for (int e = 0; e < 16; e++) {
-		z[e] = 0;
-		if (first + e < n) {
-			const int32_t x = (int32_t) __ldg(s + first + e);
-			z[e] = mc_zigzag(x - prev);
-			prev = x;
-			cnt = e + 1;
+	for (int k = 0; k < MT / NT; k++) {
+		const uint32_t i = k * NT + tid;
+		s_x[i + 2 * (i >> 4)] = i < left ? __ldg(b + i) : (uint16_t) 0;
+	}
+	__syncthreads();
+	const uint32_t *w = reinterpret_cast<const uint32_t *>(s_x) + 9 * tid;
+	const uint4 xa = make_uint4(w[0], w[1], w[2], w[3]), xb = make_uint4(w[4], w[5], w[6], w[7]);
+	const uint32_t prev = tid ? s_x[18 * tid - 3] : prev_tile;	// (sample 16 tid - 1 sits before two of padding)
+	uint32_t za[4], zb[4];
+	zd_group(xa, prev, -1, za);
+	zd_group(xb, xa.w >> 16, -1, zb);
+#pragma unroll
+	for (int j = 0; j < 4; j++) {
+		z[j] = za[j];
+		z[4 + j] = zb[j];
+	}
+	// values past the end are no values
+	const uint64_t j0 = 16ull * tid;
+	if (j0 + 16 > left) {
+		const uint32_t cnt = j0 < left ? (uint32_t) (left - j0) : 0u;
+#pragma unroll
+		for (int j = 0; j < 8; j++)
+			z[j] &= (2 * j < (int) cnt ? 0xffffu : 0u) | (2 * j + 1 < (int) cnt ? 0xffff0000u : 0u);
+	}
+}
+
+// The tile's stage -> the container.  The stage mirrors global memory from the 16-byte word g16 on;
+// its bytes [fb, lb) are the tile's.  Whole words go out as they are, the others byte by byte (the
+// neighbours' bytes belong to other tiles or reads).  REV: the bits of every byte are reversed on
+// the way (uint-zd).  The stage is left zeroed.  One CTA.
+template <bool REV>
+__device__ __forceinline__ void mc_copy_out(uint8_t *s_stage, uint8_t *g16, uint32_t fb, uint32_t lb)
+{
+	const uint32_t nw = (lb + 15) >> 4;
+	for (uint32_t w = threadIdx.x; w < nw; w += NT) {
+		uint4 x = reinterpret_cast<const uint4 *>(s_stage)[w];
+		reinterpret_cast<uint4 *>(s_stage)[w] = make_uint4(0, 0, 0, 0);
+		if (REV) {
+			x.x = __byte_perm(__brev(x.x), 0, 0x0123);
+			x.y = __byte_perm(__brev(x.y), 0, 0x0123);
+			x.z = __byte_perm(__brev(x.z), 0, 0x0123);
+			x.w = __byte_perm(__brev(x.w), 0, 0x0123);
+		}
+		const uint32_t lo = w << 4, hi = lo + 16;
+		if (lo >= fb && hi <= lb) {
+			reinterpret_cast<uint4 *>(g16)[w] = x;
+		} else {
+			const uint32_t b0 = lo < fb ? fb : lo, b1 = hi > lb ? lb : hi;
+			for (uint32_t b = b0; b < b1; b++) {
+				const uint32_t j = b & 15, v = j < 4 ? x.x : j < 8 ? x.y : j < 12 ? x.z : x.w;
+				g16[b] = (uint8_t) (v >> (8 * (j & 3)));
+			}
 		}
 	}
 }
 
-// coding sweep
-__global__ void __launch_bounds__(NT) mc_encode_kernel(const __grid_constant__ McArgs a)
+// The thread's 16 codes (e[]: code << 8 | bits, see he_put) into the zeroed stage at bit bp.  A warp
+// whose threads all bring a word's worth of bits passes the shared words along by shuffle; any
+// other warp, and every warp at its two ends, ORs them in.
+__device__ __forceinline__ void mc_put(const uint32_t (&e)[16], uint32_t bits, uint32_t bp, uint32_t stage_sa)
 {
-	__shared__ __align__(16) uint8_t s_stage[2 * MT + 64];
+	const int lane = threadIdx.x & 31;
+	const uint32_t fw = stage_sa + ((bp >> 3) & ~3u);
+	uint32_t sa = fw, first;
+	bool got;
+	const uint32_t left = he_put<true>(e, 0u, bp, sa, first, got);
+	if (__all_sync(0xffffffffu, bits >= 32)) {
+		const uint32_t before = __shfl_up_sync(0xffffffffu, left, 1);
+		if (lane)
+			asm volatile("st.shared.u32 [%0], %1;" ::"r"(fw), "r"(first | before) : "memory");
+		else
+			sred_or(fw, first);
+		if (lane == 31)
+			sred_or(sa, left);
+	} else {
+		if (got)
+			sred_or(fw, first);
+		if (left)
+			sred_or(sa, left);
+	}
+}
+
+// coding sweep
+__global__ void __launch_bounds__(NT, 4) mc_encode_kernel(const __grid_constant__ McArgs a)
+{
+	__shared__ __align__(16) uint8_t s_stage[MC_STAGE];
+	__shared__ __align__(16) uint16_t s_x[MC_XPAD];
+	__shared__ __align__(16) uint32_t s_keys[NT + 8];
 	__shared__ __align__(16) uint32_t s_warp[NW];
 	__shared__ uint32_t s_read;
 	const int tid = threadIdx.x;
 	const bool svb = a.method == PRESS_GPU_SVB0124_ZD;
 	if (a.hdr->error & ERR_CAPACITY)
 		return;
+	for (int w = tid; w < MC_STAGE / 16; w += NT)
+		reinterpret_cast<uint4 *>(s_stage)[w] = make_uint4(0, 0, 0, 0);
+	const uint32_t stage_sa = (uint32_t) __cvta_generic_to_shared(s_stage);
 	for (;;) {
 		__syncthreads();
 		if (tid == 0)
@@ -158,35 +279,33 @@ __global__ void __launch_bounds__(NT) mc_encode_kernel(const __grid_constant__ M
 		const int16_t *s = a.samples + off0;
 		uint8_t *dst = a.out + a.out_offsets[r];
 		if (svb) {
+			// streamvbyte_0124_encode.c:8-59: keys, then the values' bytes
 			const uint64_t nk = (n + 3) / 4;
 			uint8_t *data = dst + nk;
 			uint64_t D = 0;		// data bytes written so far
 			for (uint64_t t0 = 0; t0 < n; t0 += MT) {
-				const uint64_t i0 = t0 + 16 * tid;
-				uint32_t z[16], cnt;
-				mc_load16(s, n, i0, false, z, cnt);
-				uint32_t nb = 0, keys = 0;
+				uint32_t z[8], e[16];
+				mc_tile_zd(s, n, t0, t0 ? (uint32_t) (uint16_t) __ldg(s + t0 - 1) : 0u, s_x, z);
+				uint32_t keys = 0;
 #pragma unroll
-				for (int e = 0; e < 16; e++) {
-					const uint32_t code = (uint32_t) e < cnt ? (z[e] != 0) + (z[e] >= 256u) : 0u;	// streamvbyte_0124_encode.c:8-29
-					nb += code;
-					keys |= code << (2 * e);
+				for (int i = 0; i < 16; i++) {
+					const uint32_t v = (z[i >> 1] >> (16 * (i & 1))) & 0xffffu;
+					const uint32_t code = (v != 0) + (v >= 256u);	// (zd < 65536: never four bytes)
+					keys |= code << (2 * i);
+					e[i] = (v << 8) | (8 * code);
 				}
+				s_keys[tid] = keys;
+				const uint32_t nb = __popc(keys & 0x55555555u) + 2 * __popc(keys & 0xaaaaaaaau);
 				uint32_t c1[1] = {nb}, e1[1], tot;
 				block_scan<1>(c1, e1, tot, s_warp);
-				uint8_t *p = s_stage + e1[0];
-#pragma unroll
-				for (int e = 0; e < 16; e++) {
-					if ((uint32_t) e < cnt && z[e]) {
-						*p++ = (uint8_t) z[e];
-						if (z[e] >= 256u)
-							*p++ = (uint8_t) (z[e] >> 8);
-					}
-				}
-				for (uint32_t q = 0; 4 * q < cnt; q++)	// key byte i >> 2; unused high bits 0 (:56)
-					dst[i0 / 4 + q] = (uint8_t) (keys >> (8 * q));
+				uint8_t *g = data + D;
+				const uint32_t s0 = (uint32_t) (reinterpret_cast<uintptr_t>(g) & 15);
+				mc_put(e, 8 * nb, 8 * (s0 + e1[0]), stage_sa);
 				__syncthreads();
-				block_copy_out(s_stage, data + D, tot);
+				mc_copy_out<false>(s_stage, g - s0, s0, s0 + tot);
+				const uint64_t left = n - t0;
+				block_copy_out(reinterpret_cast<const uint8_t *>(s_keys), dst + t0 / 4,
+					       (uint32_t) (((left < MT ? left : MT) + 3) / 4));	// (unused high bits of the last key byte: 0, :56)
 				D += tot;
 				__syncthreads();
 			}
@@ -198,43 +317,78 @@ __global__ void __launch_bounds__(NT) mc_encode_kernel(const __grid_constant__ M
 				dst[2] = (uint8_t) bits;
 			}
 			uint8_t *pk = dst + 3;
-			const uint64_t m = n - 1;	// values
+			const uint64_t m = n - 1;	// values: zd of samples 1 ..
 			for (uint64_t t0 = 0; t0 < m && bits; t0 += MT) {
-				const uint64_t j0 = t0 + 16 * tid;
-				if (j0 >= m)
-					continue;
-				uint32_t z[16], cnt;
-				mc_load16(s, n, j0, true, z, cnt);
-				// 16 fields of `bits` bits, most significant bit first: 2 x bits whole bytes
-				uint8_t *p = pk + j0 / 16 * (2ull * bits);
-				uint64_t acc = 0;
-				uint32_t have = 0;
+				uint32_t z[8], e[16];
+				mc_tile_zd(s + 1, m, t0, (uint32_t) (uint16_t) __ldg(s + t0), s_x, z);
+				const uint64_t left = m - t0;
+				const uint32_t cntt = left < MT ? (uint32_t) left : (uint32_t) MT;
+				const uint32_t cnt = 16u * tid >= cntt ? 0u : (cntt - 16u * tid < 16u ? cntt - 16u * tid : 16u);
 #pragma unroll
-				for (int e = 0; e < 16; e++) {
-					if ((uint32_t) e < cnt) {
-						acc = (acc << bits) | z[e];
-						have += bits;
-						while (have >= 8) {
-							*p++ = (uint8_t) (acc >> (have - 8));
-							have -= 8;
-						}
-					}
+				for (int i = 0; i < 16; i++) {
+					const uint32_t v = (z[i >> 1] >> (16 * (i & 1))) & 0xffffu;
+					// the field's bits in stream order, first (most significant) bit lowest
+					e[i] = (uint32_t) i < cnt ? ((__brev(v) >> (32 - bits)) << 8) | bits : 0u;
 				}
-				if (have)	// the run's last byte, zero padded (press.c:386-390)
-					*p = (uint8_t) (acc << (8 - have));
+				uint8_t *g = pk + t0 / 8 * bits;	// (4096 fields end on a byte)
+				const uint32_t s0 = (uint32_t) (reinterpret_cast<uintptr_t>(g) & 15);
+				mc_put(e, cnt * bits, 8 * s0 + 16u * bits * tid, stage_sa);
+				__syncthreads();
+				// the run's last byte is zero padded (press.c:386-390)
+				mc_copy_out<true>(s_stage, g - s0, s0, s0 + (cntt * bits + 7) / 8);
+				__syncthreads();
 			}
 		}
 	}
 }
 
+// ---------------------------------------------------------------------------
 // decode: stream -> samples (press.c:1631-1643 / 674-687: values, un-zigzag, running sum mod 2^16)
-__global__ void __launch_bounds__(NT) mc_decode_kernel(const __grid_constant__ McArgs a)
+
+// stream bytes [g, g + len) -> the stage, from the 16-byte word holding g on (whole words, guarded at
+// the container's ends).  REV: the bits of every byte reversed (uint-zd: fields then read LSB first).
+template <bool REV>
+__device__ __forceinline__ void mc_stage_in(uint8_t *s_stage, const uint8_t *g, uint32_t len, const uint8_t *lim_lo,
+					    const uint8_t *lim_hi)
 {
+	const uint32_t al = (uint32_t) (reinterpret_cast<uintptr_t>(g) & 15);
+	const uint8_t *b16 = g - al;
+	const uint32_t nw = (al + len + 15) >> 4;
+	for (uint32_t w = threadIdx.x; w < nw + 1; w += NT) {	// (+ 1: the windows read a word past the last byte)
+		uint4 x = w < nw ? load_word_guarded(b16, w, lim_lo, lim_hi) : make_uint4(0, 0, 0, 0);
+		if (REV) {
+			x.x = __byte_perm(__brev(x.x), 0, 0x0123);
+			x.y = __byte_perm(__brev(x.y), 0, 0x0123);
+			x.z = __byte_perm(__brev(x.z), 0, 0x0123);
+			x.w = __byte_perm(__brev(x.w), 0, 0x0123);
+		}
+		reinterpret_cast<uint4 *>(s_stage)[w] = x;
+	}
+}
+
+// 64 stream bits from stage bit `pos` on
+__device__ __forceinline__ void mc_window(uint32_t stage_sa, uint32_t pos, uint32_t &lo, uint32_t &hi)
+{
+	const uint32_t a = stage_sa + ((pos >> 3) & ~3u);
+	uint32_t w0, w1, w2;
+	asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w0) : "r"(a));
+	asm volatile("ld.shared.u32 %0, [%1+4];" : "=r"(w1) : "r"(a));
+	asm volatile("ld.shared.u32 %0, [%1+8];" : "=r"(w2) : "r"(a));
+	lo = __funnelshift_r(w0, w1, pos);	// (shift taken mod 32)
+	hi = __funnelshift_r(w1, w2, pos);
+}
+
+__global__ void __launch_bounds__(NT, 4) mc_decode_kernel(const __grid_constant__ McArgs a)
+{
+	__shared__ __align__(16) uint8_t s_stage[MC_STAGE + 16];
+	__shared__ __align__(16) uint32_t s_out[MT / 2 + 8];	// the tile's samples on their way out
 	__shared__ __align__(16) uint32_t s_warp[NW];
 	__shared__ __align__(16) uint32_t s_warp2[NW];
 	__shared__ uint32_t s_read;
 	const int tid = threadIdx.x;
 	const bool svb = a.method == PRESS_GPU_SVB0124_ZD;
+	const uint32_t stage_sa = (uint32_t) __cvta_generic_to_shared(s_stage);
+	const uint8_t *lim_hi = a.in + a.in_bytes;
 	for (;;) {
 		__syncthreads();
 		if (tid == 0)
@@ -272,51 +426,79 @@ __global__ void __launch_bounds__(NT) mc_decode_kernel(const __grid_constant__ M
 		bool overrun = false;
 		for (uint64_t t0 = 0; t0 < nval && !overrun; t0 += MT) {
 			const uint64_t j0 = t0 + 16 * tid;
+			const uint32_t cntt = nval - t0 < MT ? (uint32_t) (nval - t0) : (uint32_t) MT;
 			const uint32_t cnt = j0 >= nval ? 0u : (nval - j0 < 16 ? (uint32_t) (nval - j0) : 16u);
 			uint32_t v[16];
 			if (svb) {
-				uint32_t keys = 0, nb = 0;
+				// the thread's 4 key bytes (neighbouring threads, neighbouring bytes)
+				uint32_t keys = 0;
 				for (uint32_t q = 0; 4 * q < cnt; q++)
 					keys |= (uint32_t) src[j0 / 4 + q] << (8 * q);
-#pragma unroll
-				for (int e = 0; e < 16; e++) {
-					const uint32_t code = (uint32_t) e < cnt ? (keys >> (2 * e)) & 3u : 0u;
-					nb += code == 3 ? 4u : code;	// streamvbyte_0124_decode: 0, 1, 2 or 4 bytes
-				}
+				if (cnt < 16)
+					keys &= (1u << (2 * cnt)) - 1;
+				// streamvbyte_0124_decode: 0, 1, 2 or 4 bytes
+				const uint32_t k3 = keys & (keys >> 1) & 0x55555555u;
+				const uint32_t nb = __popc(keys & 0x55555555u) + 2 * __popc(keys & 0xaaaaaaaau) + __popc(k3);
 				uint32_t c1[1] = {nb}, e1[1], tot;
 				block_scan<1>(c1, e1, tot, s_warp);
 				if (D + tot > ndata) {	// (the same in every thread)
 					overrun = true;
 					break;
 				}
-				const uint8_t *p = data + D + e1[0];
+				const uint8_t *g = data + D;
+				if (tot > 2u * MT) {
+					// four-byte values (never written for a 16-bit signal, but a valid stream): more than the
+					// stage holds, so byte by byte from the container
+					const uint8_t *p = g + e1[0];
+#pragma unroll 1
+					for (int e = 0; e < 16; e++) {
+						const uint32_t code = (keys >> (2 * e)) & 3u, len = code == 3 ? 4u : code;
+						uint32_t x = 0;
+						for (uint32_t b = 0; b < len; b++)
+							x |= (uint32_t) p[b] << (8 * b);
+						p += len;
 #pragma unroll
-				for (int e = 0; e < 16; e++) {
-					const uint32_t code = (uint32_t) e < cnt ? (keys >> (2 * e)) & 3u : 0u;
-					uint32_t x = 0;
-					const uint32_t len = code == 3 ? 4u : code;
-					for (uint32_t b = 0; b < len; b++)
-						x |= (uint32_t) p[b] << (8 * b);
-					p += len;
-					v[e] = x;
+						for (int k = 0; k < 16; k++)	// (static indices: v stays in registers)
+							if (k == e)
+								v[k] = x;
+					}
+				} else {
+					mc_stage_in<false>(s_stage, g, tot, a.in, lim_hi);
+					__syncthreads();
+					uint32_t pos = 8 * ((uint32_t) (reinterpret_cast<uintptr_t>(g) & 15) + e1[0]), lo = 0, hi = 0;
+#pragma unroll
+					for (int e = 0; e < 16; e++) {
+						if (e % 2 == 0)
+							mc_window(stage_sa, pos, lo, hi);
+						const uint32_t code = (keys >> (2 * e)) & 3u;
+						const uint32_t l = code == 3 ? 32u : 8 * code;
+						v[e] = code == 3 ? lo : lo & ((1u << l) - 1);
+						if (code == 3) {
+							lo = hi;
+							hi = 0;
+						} else {
+							lo = __funnelshift_r(lo, hi, l);
+							hi >>= l;
+						}
+						pos += l;
+					}
 				}
 				D += tot;
 			} else {
-				// 16 fields of `bits` bits from byte 2 * bits * (j0 / 16) on, most significant bit first
-				const uint8_t *p = data + j0 / 16 * (2ull * bits);
-				uint64_t acc = 0;
-				uint32_t have = 0;
+				// 16 fields of `bits` bits from bit 16 * bits * (j0 / 16) of the payload on, most significant bit first
+				const uint8_t *g = data + t0 / 8 * bits;
+				mc_stage_in<true>(s_stage, g, (cntt * bits + 7) / 8, a.in, lim_hi);
+				__syncthreads();
+				uint32_t pos = 8 * (uint32_t) (reinterpret_cast<uintptr_t>(g) & 15) + 16u * bits * tid, lo = 0, hi = 0;
 #pragma unroll
 				for (int e = 0; e < 16; e++) {
-					v[e] = 0;
-					if ((uint32_t) e < cnt && bits) {
-						while (have < bits) {
-							acc = (acc << 8) | *p++;
-							have += 8;
-						}
-						v[e] = (uint32_t) (acc >> (have - bits)) & ((1u << bits) - 1);
-						have -= bits;
-					}
+					if (e % 2 == 0)
+						mc_window(stage_sa, pos, lo, hi);
+					const uint32_t f = bits ? __brev(lo) >> (32 - bits) : 0u;	// (the field's first bit is its most significant)
+					v[e] = (uint32_t) e < cnt ? f : 0u;
+					lo = __funnelshift_r(lo, hi, bits);
+					hi >>= bits;
+					pos += bits;
 				}
 			}
 			// un-zigzag (on 32 bits, trans.c:272-282 / 16 bits, :251-258; the sum is kept mod 2^16)
@@ -330,13 +512,16 @@ __global__ void __launch_bounds__(NT) mc_decode_kernel(const __grid_constant__ M
 			uint32_t c1[1] = {run}, e1[1], tot;
 			block_scan<1>(c1, e1, tot, s_warp2);
 			const uint32_t base = carry + e1[0];
-			int16_t *o = dst + (svb ? j0 : j0 + 1);
+			uint32_t o[8];
 #pragma unroll
-			for (int e = 0; e < 16; e++)
-				if ((uint32_t) e < cnt)
-					o[e] = (int16_t) (uint16_t) (base + y[e]);
+			for (int j = 0; j < 8; j++)
+				o[j] = ((base + y[2 * j]) & 0xffffu) | ((base + y[2 * j + 1]) << 16);
+			reinterpret_cast<uint4 *>(s_out)[2 * tid] = make_uint4(o[0], o[1], o[2], o[3]);
+			reinterpret_cast<uint4 *>(s_out)[2 * tid + 1] = make_uint4(o[4], o[5], o[6], o[7]);
 			carry = (carry + tot) & 0xffffu;
-			__syncthreads();	// s_warp / s_warp2 are written again by the next tile
+			__syncthreads();
+			block_copy_out(reinterpret_cast<const uint8_t *>(s_out), reinterpret_cast<uint8_t *>(dst + (svb ? t0 : t0 + 1)), 2 * cntt);
+			__syncthreads();	// s_stage / s_out / s_warp / s_warp2 are written again by the next tile
 		}
 		if (overrun && tid == 0)
 			atomicOr(&a.hdr->error, ERR_MALFORMED);
