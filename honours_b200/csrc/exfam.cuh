@@ -569,8 +569,8 @@ __global__ void __launch_bounds__(NT, PG_COUNT_CTAS) ex_count_kernel(const __gri
 					(void) ex_compute_fast(C, q, v, orw);
 					or_thr |= orw;
 					v.i0 = (int64_t) t * XT - T.m + 16 * tid;
-					if (!HUFF)	// (ex-zd: the pass with the final q comes last)
-						*ex_lowb_ptr(a.lowb, A, t, tid) =
+					// (ex-zd: the pass with the final q comes last)
+					*ex_lowb_ptr(a.lowb, A, t, tid) =
 							make_uint4(__byte_perm(v.z[0], v.z[1], 0x6420), __byte_perm(v.z[2], v.z[3], 0x6420),
 								   __byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420));
 				} else {
@@ -917,40 +917,62 @@ __global__ void __launch_bounds__(NT, PG_HE_CTAS) huff_emit_kernel(const __grid_
 		const uint32_t nt = T.ntiles;
 		uint8_t *pay = a.out + a.out_offsets[r] + hdr;	// first payload byte of the read
 		uint16_t *sc = a.sidecar ? a.sidecar + (T.off0 >> 4) + r : nullptr;
-		ExRaw W;
-		ex_issue(a.samples, a.nsamples, A, W);
 		uint64_t pos = 0;	// payload bits written so far
 		// (the bits of the last, still partial byte wait in s_carry: 0 at every read's start)
 		// exceptions in the tile's eight slices, as sweep 1 counted them: a tile without any inside
-		// the read takes the path without masks and without the symbol-count scan
+		// the read ("all": every element a payload symbol) takes the path without masks and without the
+		// symbol-count scan, and starts from the low bytes sweep 1 left (16 bytes per thread instead of
+		// 32 of samples, no zd); the others start from the samples again
 		const uint4 *rec = reinterpret_cast<const uint4 *>(a.t_nex + (uint64_t) g0 * NW);
-		uint4 ra = __ldg(rec), rb = __ldg(rec + 1);
+		auto tile_all = [&](uint32_t t, const uint4 &ra, const uint4 &rb) {
+			const int64_t f = (int64_t) t * XT - T.m;
+			return f >= 1 && f + XT <= (int64_t) n && !(ra.x | ra.y | ra.z | ra.w | rb.x | rb.y | rb.z | rb.w);
+		};
+		// one tile ahead in registers: the low bytes or the samples; records two tiles ahead
+		ExRaw W;
+		uint4 Lw = make_uint4(0, 0, 0, 0);
+		bool all = tile_all(0, __ldg(rec), __ldg(rec + 1)), all_next = false;	// (tile 0 holds the first sample: never all)
+		ex_issue(a.samples, a.nsamples, A, W);
+		uint4 ra = make_uint4(1, 0, 0, 0), rb = ra;
+		if (nt > 1) {
+			ra = __ldg(rec + 2);
+			rb = __ldg(rec + 3);
+		}
 		uint32_t psym = 0;	// payload symbols written so far (side-car index)
-		for (uint32_t t = 0; t < nt; t++) {
+		for (uint32_t t = 0; t < nt; t++, all = all_next) {
 			T.t = t;
 			T.k0 = A + (uint64_t) t * XG;
 			const ExRaw C = W;
-			if (t + 1 < nt)
-				ex_issue(a.samples, a.nsamples, T.k0 + XG, W);
-			if (t + PG_PF_COUNT < nt)
-				prefetch_l2(a.samples + T.k0 + PG_PF_COUNT * XG + 2 * tid);
-			const int64_t f = (int64_t) t * XT - T.m;
-			const bool inside = f >= 1 && f + XT <= (int64_t) n;
-			const bool all = inside && !(ra.x | ra.y | ra.z | ra.w | rb.x | rb.y | rb.z | rb.w);
+			const uint4 Lc = Lw;
+			all_next = t + 1 < nt && tile_all(t + 1, ra, rb);
 			if (t + 1 < nt) {
-				ra = __ldg(rec + 2 * (t + 1));
-				rb = __ldg(rec + 2 * (t + 1) + 1);
+				if (all_next)
+					Lw = __ldg(ex_lowb_ptr(a.lowb, A, t + 1, tid));
+				else
+					ex_issue(a.samples, a.nsamples, T.k0 + XG, W);
 			}
-			ExVals v;
-			if (inside) {
-				uint32_t orw;
-				(void) ex_compute_fast(C, 0, v, orw);
-			} else {
-				ex_compute(C, T, 0, v);
+			if (t + 2 < nt) {
+				ra = __ldg(rec + 2 * (t + 2));
+				rb = __ldg(rec + 2 * (t + 2) + 1);
 			}
-			const uint32_t ne = v.valid & ~v.exc & ~v.first;
-			const uint32_t qv[4] = {__byte_perm(v.z[0], v.z[1], 0x6420), __byte_perm(v.z[2], v.z[3], 0x6420),
-						__byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420)};
+			if (t + PG_PF_COUNT + 1 < nt)	// (not the read's last tile: its low bytes may lie past the scratch)
+				prefetch_l2(ex_lowb_ptr(a.lowb, A, t + PG_PF_COUNT, tid));
+			uint32_t ne = 0xffffu, qv[4] = {Lc.x, Lc.y, Lc.z, Lc.w};
+			if (!all) {
+				const int64_t f = (int64_t) t * XT - T.m;
+				ExVals v;
+				if (f >= 1 && f + XT <= (int64_t) n) {
+					uint32_t orw;
+					(void) ex_compute_fast(C, 0, v, orw);
+				} else {
+					ex_compute(C, T, 0, v);
+				}
+				ne = v.valid & ~v.exc & ~v.first;
+				qv[0] = __byte_perm(v.z[0], v.z[1], 0x6420);
+				qv[1] = __byte_perm(v.z[2], v.z[3], 0x6420);
+				qv[2] = __byte_perm(v.z[4], v.z[5], 0x6420);
+				qv[3] = __byte_perm(v.z[6], v.z[7], 0x6420);
+			}
 			// payload index of the thread's first symbol
 			uint32_t si = psym + 16 * tid, nsym = XT;
 			if (!all) {
