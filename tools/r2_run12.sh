@@ -7,4 +7,3 @@ timeout 300 python bench.py --method $m --reads 60000 --steps 2 --warmup 1 --met
 python -c "
 import json; b=json.load(open('$O/bench_${m}_$T.json')); print('$m', b['value'], b['compress_gbs'], b['decompress_gbs'], b['bytes_per_sample'], {k:(v['frac'],v['ms_per_launch']) for k,v in b['kernels'].items()})"
 done
-bash tools/ncu_list.sh $T 20000 svb0124_zd uint_zd
