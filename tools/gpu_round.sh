@@ -30,9 +30,10 @@ ncu --set full --clock-control none --import-source on -k regex:svb_ -s 2 -c 2 \
     -f -o $O/prof_svb16_zd_$TAG $SHORT > $O/ncu_full_$TAG.log 2>&1
 echo "ncu full exit $?"
 # the exception / Huffman methods: launch lists and one full capture per kernel (20 k reads)
-bash tools/ncu_list.sh $TAG 20000 vbe21_zd shuff_vbe21_zd > $O/ncu_list_ex_$TAG.log 2>&1
+bash tools/ncu_list.sh $TAG 20000 vbe21_zd shuff_vbe21_zd svb0124_zd uint_zd > $O/ncu_list_ex_$TAG.log 2>&1
 bash tools/ncu_full.sh $TAG 20000 vbe21_zd ex_count ex_emit_bytes ex_decode2 > $O/ncu_full_vbe21_$TAG.log 2>&1
 bash tools/ncu_full.sh $TAG 20000 shuff_vbe21_zd ex_count huff_emit huff_fused > $O/ncu_full_shuff_$TAG.log 2>&1
+bash tools/ncu_full.sh $TAG 20000 svb0124_zd mc_size mc_encode mc_decode > $O/ncu_full_svb0124_$TAG.log 2>&1
 # digest on the box (ncu is here), then drop the captures: gpurun brings back at most 64 MiB
 python tools/round_digest.py $TAG $O/digest_$TAG > $O/digest_$TAG.log 2>&1; tail -2 $O/digest_$TAG.log
 rm -f $O/*.ncu-rep

@@ -39,7 +39,8 @@ for a, b in [(f"pytest_gpu_{tag}.log", f"{tag}_pytest_gpu.log"), (f"smoke_{tag}.
 pd.launches(os.path.join(G, f"launches_svb16_zd_{tag}.csv"), os.path.join(P, f"{tag}_svb16_zd_launches.txt"))
 pd.kernels(os.path.join(G, f"prof_svb16_zd_{tag}.ncu-rep"), os.path.join(P, f"{tag}_svb16_zd_kernels.txt"))
 caps = {"vbe21_zd": ["ex_count", "ex_emit_bytes", "ex_decode2"],
-        "shuff_vbe21_zd": ["ex_count", "huff_emit", "huff_fused"]}
+        "shuff_vbe21_zd": ["ex_count", "huff_emit", "huff_fused"],
+        "svb0124_zd": ["mc_size", "mc_encode", "mc_decode"], "uint_zd": []}
 for m, ks in caps.items():
     lc = os.path.join(G, f"launches_{m}_{tag}.csv")
     if os.path.exists(lc):
