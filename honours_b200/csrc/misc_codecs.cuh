@@ -443,12 +443,10 @@ __global__ void __launch_bounds__(NT, 4) mc_decode_kernel(const __grid_constant_
 			const uint32_t cntt = nval - t0 < MT ? (uint32_t) (nval - t0) : (uint32_t) MT;
 			const uint32_t cnt = j0 >= nval ? 0u : (nval - j0 < 16 ? (uint32_t) (nval - j0) : 16u);
 			uint32_t v[16];
-			bool wide = false;	// a four-byte value among the thread's
 			if (svb) {
 				const uint32_t keys = keys_next;
 				if (t0 + MT < nval)
 					keys_next = load_keys(t0 + MT);
-				wide = (keys & (keys >> 1) & 0x55555555u) != 0;
 				// streamvbyte_0124_decode: 0, 1, 2 or 4 bytes
 				const uint32_t k3 = keys & (keys >> 1) & 0x55555555u;
 				const uint32_t nb = __popc(keys & 0x55555555u) + 2 * __popc(keys & 0xaaaaaaaau) + __popc(k3);
@@ -518,26 +516,15 @@ __global__ void __launch_bounds__(NT, 4) mc_decode_kernel(const __grid_constant_
 					pos += bits;
 				}
 			}
-			// un-zigzag (on 32 bits, trans.c:272-282 / 16 bits, :251-258; the sum is kept mod 2^16), running
-			// sum inside the thread on 16-bit pairs, then over the CTA
+			// un-zigzag the values' low 16 bits (trans.c:272-282 hands every value to unzigzag_one_16, which
+			// takes a uint16_t: a four-byte value counts by its low half), running sum inside the thread on
+			// 16-bit pairs, then over the CTA
 			uint32_t y[8], cs = 0;
-			if (!wide) {
 #pragma unroll
-				for (int j = 0; j < 8; j++) {
-					const uint32_t d = unzigzag16x2(v[2 * j] | (v[2 * j + 1] << 16));	// (values past cnt are 0)
-					y[j] = add16x2(d * 0x00010001u, cs);
-					cs = __byte_perm(y[j], 0, 0x3232);
-				}
-			} else {
-				uint32_t run = 0;
-#pragma unroll
-				for (int j = 0; j < 8; j++) {
-					const uint32_t d0 = (v[2 * j] >> 1) ^ (0u - (v[2 * j] & 1u)), d1 = (v[2 * j + 1] >> 1) ^ (0u - (v[2 * j + 1] & 1u));
-					const uint32_t r0 = (run + d0) & 0xffffu;
-					run = (r0 + d1) & 0xffffu;
-					y[j] = r0 | (run << 16);
-				}
-				cs = run;
+			for (int j = 0; j < 8; j++) {
+				const uint32_t d = unzigzag16x2((v[2 * j] & 0xffffu) | (v[2 * j + 1] << 16));	// (values past cnt are 0)
+				y[j] = add16x2(d * 0x00010001u, cs);
+				cs = __byte_perm(y[j], 0, 0x3232);
 			}
 			uint32_t c1[1] = {cs & 0xffffu}, e1[1], tot;
 			block_scan<1>(c1, e1, tot, s_warp2);

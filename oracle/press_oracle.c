@@ -932,7 +932,10 @@ static int svb0124_zd_depress(const uint8_t *in, uint64_t n, int16_t *out, uint6
 			v = get_u32(data);
 			data += 4;
 		}
-		acc = (uint16_t) (acc + (uint16_t) ((v >> 1) ^ (0u - (v & 1u))));
+		/* trans.c:272-282 hands the uint32 value to unzigzag_one_16(uint16_t), trans.c:80-83: a four-byte
+		 * value counts by its low half (a 16-bit signal never makes the encoder write one) */
+		const uint16_t z = (uint16_t) v;
+		acc = (uint16_t) (acc + (uint16_t) ((z >> 1) ^ (uint16_t) (0u - (z & 1u))));
 		out[i] = (int16_t) acc;
 	}
 	*nout = n;

@@ -1,6 +1,7 @@
 import os
 import sys
 
+import numpy as _np
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -45,3 +46,21 @@ def checker(oracle):
         r.set_huffman_table(open(os.path.join(ROOT, "honours_b200", "data", "NA12878_zd.huffman"), "rb").read())
         return r
     return oracle
+
+
+def svb0124_stream(rng, n, p4):
+    """a hand-made svb0124 stream (streamvbyte_0124_encode.c:8-59 layout) whose values take 0, 1, 2 or 4
+    bytes: a 16-bit signal never makes the reference write a 4-byte value, but its decoder reads them"""
+    codes = rng.choice(4, size=n, p=[0.1, 0.6 - p4, 0.3, p4]).astype(_np.uint8)
+    keys = _np.zeros((n + 3) // 4, dtype=_np.uint8)
+    for sh in range(4):
+        part = codes[sh::4]
+        keys[: part.size] |= part << (2 * sh)
+    data = bytearray()
+    for c in codes:
+        nb = (0, 1, 2, 4)[c]
+        b = bytearray(rng.integers(0, 256, nb, dtype=_np.uint8).tobytes())
+        if nb:
+            b[-1] |= 1          # (a nonzero top byte, as an encoder would have it)
+        data += b
+    return keys.tobytes() + bytes(data)

@@ -8,6 +8,8 @@ import os
 import numpy as np
 import pytest
 
+from conftest import svb0124_stream
+
 pytestmark = pytest.mark.gpu
 
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
@@ -137,6 +139,17 @@ def test_long_read_many_tiles(gpu, oracle):
         assert rc == 0 and st == oracle.press(method, s)[1]
         rc, back = gpu.depress(method, st, s.size)
         assert rc == 0 and np.array_equal(back, s)
+
+
+@pytest.mark.parametrize("n,p4", [(5000, 0.002), (9000, 0.02), (12000, 0.55), (4099, 0.58)])
+def test_svb0124_decodes_four_byte_values(gpu, checker, n, p4):
+    """svb0124-zd decode of values wider than 16 bits: a few among many (the per-thread 32-bit path) and
+    tiles that hold more bytes than the shared-memory stage (read from the container byte by byte)"""
+    rng = np.random.default_rng(n)
+    st = svb0124_stream(rng, n, p4)
+    rc0, want = checker.depress("svb0124_zd", st, n)
+    rc, got = gpu.depress("svb0124_zd", st, n)
+    assert rc == rc0 == 0 and np.array_equal(got, want)
 
 
 @pytest.mark.parametrize("method", ["svb16_zd", "vbe21_zd", "vbsse21_zd", "ex_zd", "shuff_vbe21_zd", "vbbe21_zd",

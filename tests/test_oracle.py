@@ -153,6 +153,18 @@ def test_scalar_twin_nosimd_equals_simd(oracle, ref):
         assert rc == 0 and np.array_equal(back, s)
 
 
+def test_svb0124_four_byte_values_pinned(oracle, ref):
+    """svb0124-zd decode of hand-made streams with 4-byte values (the reference's encoder never writes
+    one for a 16-bit signal; its decoder takes them and keeps their low 16 bits, trans.c:272-282 ->
+    unzigzag_one_16): the restatement follows the compiled reference"""
+    from conftest import svb0124_stream
+    for n, p4 in [(1, 0.5), (7, 0.4), (5000, 0.002), (9000, 0.02), (12000, 0.55), (4099, 0.58)]:
+        st = svb0124_stream(np.random.default_rng(n), n, p4)
+        rc0, want = ref.depress("svb0124_zd", st, n)
+        rc, got = oracle.depress("svb0124_zd", st, n)
+        assert rc == rc0 == 0 and np.array_equal(got, want), (n, p4)
+
+
 def test_hash_batch_matches_per_read_hashes(oracle, ref, three_reads):
     """the multi-threaded fingerprint used by the bench-scale GPU parity test"""
     samples, offsets, _ = three_reads
