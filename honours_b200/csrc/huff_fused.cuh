@@ -516,6 +516,33 @@ __global__ void __launch_bounds__(NT, 4) huff_fused_decode_kernel(const __grid_c
 							zz[2 * j] = sext8x2(v, 0x9180);
 							zz[2 * j + 1] = sext8x2(v, 0xb3a2);
 						}
+					} else if (valid == 0xffffu && jf >= 0 && (e + 1 >= e_hi || (uint64_t) xs[e + 1].x >= (uint64_t) jf + 16)) {
+						// ONE exception among the thread's 16 values, at element x: 15 symbols in a row, those
+						// from x on moved up by one, the exception's delta put in the gap (cf. ex_decode2_kernel)
+						const uint32_t x = nextpos - (uint32_t) jf;
+						const uint32_t pp = (uint32_t) jf - e;	// payload index of the first one
+						const uint32_t sh = (pp & 3) * 8;
+						uint32_t w[5], b[4];
+#pragma unroll
+						for (int j = 0; j < 5; j++)
+							w[j] = ring32[((pp >> 2) + j) & (HF_RING / 4 - 1)];
+#pragma unroll
+						for (int j = 0; j < 4; j++)
+							b[j] = __funnelshift_r(w[j], w[j + 1], sh);
+#pragma unroll
+						for (int j = 0; j < 4; j++) {
+							const uint32_t up = __funnelshift_l(j ? b[j - 1] : 0u, b[j], 8);	// byte i = symbol i - 1
+							const uint32_t m = x <= 4u * j ? 0u : x >= 4u * j + 4 ? 0xffffffffu : (1u << (8 * (x - 4u * j))) - 1;
+							const uint32_t r = (b[j] & m) | (up & ~m);
+							zz[2 * j] = sext8x2(r, 0x9180);
+							zz[2 * j + 1] = sext8x2(r, 0xb3a2);
+						}
+						const uint32_t v = xs[e].y, dv = (((v >> 1) ^ (0u - (v & 1u))) & 0xffffu) * 0x00010001u;	// trans.c:80-83
+#pragma unroll
+						for (int j = 0; j < 8; j++) {	// (masks, not an indexed store: zz stays in registers)
+							const uint32_t hit = (x >> 1) == (uint32_t) j ? ((x & 1) ? 0xffff0000u : 0x0000ffffu) : 0u;
+							zz[j] = (zz[j] & ~hit) | (dv & hit);
+						}
 					} else
 #pragma unroll
 					for (int el = 0; el < 16; el++) {
