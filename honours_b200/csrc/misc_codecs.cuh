@@ -252,7 +252,10 @@ __device__ __forceinline__ void mc_put(const uint32_t (&e)[16], uint32_t bits, u
 }
 
 // coding sweep
-__global__ void __launch_bounds__(NT, 4) mc_encode_kernel(const __grid_constant__ McArgs a)
+#ifndef PG_MC_CTAS
+#define PG_MC_CTAS 4
+#endif
+__global__ void __launch_bounds__(NT, PG_MC_CTAS) mc_encode_kernel(const __grid_constant__ McArgs a)
 {
 	__shared__ __align__(16) uint8_t s_stage[MC_STAGE];
 	__shared__ __align__(16) uint16_t s_x[MC_XPAD];
@@ -381,7 +384,7 @@ __device__ __forceinline__ void mc_window(uint32_t stage_sa, uint32_t pos, uint3
 	hi = __funnelshift_r(w1, w2, pos);
 }
 
-__global__ void __launch_bounds__(NT, 4) mc_decode_kernel(const __grid_constant__ McArgs a)
+__global__ void __launch_bounds__(NT, PG_MC_CTAS) mc_decode_kernel(const __grid_constant__ McArgs a)
 {
 	__shared__ __align__(16) uint8_t s_stage[MC_STAGE + 16];
 	__shared__ __align__(16) uint32_t s_out[MT / 2 + 8];	// the tile's samples on their way out

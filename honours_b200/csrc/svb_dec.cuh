@@ -285,6 +285,38 @@ __global__ void __launch_bounds__(NT, PG_DEC_CTAS) svb_dec2_kernel(const __grid_
 					uint32_t w[4];
 					stage_words_any(s_in, p, w);
 					unzigzag_bytes_x16(w, d);
+				} else if (vah == 0xffffu && (flh & (flh - 1)) == 0) {
+					// ONE two-byte value among the thread's 16, at element x (one step in three has such a
+					// thread at NA12878's rate, and the element loop below holds its warp, and with it the
+					// CTA's next barrier, for 16 dependent shared-memory loads): 17 bytes in a row, those
+					// after element x moved down by one, the value's 16 bits put in its place
+					const uint32_t x = __ffs(flh) - 1;
+					const uint32_t *w32 = reinterpret_cast<const uint32_t *>(s_in) + (p >> 2);
+					const uint32_t sh = (p & 3) * 8;
+					uint32_t u[6], b[5], r[4];
+#pragma unroll
+					for (int j = 0; j < 6; j++)
+						u[j] = w32[j];
+#pragma unroll
+					for (int j = 0; j < 5; j++)
+						b[j] = __funnelshift_r(u[j], u[j + 1], sh);
+#pragma unroll
+					for (int j = 0; j < 4; j++) {
+						const uint32_t dn = __funnelshift_r(b[j], b[j + 1], 8);	// byte i = byte i + 1
+						const uint32_t m = x + 1 <= 4u * j ? 0u : x + 1 >= 4u * j + 4 ? 0xffffffffu : (1u << (8 * (x + 1 - 4u * j))) - 1;
+						r[j] = (b[j] & m) | (dn & ~m);
+					}
+					unzigzag_bytes_x16(r, d);
+					const uint32_t q = x >> 2;
+					const uint32_t wl = q == 0 ? b[0] : q == 1 ? b[1] : q == 2 ? b[2] : b[3];
+					const uint32_t wh = q == 0 ? b[1] : q == 1 ? b[2] : q == 2 ? b[3] : b[4];
+					const uint32_t zx = __funnelshift_r(wl, wh, 8 * (x & 3)) & 0xffffu;
+					const uint32_t dv = (((zx >> 1) ^ (0u - (zx & 1u))) & 0xffffu) * 0x00010001u;	// trans.c:80-83
+#pragma unroll
+					for (int j = 0; j < 8; j++) {	// (masks, not an indexed store: d stays in registers)
+						const uint32_t hit = (x >> 1) == (uint32_t) j ? ((x & 1) ? 0xffff0000u : 0x0000ffffu) : 0u;
+						d[j] = (d[j] & ~hit) | (dv & hit);
+					}
 				} else {
 					const uint8_t *q = s_in + p;
 					uint32_t zz[8];
