@@ -1121,12 +1121,34 @@ __device__ __forceinline__ void ex_store_slice_packed(const uint32_t (&qv)[4], u
 	__syncwarp();
 }
 
+#ifndef PG_EMIT_RING
+#define PG_EMIT_RING 4	// tiles of low bytes per warp on their way through shared memory (4 / 6 / 8: the same)
+#endif
+// four words holding the 16 bytes at stage[16 i + al .. + 16), 0 < al < 16 the same in every lane
+// (two conflict-free 128-bit loads)
+__device__ __forceinline__ void stage_words16(const uint8_t *stage, uint32_t al, int i, uint32_t (&w)[4])
+{
+	const uint4 a = reinterpret_cast<const uint4 *>(stage)[i], b = reinterpret_cast<const uint4 *>(stage)[i + 1];
+	uint32_t u0, u1, u2, u3, u4;
+	switch (al >> 2) {
+	case 0: u0 = a.x; u1 = a.y; u2 = a.z; u3 = a.w; u4 = b.x; break;
+	case 1: u0 = a.y; u1 = a.z; u2 = a.w; u3 = b.x; u4 = b.y; break;
+	case 2: u0 = a.z; u1 = a.w; u2 = b.x; u3 = b.y; u4 = b.z; break;
+	default: u0 = a.w; u1 = b.x; u2 = b.y; u3 = b.z; u4 = b.w; break;
+	}
+	const uint32_t sh = (al & 3) * 8;
+	w[0] = __funnelshift_r(u0, u1, sh);
+	w[1] = __funnelshift_r(u1, u2, sh);
+	w[2] = __funnelshift_r(u2, u3, sh);
+	w[3] = __funnelshift_r(u3, u4, sh);
+}
 #ifndef PG_EMIT_CTAS
-#define PG_EMIT_CTAS 4	// (64 registers: the walk's pointers and the prefetched slice stay in registers)
+#define PG_EMIT_CTAS 5	// (48 registers: nothing of the slices ahead is held in them; 4: 52.4, 5: 53.4, 6: 53.2, 8: 45.8 %)
 #endif
 __global__ void __launch_bounds__(NT, PG_EMIT_CTAS) ex_emit_bytes_kernel(const __grid_constant__ ExArgs a)
 {
 	__shared__ __align__(16) uint8_t s_line[NW][512 + 16];
+	__shared__ __align__(16) uint8_t s_ring[NW][PG_EMIT_RING][512];
 	__shared__ uint32_t s_read;
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	if (a.hdr->error & (ERR_CAPACITY | ERR_SCRATCH))
@@ -1196,12 +1218,11 @@ __global__ void __launch_bounds__(NT, PG_EMIT_CTAS) ex_emit_bytes_kernel(const _
 		ex_issue(a.samples, a.nsamples, A, E0);
 		const uint32_t eb0 = __ldg(a.t_eb + rec0);
 		if (t_in > 1) {
-			// records two tiles ahead, low bytes one tile ahead (in registers; PG_PF_EMIT tiles
-			// ahead in L2); every address advances by a constant.  The low bytes are loaded at the
-			// DESTINATION's 16-byte phase s: five 32-bit words per lane, so that lane j holds the
-			// aligned output word j after four funnel shifts, and one byte for each of the < 16
-			// bytes either side.  A slice with an exception is computed again from its samples
-			// (asked from L2 when its record arrives).
+			// records two tiles ahead, low bytes PG_EMIT_RING tiles ahead (shared memory; the first ones
+			// also asked from L2 at once); every address advances by a constant.  A slice's low bytes are
+			// read from the ring at the DESTINATION's 16-byte phase s, so that lane j holds the aligned
+			// output word j, and one byte for each of the < 16 bytes either side.  A slice with an
+			// exception is computed again from its samples (asked from L2 when its record arrives).
 			const uint8_t *lp = reinterpret_cast<const uint8_t *>(ex_lowb_ptr(a.lowb, A, 1, 32 * warp));
 			const uint4 *sp = a.samples + A + XG + 2 * tid;
 			const uint32_t *pe = a.t_eb + rec0 + NW;
@@ -1218,58 +1239,53 @@ __global__ void __launch_bounds__(NT, PG_EMIT_CTAS) ex_emit_bytes_kernel(const _
 					prefetch_l2(lp + k * XT + 16 * lane);
 			prefetch_tail(t_in);
 			edge_finish(0, E0, eb0);
-			uint32_t W[6] = {0, 0, 0, 0, 0, 0};
-			// byte k of the slice that lane < 16 copies by itself: the 16 - s bytes before the first
-			// aligned word, the s bytes after the last one
-			auto issue = [&](uint32_t nx, const uint8_t *D) {
-				if (nx == 0) {
-					const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(D) & 15);
-					if (lane > 0 || s == 0) {
-						const uint8_t *p = lp + ((16 * lane - (int) s) & ~3);
-						asm("ld.global.cs.u32 %0, [%5];\n\tld.global.cs.u32 %1, [%5+4];\n\tld.global.cs.u32 %2, [%5+8];\n\t"
-						    "ld.global.cs.u32 %3, [%5+12];\n\tld.global.cs.u32 %4, [%5+16];"
-						    : "=r"(W[0]), "=r"(W[1]), "=r"(W[2]), "=r"(W[3]), "=r"(W[4])
-						    : "l"(p));
-					}
-					if (s && lane < 16)
-						W[5] = __ldcs(lp + ((uint32_t) lane < 16 - s ? lane : 496 + lane));
-				} else {
-					prefetch_l2(sp);
-				}
+			// the warp's low bytes, PG_EMIT_RING tiles ahead, through a ring in shared memory (cp.async: no
+			// register waits for them, and the destination's phase is dealt with when they are read)
+			const uint8_t *lp0 = lp;
+			auto ring_issue = [&](uint32_t t) {
+				if (t < t_in)
+					cp_async16(s_ring[warp][t % PG_EMIT_RING] + 16 * lane, lp0 + (uint64_t) (t - 1) * XT + 16 * lane);
+				cp_async_commit();
 			};
-			issue(nx1, Db - eb1);
-#pragma unroll 2
-			for (uint32_t t = 1; t < t_in; t++) {
-				uint32_t C[6];
 #pragma unroll
-				for (int k = 0; k < 6; k++)
-					C[k] = W[k];
+			for (int k = 1; k <= PG_EMIT_RING; k++)
+				ring_issue(k);
+			if (nx1)
+				prefetch_l2(sp);
+#pragma unroll 1
+			for (uint32_t t = 1; t < t_in; t++) {
 				const uint32_t eb = eb1, nx = nx1;
 				uint8_t *D = Db - eb;
 				const uint4 *spc = sp;
 				eb1 = eb2;
 				nx1 = nx2;
-				lp += XT;
 				sp += XG;
 				pe += NW;
 				Db += XT;
-				if (t + PG_PF_EMIT < t_in)
-					prefetch_l2(lp + (PG_PF_EMIT - 1) * XT + 16 * lane);
 				if (t + 1 < t_in) {
-					issue(nx1, Db - eb1);
+					if (nx1)
+						prefetch_l2(sp);
 					if (t + 2 < t_in) {
 						eb2 = __ldg(pe + NW);
 						nx2 = __ldg(pe + dnx + NW);
 					}
 				}
+				asm volatile("cp.async.wait_group %0;" ::"n"(PG_EMIT_RING - 1) : "memory");
+				__syncwarp();
 				if (nx == 0) {
-					const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(D) & 15), bs = ((16 - s) & 3) * 8;
-					if (lane > 0 || s == 0)
-						reinterpret_cast<uint4 *>(D - s)[lane] =
-							make_uint4(__funnelshift_r(C[0], C[1], bs), __funnelshift_r(C[1], C[2], bs),
-								   __funnelshift_r(C[2], C[3], bs), __funnelshift_r(C[3], C[4], bs));
-					if (s && lane < 16)
-						D[(uint32_t) lane < 16 - s ? lane : 496 + lane] = (uint8_t) C[5];
+					const uint8_t *S = s_ring[warp][t % PG_EMIT_RING];
+					const uint32_t s = (uint32_t) (reinterpret_cast<uintptr_t>(D) & 15);
+					if (s == 0) {
+						reinterpret_cast<uint4 *>(D)[lane] = reinterpret_cast<const uint4 *>(S)[lane];
+					} else {
+						if (lane > 0) {	// aligned word `lane` = slice bytes [16 lane - s, 16 lane - s + 16)
+							uint32_t w[4];
+							stage_words16(S - 16, 16 - s, lane, w);
+							reinterpret_cast<uint4 *>(D - s)[lane] = make_uint4(w[0], w[1], w[2], w[3]);
+						}
+						if (lane < 16)	// the 16 - s bytes before the first aligned word, the s bytes after the last
+							D[(uint32_t) lane < 16 - s ? lane : 496 + lane] = S[(uint32_t) lane < 16 - s ? lane : 496 + lane];
+					}
 				} else {
 					ExRaw R;
 					R.xa = __ldg(spc);
@@ -1282,7 +1298,11 @@ __global__ void __launch_bounds__(NT, PG_EMIT_CTAS) ex_emit_bytes_kernel(const _
 								__byte_perm(v.z[4], v.z[5], 0x6420), __byte_perm(v.z[6], v.z[7], 0x6420)};
 					ex_store_slice_packed(qv, ~v.exc & 0xffffu, D, line, lane);
 				}
+				__syncwarp();	// (every lane has read the stage)
+				ring_issue(t + PG_EMIT_RING);
 			}
+			cp_async_wait_all();
+			__syncwarp();
 		} else {
 			edge_finish(0, E0, eb0);
 		}
