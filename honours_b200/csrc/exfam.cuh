@@ -853,7 +853,7 @@ __device__ __forceinline__ uint32_t he_put(const uint32_t (&e)[16], uint32_t a0,
 		const uint32_t c = e[i] >> 8;
 		a0 |= __funnelshift_l(0u, c, pos);	// (shifts by pos & 31)
 		const uint32_t a1 = __funnelshift_l(c, 0u, pos);
-		const uint32_t np = pos + (e[i] & 0xffu);
+		const uint32_t np = pos + e[i];	// (only bits 0..5 of a position are ever looked at: the code above bit 8 may ride along)
 		if ((np ^ pos) & 32u) {		// a code is 24 bits at most: one word boundary at most
 			if (EDGE || i < 8) {
 				if (got)
