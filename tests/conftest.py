@@ -64,3 +64,19 @@ def svb0124_stream(rng, n, p4):
             b[-1] |= 1          # (a nonzero top byte, as an encoder would have it)
         data += b
     return keys.tobytes() + bytes(data)
+
+
+def narrow_reads(rng):
+    """signals whose zd values are tiny or sparse: widths 0 .. 3 for uint-zd (threads that bring fewer
+    than 32 bits: the packer's OR path), mostly-zero values for svb0124-zd (threads with under 4 bytes)"""
+    out = []
+    for n in (1, 2, 17, 4096, 4097, 9001, 20000):
+        out.append(_np.full(n, 321, dtype=_np.int16))                                    # constant: zd = 0, width 0
+        out.append((700 - _np.cumsum(rng.integers(0, 2, n))).astype(_np.int16))          # steps of 0 / -1: zd in {0, 1}
+        out.append((100 + _np.cumsum(rng.integers(0, 2, n))).astype(_np.int16))          # steps of 0 / +1: zd in {0, 2}
+        d = _np.zeros(n, dtype=_np.int64)
+        k = rng.random(n) < 0.02
+        d[k] = rng.integers(-300, 300, int(k.sum()))                                   # flat with rare jumps
+        out.append((1000 + _np.cumsum(d)).astype(_np.int16))
+        out.append((_np.arange(n) % 7 - 3).astype(_np.int16))                            # small sawtooth: width 3..4
+    return out

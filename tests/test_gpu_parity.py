@@ -8,7 +8,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import svb0124_stream
+from conftest import narrow_reads, svb0124_stream
 
 pytestmark = pytest.mark.gpu
 
@@ -141,26 +141,10 @@ def test_long_read_many_tiles(gpu, oracle):
         assert rc == 0 and np.array_equal(back, s)
 
 
-def _narrow_reads(rng):
-    """signals whose zd values are tiny or sparse: widths 0 .. 3 for uint-zd (threads that bring fewer
-    than 32 bits: the packer's OR path), mostly-zero values for svb0124-zd (threads with under 4 bytes)"""
-    out = []
-    for n in (1, 2, 17, 4096, 4097, 9001, 20000):
-        out.append(np.full(n, 321, dtype=np.int16))                                    # constant: zd = 0, width 0
-        out.append((700 - np.cumsum(rng.integers(0, 2, n))).astype(np.int16))          # steps of 0 / -1: zd in {0, 1}
-        out.append((100 + np.cumsum(rng.integers(0, 2, n))).astype(np.int16))          # steps of 0 / +1: zd in {0, 2}
-        d = np.zeros(n, dtype=np.int64)
-        k = rng.random(n) < 0.02
-        d[k] = rng.integers(-300, 300, int(k.sum()))                                   # flat with rare jumps
-        out.append((1000 + np.cumsum(d)).astype(np.int16))
-        out.append((np.arange(n) % 7 - 3).astype(np.int16))                            # small sawtooth: width 3..4
-    return out
-
-
 @pytest.mark.parametrize("method", ["svb0124_zd", "uint_zd", "svb16_zd", "shuff_vbe21_zd"])
 def test_narrow_and_sparse_values(gpu, checker, method):
     rng = np.random.default_rng(77)
-    reads = _narrow_reads(rng)
+    reads = narrow_reads(rng)
     if method.startswith("shuff"):     # (a stream without payload symbols cannot be read back, huffman.c:706: tested elsewhere)
         reads = [r for r in reads if r.size > 2]
     for s in reads:     # per read (the press.h-shaped calls)

@@ -153,6 +153,23 @@ def test_scalar_twin_nosimd_equals_simd(oracle, ref):
         assert rc == 0 and np.array_equal(back, s)
 
 
+def test_narrow_and_sparse_values_pinned(oracle, ref):
+    """constant, staircase, rare-jump and sawtooth signals (uint-zd widths 0 .. 4, mostly-zero svb0124
+    values, Huffman runs of one symbol): the restatement writes the compiled reference's bytes for every
+    method, and each decodes the other's stream"""
+    from conftest import narrow_reads
+    reads = narrow_reads(np.random.default_rng(77))
+    for method in cpu_impl.METHODS:
+        for s in reads:
+            rc0, want = ref.press(method, s)
+            rc, got = oracle.press(method, s)
+            assert rc == rc0 and got == want, (method, s.size)
+            if rc == 0 and not (method.startswith("shuff") and s.size <= 2):
+                a = oracle.depress(method, want, s.size)
+                b = ref.depress(method, got, s.size)
+                assert a[0] == b[0] == 0 and np.array_equal(a[1], s) and np.array_equal(b[1], s), (method, s.size)
+
+
 def test_svb0124_four_byte_values_pinned(oracle, ref):
     """svb0124-zd decode of hand-made streams with 4-byte values (the reference's encoder never writes
     one for a 16-bit signal; its decoder takes them and keeps their low 16 bits, trans.c:272-282 ->
