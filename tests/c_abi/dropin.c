@@ -203,6 +203,42 @@ static int test_shuffman_vbe21_zd_gpu(const int16_t *sigs, uint32_t nr_sigs)
 	return 0;
 }
 
+/* press/test.c (svb0124_zd, press.h:332-336): depress nin = SAMPLES */
+static int test_svb0124_zd_gpu(const int16_t *sigs, uint64_t nr_sigs)
+{
+	uint64_t pressbound = svb0124_zd_gpu_bound_16(nr_sigs);
+	uint8_t *sigs_press = malloc(pressbound);
+	uint64_t press_len = pressbound, depress_len = nr_sigs;
+	int16_t *sigs_depress = malloc(nr_sigs * sizeof *sigs_depress);
+	ASSERT(sigs_press && sigs_depress);
+	svb0124_zd_gpu_press_16(sigs, nr_sigs, sigs_press, &press_len);
+	ASSERT(press_len > 0 && press_len <= pressbound);
+	svb0124_zd_gpu_depress_16(sigs_press, nr_sigs, sigs_depress, &depress_len);
+	ASSERT(depress_len == nr_sigs && memcmp(sigs, sigs_depress, nr_sigs * sizeof *sigs) == 0);
+	report("svb0124_zd_gpu", nr_sigs, sigs_press, press_len);
+	free(sigs_press);
+	free(sigs_depress);
+	return 0;
+}
+
+/* press/test.c (uint_zd, press.h:106-112: uint_zd_get_minbits_16 + uint_zd_press_16 in one call) */
+static int test_uint_zd_gpu(const int16_t *sigs, uint64_t nr_sigs)
+{
+	uint64_t pressbound = uint_zd_gpu_bound_16(nr_sigs);
+	uint8_t *sigs_press = malloc(pressbound);
+	uint64_t press_len = pressbound, depress_len = nr_sigs;
+	int16_t *sigs_depress = malloc(nr_sigs * sizeof *sigs_depress);
+	ASSERT(sigs_press && sigs_depress);
+	ASSERT(uint_zd_gpu_press_16(sigs, nr_sigs, sigs_press, &press_len) == 0);
+	ASSERT(press_len > 0 && press_len <= pressbound);
+	ASSERT(uint_zd_gpu_depress_16(sigs_press, nr_sigs, sigs_depress, &depress_len) == 0);	/* nin = samples, press.h:111 */
+	ASSERT(depress_len == nr_sigs && memcmp(sigs, sigs_depress, nr_sigs * sizeof *sigs) == 0);
+	report("uint_zd_gpu", nr_sigs, sigs_press, press_len);
+	free(sigs_press);
+	free(sigs_depress);
+	return 0;
+}
+
 int main(int argc, char **argv)
 {
 	FILE *fp;
@@ -240,6 +276,8 @@ int main(int argc, char **argv)
 		bad |= test_vbe21_zd_gpu(s, (uint32_t) n);
 		bad |= test_hasgam_vbsse21_zdq_gpu(s, (uint32_t) n);
 		bad |= test_shuffman_vbe21_zd_gpu(s, (uint32_t) n);
+		bad |= test_svb0124_zd_gpu(s, n);
+		bad |= test_uint_zd_gpu(s, n);
 	}
 	press_gpu_shutdown();
 	free(offsets);
@@ -248,6 +286,6 @@ int main(int argc, char **argv)
 		fprintf(stderr, "dropin: FAILED\n");
 		return 1;
 	}
-	fprintf(stderr, "dropin ok: %" PRIu64 " reads x 5 methods\n", nreads);
+	fprintf(stderr, "dropin ok: %" PRIu64 " reads x 7 methods\n", nreads);
 	return 0;
 }

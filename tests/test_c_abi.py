@@ -70,11 +70,12 @@ def test_dropin_round_trips_fixture_reads(oracle, tmp_path):
     r = subprocess.run([os.path.join(CABI, "dropin"), str(p), table], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
     name = {"svb12_zd_gpu": "svb16_zd", "svb12_zd_nosimd_gpu": "svb16_zd", "vbe21_zd_gpu": "vbe21_zd",
-            "hasgam_vbsse21_zdq_gpu": "ex_zd", "shuffman_vbe21_zd_gpu": "shuff_vbe21_zd"}
+            "hasgam_vbsse21_zdq_gpu": "ex_zd", "shuffman_vbe21_zd_gpu": "shuff_vbe21_zd",
+            "svb0124_zd_gpu": "svb0124_zd", "uint_zd_gpu": "uint_zd"}
     lines = [ln.split("\t") for ln in r.stdout.strip().split("\n")]
-    assert len(lines) == 5 * len(reads)
+    assert len(lines) == 7 * len(reads)
     for i, (m, n, nbytes, h) in enumerate(lines):
-        s = reads[i // 5]
+        s = reads[i // 7]
         rc, st = oracle.press(name[m], s)
         assert rc == 0 and int(n) == s.size and int(nbytes) == len(st), (m, n)
         assert h == f"{cpu_impl.fnv1a64(st):016x}", (m, n)
