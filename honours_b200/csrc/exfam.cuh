@@ -878,7 +878,7 @@ __device__ __forceinline__ void sred_or(uint32_t saddr, uint32_t v)	// OR into a
 }
 
 #ifndef PG_HE_CTAS
-#define PG_HE_CTAS 4
+#define PG_HE_CTAS 5	// (47 registers; 4: 21.1, 5 and 6: 21.3 % of HBM peak)
 #endif
 __global__ void __launch_bounds__(NT, PG_HE_CTAS) huff_emit_kernel(const __grid_constant__ ExArgs a)
 {
